@@ -1,0 +1,164 @@
+/* nerf_b200.h -- C ABI of libnerf_b200.so (sm_100a only).
+ *
+ * The reference (stanford-iprl-lab/nerf_shared) has no FFI of its own: its hot path is a
+ * stream of ATen ops launched from Python.  Each entry point below replaces the ATen call
+ * sites of one stage of that path; the `replaces:` line cites them (file:line in the
+ * reference tree).  The Python side (nerf_shared_b200/_lib.py) binds these with ctypes;
+ * INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host; row-major, fp32
+ *     unless stated; the library never allocates or frees caller-visible memory;
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), does no
+ *     host synchronisation and is CUDA-graph capturable;
+ *   - return value: 0 = ok, <0 = argument error (NB_E_*), >0 = cudaError_t;
+ *     nb_last_error() returns a thread-local message for the last non-zero return;
+ *   - there is no CPU fallback: nb_init() fails unless the device is compute capability 10.x.
+ */
+#ifndef NERF_B200_H_
+#define NERF_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NB_VERSION 100
+#define NB_API __attribute__((visibility("default")))
+
+#define NB_E_ARG (-1)       /* bad pointer / size / flag */
+#define NB_E_UNSUPPORTED (-2) /* configuration the sm_100a kernels do not implement */
+#define NB_E_DEVICE (-3)    /* not an sm_100 device */
+
+/* ---- library state --------------------------------------------------------------- */
+NB_API int nb_version(void);
+NB_API const char* nb_last_error(void);
+/* Checks that `device` is sm_100 and sets the kernels' dynamic shared-memory attributes. */
+NB_API int nb_init(int device);
+NB_API int nb_shutdown(void);
+/* Number of kernels this library has launched since load (all streams); for bench.py. */
+NB_API int64_t nb_launch_count(void);
+
+/* ---- rays ------------------------------------------------------------------------ */
+/* Pinhole rays for the full H x W grid.
+ * replaces: utils.get_rays utils.py:33-42 (+ viewdir normalisation render_utils.py:211).
+ * c2w: 3 rows x 4 cols with row stride `c2w_ld` floats.  rays_o/rays_d: [H*W,3].
+ * viewdirs: [H*W,3] or NULL.  Bit-exact with the reference's CPU result for rays_o/rays_d. */
+NB_API int nb_get_rays_fwd(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, int c2w_ld,
+                    float* rays_o, float* rays_d, float* viewdirs, void* stream);
+/* Same for a list of `n` pixels, pix[k] = y*W + x (int64): only the selected rays are made.
+ * replaces: get_rays + fancy-index at utils.py:419,437-438 and demo_est_rel_pose.py:82-84. */
+NB_API int nb_get_rays_sel_fwd(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, int c2w_ld,
+                        const int64_t* pix, int64_t n, float* rays_o, float* rays_d, float* viewdirs, void* stream);
+/* Gradient of the above wrt c2w[:3,:4]; pix may be NULL (full grid, n = H*W).
+ * d_rays_o / d_rays_d: [n,3] or NULL.  d_c2w: 12 floats, row-major 3x4, ACCUMULATED into
+ * (caller zeroes).  replaces: autograd of utils.py:37-41 (demo_est_rel_pose.py:97). */
+NB_API int nb_get_rays_bwd(int H, int W, float fx, float fy, float cx, float cy, const int64_t* pix, int64_t n,
+                    const float* d_rays_o, const float* d_rays_d, float* d_c2w, void* stream);
+/* viewdirs = rays_d / |rays_d| and its backward.  replaces: render_utils.py:211. */
+NB_API int nb_normalize_fwd(const float* v, int64_t n, float* out, void* stream);
+NB_API int nb_normalize_bwd(const float* v, const float* d_out, int64_t n, float* d_v, void* stream);
+/* NDC reparametrisation.  replaces: utils.ndc_rays utils.py:54-71 (bit-exact forward). */
+NB_API int nb_ndc_rays_fwd(int H, int W, double focal, double near_, const float* rays_o, const float* rays_d, int64_t n,
+                    float* out_o, float* out_d, void* stream);
+NB_API int nb_ndc_rays_bwd(int H, int W, double focal, double near_, const float* rays_o, const float* rays_d,
+                    const float* d_out_o, const float* d_out_d, int64_t n, float* d_rays_o, float* d_rays_d,
+                    void* stream);
+
+/* ---- sampling along the ray ---------------------------------------------------------- */
+/* Stratified depths and sample positions.
+ * replaces: render_utils.py:105-131.
+ * rays: [n, ld] rows = o(3) d(3) near far [viewdirs(3)] exactly as Renderer.render builds
+ * them (render_utils.py:223-226).  t_vals: [S] = torch.linspace(0,1,S) (passed in because
+ * linspace is not reproducible by a closed form).  t_rand: [n,S] uniform
+ * draws or NULL (perturb == 0).  z: [n,S] out (bit-exact).  pts: [n,S,3] out or NULL. */
+NB_API int nb_sample_coarse(const float* rays, int64_t n, int ld, const float* t_vals, const float* t_rand, int S,
+                     int lindisp, float* z, float* pts, void* stream);
+/* pts[r,s,:] = o[r] + d[r]*z[r,s] and its backward (d_o = sum_s d_pts, d_d = sum_s z d_pts).
+ * replaces: render_utils.py:131,148 and their autograd. */
+NB_API int nb_ray_points_fwd(const float* rays_o, const float* rays_d, const float* z, int64_t n, int S, float* pts,
+                      void* stream);
+NB_API int nb_ray_points_bwd(const float* z, const float* d_pts, int64_t n, int S, float* d_rays_o, float* d_rays_d,
+                      void* stream);
+/* Hierarchical resampling: inverse-CDF samples of the coarse weights, merged into the
+ * coarse depths and sorted.  replaces: utils.sample_pdf utils.py:74-117 and the
+ * sort/cat/std at render_utils.py:141-147,168.
+ * z: [n,S], weights: [n,S] (the interior S-2 are used), u: [n,I] or NULL (det: u=u_det[I],
+ * u_det = torch.linspace(0,1,I)).  Outputs: z_out [n,S+I] sorted; z_std [n] or NULL;
+ * z_samples [n,I] or NULL (unsorted, as sample_pdf returns them). */
+NB_API int nb_sample_pdf_merge(const float* z, const float* weights, const float* u, const float* u_det, int64_t n, int S,
+                        int I, float* z_out, float* z_std, float* z_samples, void* stream);
+/* utils.sample_pdf on explicit bins (utils.py:74-117): bins [n,B], weights [n,B-1],
+ * u [n,I] or NULL (det, u_det [I]) -> samples [n,I]. */
+NB_API int nb_sample_pdf(const float* bins, const float* weights, const float* u, const float* u_det, int64_t n, int B,
+                         int I, float* samples, void* stream);
+/* The inverse-CDF step alone, from a caller-supplied cdf (bit-exact searchsorted indices).
+ * bins/cdf: [n,B]; u: [n,I]; samples: [n,I]; inds: [n,I] int64 (searchsorted right=True).
+ * replaces: utils.py:100-115. */
+NB_API int nb_invert_cdf(const float* bins, const float* cdf, const float* u, int64_t n, int B, int I, float* samples,
+                  int64_t* inds, void* stream);
+
+/* ---- volume compositing -------------------------------------------------------------- */
+/* replaces: Renderer.raw2outputs render_utils.py:241-290.
+ * raw: [n,S,4]; z: [n,S]; rays_d: [n,3]; noise: [n,S] (already scaled by raw_noise_std) or NULL.
+ * Outputs (any may be NULL): rgb_map [n,3], disp [n], acc [n], weights [n,S], depth [n]. */
+NB_API int nb_composite_fwd(const float* raw, const float* z, const float* rays_d, const float* noise, int64_t n, int S,
+                     int white_bkgd, float* rgb_map, float* disp, float* acc, float* weights, float* depth,
+                     void* stream);
+/* Hand-written reverse-scan backward.  Upstream grads d_rgb [n,3], d_disp, d_acc, d_depth
+ * [n] (any may be NULL = zero).  Outputs: d_raw [n,S,4]; d_rays_d [n,3] or NULL
+ * (through |rays_d| in the interval lengths, render_utils.py:259). */
+NB_API int nb_composite_bwd(const float* raw, const float* z, const float* rays_d, const float* noise, int64_t n, int S,
+                     int white_bkgd, const float* d_rgb, const float* d_disp, const float* d_acc,
+                     const float* d_depth, float* d_raw, float* d_rays_d, void* stream);
+
+/* ---- the NeRF MLP (positional encoding fused) ---------------------------------------- */
+/* Network shape (nerf.py:61-94, use_viewdirs=True): D=8, W=256, skip after layer 4,
+ * L_pts / L_dirs encoding octaves (10 / 4 in every shipped config but one). */
+typedef struct NbMlpWeights {
+  /* fp32 nn.Linear parameters, PyTorch layout [out,in] row-major */
+  const float* pts_w[8];
+  const float* pts_b[8];
+  const float* feature_w; const float* feature_b; /* [256,256] */
+  const float* alpha_w;   const float* alpha_b;   /* [1,256]   */
+  const float* views_w;   const float* views_b;   /* [128,256+in_views] */
+  const float* rgb_w;     const float* rgb_b;     /* [3,128]   */
+  int L_pts;   /* multires        -> input_ch = 3+6*L_pts */
+  int L_dirs;  /* multires_views  -> input_ch_views = 3+6*L_dirs */
+} NbMlpWeights;
+
+/* fp32 CUDA-core evaluation (parity / debugging path, exact fp32 operands).
+ * pts: [M,3]; viewdirs: [M/S,3] (one per ray, S consecutive samples share it); raw: [M,4].
+ * replaces: NeRF.forward nerf.py:96-134. */
+NB_API int nb_mlp_fwd_f32(const NbMlpWeights* w, const float* pts, const float* viewdirs, int64_t M, int S, float* raw,
+                   void* stream);
+
+/* Size in bytes of the packed bf16 operand blob + fp32 side table used by the tensor-core
+ * kernels for one model. */
+NB_API int64_t nb_mlp_packed_bytes(int L_pts, int L_dirs);
+/* Re-pack fp32 parameters into `packed` (call after every optimizer step). */
+NB_API int nb_mlp_pack(const NbMlpWeights* w, void* packed, void* stream);
+/* Persistent fused tcgen05/TMEM forward: encoding -> 10 GEMM layers -> raw, activations
+ * never leave the SM.  bf16 operands, fp32 accumulation, sigma and rgb heads in fp32.
+ * If `acts` is non-NULL the bf16 layer activations needed by the backward pass are stored
+ * there ([M, NB_ACT_STRIDE] bf16, see nb_mlp_act_stride). */
+NB_API int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, const float* viewdirs, int64_t M,
+                  int S, float* raw, void* acts, void* stream);
+NB_API int nb_mlp_act_stride(void);
+
+/* ---- optimizer ------------------------------------------------------------------------- */
+/* torch.optim.Adam (utils.py:170) on flat fp32 buffers; step is 1-based.
+ * replaces: Adam.step main.py:104. */
+NB_API int nb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                 float eps, int step, float grad_scale, void* stream);
+
+/* ---- self test ------------------------------------------------------------------------- */
+/* D[128,128] = A[128,K] * B[128,K]^T (bf16-rounded operands, fp32 accumulate) through the same
+ * swizzle / descriptor / tcgen05 sequence as nb_mlp_fwd_tc; K in {64,128,192,256}. */
+NB_API int nb_debug_umma(const float* A, const float* B, int K, float* D, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NERF_B200_H_ */

@@ -1,0 +1,343 @@
+"""torch.autograd.Function wrappers around the C ABI (include/nerf_b200.h).
+
+Tensors stay ordinary torch tensors owned by the caching allocator; every kernel is launched on
+torch's current stream.  Nothing here falls back to eager PyTorch math: a missing library or a
+non-sm_100 device raises (see _lib.py).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import check, ensure_device, f32c, ptr, stream_ptr
+
+_const_cache = {}
+
+
+def linspace01(n: int, device) -> torch.Tensor:
+    """torch.linspace(0, 1, n) evaluated by the CPU ATen kernel (the reference's oracle device;
+    its bits are not reproducible by a closed form) and cached on `device`."""
+    key = (int(n), str(device))
+    t = _const_cache.get(key)
+    if t is None:
+        t = torch.linspace(0.0, 1.0, steps=int(n), device="cpu", dtype=torch.float32).to(device)
+        _const_cache[key] = t
+    return t
+
+
+def _lib_for(t: torch.Tensor):
+    ensure_device(t.device)
+    return _lib.load()
+
+
+# ----------------------------------------------------------------------------------------- rays
+class GetRays(torch.autograd.Function):
+    """utils.get_rays (utils.py:33-42); differentiable wrt c2w (demo_est_rel_pose.py:80-82)."""
+
+    @staticmethod
+    def forward(ctx, c2w, H, W, fx, fy, cx, cy, pix):
+        lib = _lib_for(c2w)
+        c = f32c(c2w)
+        n = H * W if pix is None else pix.numel()
+        rays_o = torch.empty((n, 3), device=c.device, dtype=torch.float32)
+        rays_d = torch.empty((n, 3), device=c.device, dtype=torch.float32)
+        with torch.cuda.device(c.device):
+            check(lib.nb_get_rays_sel_fwd(H, W, fx, fy, cx, cy, ptr(c), c.stride(0), ptr(pix), n, ptr(rays_o),
+                                          ptr(rays_d), None, stream_ptr()), "nb_get_rays")
+        ctx.geom = (H, W, fx, fy, cx, cy)
+        ctx.pix = pix
+        ctx.c2w_shape = tuple(c2w.shape)
+        if pix is None:
+            rays_o, rays_d = rays_o.view(H, W, 3), rays_d.view(H, W, 3)
+        return rays_o, rays_d
+
+    @staticmethod
+    def backward(ctx, g_o, g_d):
+        H, W, fx, fy, cx, cy = ctx.geom
+        ref = g_d if g_d is not None else g_o
+        lib = _lib_for(ref)
+        n = H * W if ctx.pix is None else ctx.pix.numel()
+        go = f32c(g_o).view(-1, 3) if g_o is not None else None
+        gd = f32c(g_d).view(-1, 3) if g_d is not None else None
+        d34 = torch.zeros((3, 4), device=ref.device, dtype=torch.float32)
+        with torch.cuda.device(ref.device):
+            check(lib.nb_get_rays_bwd(H, W, fx, fy, cx, cy, ptr(ctx.pix), n, ptr(go), ptr(gd), ptr(d34), stream_ptr()),
+                  "nb_get_rays_bwd")
+        g = torch.zeros(ctx.c2w_shape, device=ref.device, dtype=torch.float32)
+        g[:3, :4] = d34
+        return g, None, None, None, None, None, None, None
+
+
+class Normalize(torch.autograd.Function):
+    """v / |v| over the last dim (render_utils.py:211)."""
+
+    @staticmethod
+    def forward(ctx, v):
+        lib = _lib_for(v)
+        vc = f32c(v).view(-1, 3)
+        out = torch.empty_like(vc)
+        with torch.cuda.device(v.device):
+            check(lib.nb_normalize_fwd(ptr(vc), vc.shape[0], ptr(out), stream_ptr()), "nb_normalize_fwd")
+        ctx.save_for_backward(vc)
+        ctx.shape = v.shape
+        return out.view(v.shape)
+
+    @staticmethod
+    def backward(ctx, g):
+        (vc,) = ctx.saved_tensors
+        lib = _lib_for(vc)
+        gc = f32c(g).view(-1, 3)
+        dv = torch.empty_like(vc)
+        with torch.cuda.device(vc.device):
+            check(lib.nb_normalize_bwd(ptr(vc), ptr(gc), vc.shape[0], ptr(dv), stream_ptr()), "nb_normalize_bwd")
+        return dv.view(ctx.shape)
+
+
+class NdcRays(torch.autograd.Function):
+    """utils.ndc_rays (utils.py:54-71)."""
+
+    @staticmethod
+    def forward(ctx, rays_o, rays_d, H, W, focal, near):
+        lib = _lib_for(rays_d)
+        o, d = f32c(rays_o).view(-1, 3), f32c(rays_d).view(-1, 3)
+        if o.data_ptr() == rays_o.data_ptr() and not rays_o.is_contiguous():
+            o = o.contiguous()
+        oo, od = torch.empty_like(o), torch.empty_like(d)
+        with torch.cuda.device(d.device):
+            check(lib.nb_ndc_rays_fwd(H, W, float(focal), float(near), ptr(o), ptr(d), o.shape[0], ptr(oo), ptr(od),
+                                      stream_ptr()), "nb_ndc_rays_fwd")
+        ctx.save_for_backward(o, d)
+        ctx.args = (H, W, float(focal), float(near))
+        ctx.shape = rays_d.shape
+        return oo.view(rays_d.shape), od.view(rays_d.shape)
+
+    @staticmethod
+    def backward(ctx, g_o, g_d):
+        o, d = ctx.saved_tensors
+        lib = _lib_for(d)
+        H, W, focal, near = ctx.args
+        go = f32c(g_o).view(-1, 3) if g_o is not None else None
+        gd = f32c(g_d).view(-1, 3) if g_d is not None else None
+        do, dd = torch.empty_like(o), torch.empty_like(d)
+        with torch.cuda.device(d.device):
+            check(lib.nb_ndc_rays_bwd(H, W, focal, near, ptr(o), ptr(d), ptr(go), ptr(gd), o.shape[0], ptr(do), ptr(dd),
+                                      stream_ptr()), "nb_ndc_rays_bwd")
+        return do.view(ctx.shape), dd.view(ctx.shape), None, None, None, None
+
+
+# ------------------------------------------------------------------------------------- sampling
+def sample_coarse(ray_batch: torch.Tensor, n_samples: int, t_rand, lindisp: bool, want_pts: bool = False):
+    """render_utils.py:105-131 -> z [N,S] (and pts [N,S,3]); no gradient (near/far are constants)."""
+    lib = _lib_for(ray_batch)
+    rb = f32c(ray_batch.detach())
+    n, ld = rb.shape
+    z = torch.empty((n, n_samples), device=rb.device, dtype=torch.float32)
+    pts = torch.empty((n, n_samples, 3), device=rb.device, dtype=torch.float32) if want_pts else None
+    tr = f32c(t_rand) if t_rand is not None else None
+    if tr is not None:
+        assert tuple(tr.shape) == (n, n_samples)
+    with torch.cuda.device(rb.device):
+        check(lib.nb_sample_coarse(ptr(rb), n, ld, ptr(linspace01(n_samples, rb.device)), ptr(tr), n_samples,
+                                   int(bool(lindisp)), ptr(z), ptr(pts), stream_ptr()), "nb_sample_coarse")
+    return (z, pts) if want_pts else z
+
+
+class RayPoints(torch.autograd.Function):
+    """pts = o + d * z (render_utils.py:131,148)."""
+
+    @staticmethod
+    def forward(ctx, rays_o, rays_d, z):
+        lib = _lib_for(z)
+        o, d, zc = f32c(rays_o), f32c(rays_d), f32c(z)
+        n, S = zc.shape
+        pts = torch.empty((n, S, 3), device=zc.device, dtype=torch.float32)
+        with torch.cuda.device(zc.device):
+            check(lib.nb_ray_points_fwd(ptr(o), ptr(d), ptr(zc), n, S, ptr(pts), stream_ptr()), "nb_ray_points_fwd")
+        ctx.save_for_backward(zc)
+        return pts
+
+    @staticmethod
+    def backward(ctx, g):
+        (zc,) = ctx.saved_tensors
+        lib = _lib_for(zc)
+        n, S = zc.shape
+        gc = f32c(g)
+        need_o, need_d = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        do = torch.empty((n, 3), device=zc.device, dtype=torch.float32) if need_o else None
+        dd = torch.empty((n, 3), device=zc.device, dtype=torch.float32) if need_d else None
+        if need_o or need_d:
+            with torch.cuda.device(zc.device):
+                check(lib.nb_ray_points_bwd(ptr(zc), ptr(gc), n, S, ptr(do), ptr(dd), stream_ptr()), "nb_ray_points_bwd")
+        return do, dd, None
+
+
+def sample_pdf_merge(z, weights, n_importance: int, u=None, want_samples: bool = False):
+    """utils.sample_pdf + sort/cat/std (utils.py:74-117, render_utils.py:141-147,168); detached."""
+    lib = _lib_for(z)
+    zc, wc = f32c(z.detach()), f32c(weights.detach())
+    n, S = zc.shape
+    z_out = torch.empty((n, S + n_importance), device=zc.device, dtype=torch.float32)
+    z_std = torch.empty((n,), device=zc.device, dtype=torch.float32)
+    z_samples = torch.empty((n, n_importance), device=zc.device, dtype=torch.float32) if want_samples else None
+    uc = f32c(u) if u is not None else None
+    with torch.cuda.device(zc.device):
+        check(lib.nb_sample_pdf_merge(ptr(zc), ptr(wc), ptr(uc), ptr(linspace01(n_importance, zc.device)), n, S,
+                                      n_importance, ptr(z_out), ptr(z_std), ptr(z_samples), stream_ptr()),
+              "nb_sample_pdf_merge")
+    return (z_out, z_std, z_samples) if want_samples else (z_out, z_std)
+
+
+def invert_cdf(bins, cdf, u):
+    """utils.py:100-115 from an explicit cdf -> (samples, searchsorted indices)."""
+    lib = _lib_for(cdf)
+    b, c, uc = f32c(bins), f32c(cdf), f32c(u)
+    n, B = c.shape
+    I = uc.shape[-1]
+    samples = torch.empty((n, I), device=c.device, dtype=torch.float32)
+    inds = torch.empty((n, I), device=c.device, dtype=torch.int64)
+    with torch.cuda.device(c.device):
+        check(lib.nb_invert_cdf(ptr(b), ptr(c), ptr(uc), n, B, I, ptr(samples), ptr(inds), stream_ptr()), "nb_invert_cdf")
+    return samples, inds
+
+
+# ----------------------------------------------------------------------------------- compositing
+class Composite(torch.autograd.Function):
+    """Renderer.raw2outputs (render_utils.py:241-290)."""
+
+    @staticmethod
+    def forward(ctx, raw, z, rays_d, noise, white_bkgd):
+        lib = _lib_for(raw)
+        r, zc, d = f32c(raw), f32c(z), f32c(rays_d)
+        nz = f32c(noise) if noise is not None else None
+        n, S = zc.shape
+        dev = r.device
+        rgb = torch.empty((n, 3), device=dev, dtype=torch.float32)
+        disp = torch.empty((n,), device=dev, dtype=torch.float32)
+        acc = torch.empty((n,), device=dev, dtype=torch.float32)
+        depth = torch.empty((n,), device=dev, dtype=torch.float32)
+        weights = torch.empty((n, S), device=dev, dtype=torch.float32)
+        with torch.cuda.device(dev):
+            check(lib.nb_composite_fwd(ptr(r), ptr(zc), ptr(d), ptr(nz), n, S, int(bool(white_bkgd)), ptr(rgb), ptr(disp),
+                                       ptr(acc), ptr(weights), ptr(depth), stream_ptr()), "nb_composite_fwd")
+        ctx.save_for_backward(r, zc, d, nz)
+        ctx.white = int(bool(white_bkgd))
+        ctx.mark_non_differentiable(weights)
+        return rgb, disp, acc, weights, depth
+
+    @staticmethod
+    def backward(ctx, g_rgb, g_disp, g_acc, g_w, g_depth):
+        r, zc, d, nz = ctx.saved_tensors
+        lib = _lib_for(r)
+        n, S = zc.shape
+        c = lambda g: f32c(g) if g is not None else None
+        d_raw = torch.empty_like(r)
+        d_rd = torch.empty_like(d) if ctx.needs_input_grad[2] else None
+        with torch.cuda.device(r.device):
+            check(lib.nb_composite_bwd(ptr(r), ptr(zc), ptr(d), ptr(nz), n, S, ctx.white, ptr(c(g_rgb)), ptr(c(g_disp)),
+                                       ptr(c(g_acc)), ptr(c(g_depth)), ptr(d_raw), ptr(d_rd), stream_ptr()),
+                  "nb_composite_bwd")
+        return d_raw, None, d_rd, None, None
+
+
+# ------------------------------------------------------------------------------------------ MLP
+def mlp_weight_struct(model) -> _lib.NbMlpWeights:
+    """Fill NbMlpWeights from a nerf.NeRF module's fp32 parameters (no copies)."""
+    w = _lib.NbMlpWeights()
+    for i in range(8):
+        w.pts_w[i] = model.pts_linears[i].weight.data_ptr()
+        w.pts_b[i] = model.pts_linears[i].bias.data_ptr()
+    w.feature_w, w.feature_b = model.feature_linear.weight.data_ptr(), model.feature_linear.bias.data_ptr()
+    w.alpha_w, w.alpha_b = model.alpha_linear.weight.data_ptr(), model.alpha_linear.bias.data_ptr()
+    w.views_w, w.views_b = model.views_linears[0].weight.data_ptr(), model.views_linears[0].bias.data_ptr()
+    w.rgb_w, w.rgb_b = model.rgb_linear.weight.data_ptr(), model.rgb_linear.bias.data_ptr()
+    w.L_pts, w.L_dirs = int(model.multires), int(model.multires_views)
+    return w
+
+
+def mlp_params(model):
+    return ([model.pts_linears[i].weight for i in range(8)] + [model.pts_linears[i].bias for i in range(8)] +
+            [model.feature_linear.weight, model.feature_linear.bias, model.alpha_linear.weight,
+             model.alpha_linear.bias, model.views_linears[0].weight, model.views_linears[0].bias,
+             model.rgb_linear.weight, model.rgb_linear.bias])
+
+
+def packed_weights(model) -> torch.Tensor:
+    """bf16 operand blob + fp32 side table for the tensor-core kernels, re-packed whenever a
+    parameter changed (its autograd version counter or storage moved)."""
+    params = mlp_params(model)
+    for p in params:
+        if p.dtype != torch.float32 or not p.is_contiguous():
+            raise _lib.NerfB200Error("NeRF parameters must be contiguous fp32 tensors")
+    dev = params[0].device
+    lib = _lib_for(params[0])
+    key = tuple((p.data_ptr(), p._version) for p in params)
+    cache = model.__dict__.get("_nb_packed")
+    if cache is not None and cache[0] == key and cache[1].device == dev:
+        return cache[1]
+    nbytes = int(lib.nb_mlp_packed_bytes(int(model.multires), int(model.multires_views)))
+    buf = cache[1] if (cache is not None and cache[1].device == dev and cache[1].numel() == nbytes) else \
+        torch.empty((nbytes,), device=dev, dtype=torch.uint8)
+    w = mlp_weight_struct(model)
+    with torch.cuda.device(dev):
+        check(lib.nb_mlp_pack(C.byref(w), ptr(buf), stream_ptr()), "nb_mlp_pack")
+    model.__dict__["_nb_packed"] = (key, buf)
+    return buf
+
+
+def mlp_forward_f32(model, pts, viewdirs, S):
+    lib = _lib_for(pts)
+    p, v = f32c(pts).view(-1, 3), f32c(viewdirs).view(-1, 3)
+    M = p.shape[0]
+    raw = torch.empty((M, 4), device=p.device, dtype=torch.float32)
+    w = mlp_weight_struct(model)
+    with torch.cuda.device(p.device):
+        check(lib.nb_mlp_fwd_f32(C.byref(w), ptr(p), ptr(v), M, S, ptr(raw), stream_ptr()), "nb_mlp_fwd_f32")
+    return raw
+
+
+def mlp_forward_tc(model, pts, viewdirs, S, save_acts=False):
+    lib = _lib_for(pts)
+    p, v = f32c(pts).view(-1, 3), f32c(viewdirs).view(-1, 3)
+    M = p.shape[0]
+    packed = packed_weights(model)
+    raw = torch.empty((M, 4), device=p.device, dtype=torch.float32)
+    acts = None
+    if save_acts:
+        acts = torch.empty((M, int(lib.nb_mlp_act_stride())), device=p.device, dtype=torch.bfloat16)
+    with torch.cuda.device(p.device):
+        check(lib.nb_mlp_fwd_tc(ptr(packed), int(model.multires), int(model.multires_views), ptr(p), ptr(v), M, S,
+                                ptr(raw), ptr(acts), stream_ptr()), "nb_mlp_fwd_tc")
+    return raw, acts
+
+
+class NerfMLP(torch.autograd.Function):
+    """NeRF.forward (nerf.py:96-134): pts [M,3], viewdirs [M/S,3] -> raw [M,4]."""
+
+    @staticmethod
+    def forward(ctx, pts, viewdirs, S, model, *params):
+        need_grad = any(ctx.needs_input_grad)
+        if model.precision == "fp32":
+            if need_grad:
+                raise _lib.NerfB200Error("precision='fp32' is an inference/parity path; training uses the bf16 kernels")
+            return mlp_forward_f32(model, pts, viewdirs, S)
+        raw, acts = mlp_forward_tc(model, pts, viewdirs, S, save_acts=need_grad)
+        if need_grad:
+            ctx.model, ctx.S = model, S
+            ctx.save_for_backward(f32c(pts).view(-1, 3), f32c(viewdirs).view(-1, 3), acts)
+        return raw
+
+    @staticmethod
+    def backward(ctx, g_raw):
+        from . import _bwd
+        return _bwd.nerf_mlp_backward(ctx, g_raw)
+
+
+def debug_umma(A: torch.Tensor, B: torch.Tensor) -> torch.Tensor:
+    lib = _lib_for(A)
+    a, b = f32c(A), f32c(B)
+    D = torch.empty((128, 128), device=a.device, dtype=torch.float32)
+    with torch.cuda.device(a.device):
+        check(lib.nb_debug_umma(ptr(a), ptr(b), a.shape[1], ptr(D), stream_ptr()), "nb_debug_umma")
+    return D

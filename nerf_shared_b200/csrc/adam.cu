@@ -1,0 +1,34 @@
+// Fused Adam over flat fp32 buffers (torch.optim.Adam semantics, utils.py:170 / main.py:104).
+// Streaming kernel: reads p, g, m, v (16 B/param) and writes p, m, v (12 B/param).
+#include "common.cuh"
+
+namespace nb {
+
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                   float* __restrict__ m, float* __restrict__ v, int64_t n,
+                                                   float step_size, float beta1, float beta2, float eps,
+                                                   float inv_sqrt_bc2, float grad_scale) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float gi = g[i] * grad_scale;
+    float mi = beta1 * m[i] + (1.0f - beta1) * gi;
+    float vi = beta2 * v[i] + (1.0f - beta2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
+    p[i] = p[i] - step_size * (mi / denom);
+  }
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" int nb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                            float eps, int step, float grad_scale, void* stream) {
+  NB_REQUIRE(p && g && m && v && step >= 1, "nb_adam_step: bad arguments");
+  if (n == 0) return 0;
+  double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
+  adam_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(p, g, m, v, n, (float)(lr / bc1), beta1, beta2, eps,
+                                                              (float)(1.0 / sqrt(bc2)), grad_scale);
+  return check_launch("nb_adam_step");
+}

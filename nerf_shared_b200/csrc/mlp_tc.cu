@@ -1,0 +1,552 @@
+// The NeRF MLP on the 5th-generation tensor cores: weight packing, a UMMA self-test and the
+// persistent fused forward kernel.
+//
+// replaces NeRF.forward / MLP (nerf.py:96-134) including both Embedder calls (nerf.py:98,103)
+// and the netchunk loop (nerf.py:106): the encodings are computed in registers and written
+// straight into the first layer's shared-memory operand, activations stay on the SM for all
+// ten GEMM layers, and only raw [M,4] (and, for training, the bf16 activations the backward
+// needs) reach HBM.
+//
+// Tiling.  A tile is 128 samples (UMMA M = 128, one TMEM lane per sample).  A CTA works on two
+// tiles A/B at a time so that the epilogue of one overlaps the MMAs of the other; each tile
+// owns 256 TMEM columns (128 x 256 fp32 accumulator), a 64 KB activation operand (4 K-slabs of
+// [128 x 64] bf16, K-major, 128-byte swizzle) and one 16 KB auxiliary slab that holds the
+// position encoding (layers 0 and 5) and later the view-direction encoding (view branch).
+// Weights are pre-packed (nb_mlp_pack) into 16 KB slabs [128 out x 64 in] in exactly the
+// shared-memory image the UMMA descriptor expects, in consumption order, and streamed
+// L2 -> SMEM with 1-D bulk async copies through a 3-stage mbarrier ring.
+//
+// Warp roles (384 threads): warp 0 = weight producer, warp 1 = MMA issuer, warp 2 = TMEM
+// allocator, warps 4-7 = epilogue of tile A, warps 8-11 = epilogue of tile B.
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace nb {
+
+using namespace ptx;
+
+constexpr int kTileM = 128;
+constexpr int kSlabBytes = 16384;  // [128 x 64] bf16
+constexpr int kStages = 3;
+constexpr int kNumSlabs = 73;
+constexpr int kConstFloats = 3200;
+constexpr int kActStride = 2432;  // bf16 per sample: h0..h7 (8*256) | feature (256) | view hidden (128)
+
+// fp32 side table offsets (floats)
+constexpr int kOffBias = 0;        // 8 x 256 trunk biases
+constexpr int kOffFeatB = 2048;    // 256
+constexpr int kOffViewB = 2304;    // 128
+constexpr int kOffAlphaW = 2432;   // 256
+constexpr int kOffRgbW = 2688;     // 3 x 128
+constexpr int kOffRgbB = 3072;     // 3
+constexpr int kOffAlphaB = 3075;   // 1
+
+// shared memory map (bytes from a 1024-aligned base)
+constexpr uint32_t kSmAct0 = 0, kSmEnc0 = 65536, kSmAct1 = 81920, kSmEnc1 = 147456;
+constexpr uint32_t kSmRing = 163840;
+constexpr uint32_t kSmConst = kSmRing + kStages * kSlabBytes;  // 212992
+constexpr uint32_t kSmBar = kSmConst + kConstFloats * 4;       // 225792
+constexpr uint32_t kSmTmemPtr = kSmBar + 120;
+constexpr uint32_t kSmemBytes = kSmBar + 128 + 1024;           // + alignment slack
+
+__host__ __device__ constexpr int ks_count(int layer) { return layer == 0 ? 1 : ((layer == 5 || layer == 9) ? 5 : 4); }
+__host__ __device__ constexpr int nh_count(int layer) { return layer == 9 ? 1 : 2; }
+__host__ __device__ constexpr int slab_base(int layer) {
+  int b = 0;
+  for (int l = 0; l < layer; ++l) b += ks_count(l) * nh_count(l);
+  return b;
+}
+static_assert(slab_base(10) == kNumSlabs, "slab schedule");
+
+// ------------------------------------------------------------------------------------------
+// weight packing
+// ------------------------------------------------------------------------------------------
+struct SlabSrc {
+  const float* w;  // fp32 [out,in] matrix
+  int ld;          // in-features (row stride)
+  int n0;          // first output row of this slab
+  int k0;          // first input column
+  int kvalid;      // columns actually present (rest is zero padding)
+};
+struct PackArgs {
+  SlabSrc slab[kNumSlabs];
+};
+
+__global__ void __launch_bounds__(256) pack_weights_kernel(PackArgs a, NbMlpWeights w, uint8_t* __restrict__ blob) {
+  // one thread per 16-byte chunk: slab s, row n (0..127), chunk g (0..7)
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < kNumSlabs * 128 * 8) {
+    int s = idx / 1024, rem = idx - s * 1024;
+    int n = rem >> 3, g = rem & 7;
+    const SlabSrc src = a.slab[s];
+    const float* row = src.w + (size_t)(src.n0 + n) * src.ld + src.k0;
+    uint32_t p[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int k = g * 8 + j * 2;
+      float lo = (k < src.kvalid) ? row[k] : 0.f;
+      float hi = (k + 1 < src.kvalid) ? row[k + 1] : 0.f;
+      p[j] = pack_bf16x2(lo, hi);
+    }
+    *reinterpret_cast<uint4*>(blob + (size_t)s * kSlabBytes + sw128_chunk_off(n, g)) = make_uint4(p[0], p[1], p[2], p[3]);
+  }
+  // fp32 side table
+  float* c = reinterpret_cast<float*>(blob + (size_t)kNumSlabs * kSlabBytes);
+  if (idx < kConstFloats) {
+    float v = 0.f;
+    if (idx < 2048) v = w.pts_b[idx >> 8][idx & 255];
+    else if (idx < kOffViewB) v = w.feature_b[idx - kOffFeatB];
+    else if (idx < kOffAlphaW) v = w.views_b[idx - kOffViewB];
+    else if (idx < kOffRgbW) v = w.alpha_w[idx - kOffAlphaW];
+    else if (idx < kOffRgbB) v = w.rgb_w[idx - kOffRgbW];
+    else if (idx < kOffAlphaB) v = w.rgb_b[idx - kOffRgbB];
+    else if (idx == kOffAlphaB) v = w.alpha_b[0];
+    c[idx] = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// UMMA self-test: D[128,128] = A[128,K] * B[128,K]^T through the same swizzle helper,
+// descriptors, tcgen05.mma / commit / ld sequence as the fused kernel (K multiple of 64 <= 256).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) umma_selftest_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                               int K, float* __restrict__ D) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+  const int nslab = K / 64;
+  const uint32_t sA = base, sB = base + nslab * kSlabBytes, sBar = sB + nslab * kSlabBytes, sPtr = sBar + 8;
+  const int row = threadIdx.x, warp = threadIdx.x >> 5;
+  for (int s = 0; s < nslab; ++s)
+    for (int g = 0; g < 8; ++g) {
+      uint32_t pa[4], pb[4];
+      for (int j = 0; j < 4; ++j) {
+        int k = s * 64 + g * 8 + j * 2;
+        pa[j] = pack_bf16x2(A[row * K + k], A[row * K + k + 1]);
+        pb[j] = pack_bf16x2(B[row * K + k], B[row * K + k + 1]);
+      }
+      st_shared_v4(sA + s * kSlabBytes + sw128_chunk_off(row, g), pa[0], pa[1], pa[2], pa[3]);
+      st_shared_v4(sB + s * kSlabBytes + sw128_chunk_off(row, g), pb[0], pb[1], pb[2], pb[3]);
+    }
+  fence_proxy_async();
+  if (threadIdx.x == 0) {
+    mbar_init(sBar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(sPtr, 128);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + (sPtr - base));
+  if (threadIdx.x == 0) {
+    const uint32_t idesc = make_idesc_bf16(128, 128);
+    for (int s = 0; s < nslab; ++s) {
+      uint64_t ad = make_desc_kmajor_sw128(sA + s * kSlabBytes), bd = make_desc_kmajor_sw128(sB + s * kSlabBytes);
+      for (int k16 = 0; k16 < 4; ++k16) umma_bf16(tmem, ad + 2 * k16, bd + 2 * k16, idesc, (s | k16) != 0);
+    }
+    umma_commit(sBar);
+  }
+  mbar_wait(sBar, 0);
+  tc_fence_after();
+  for (int c = 0; c < 4; ++c) {
+    uint32_t v[32];
+    tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c * 32, v);
+    tmem_ld_wait();
+    for (int j = 0; j < 32; ++j) D[row * 128 + c * 32 + j] = __uint_as_float(v[j]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 128);
+}
+
+// ------------------------------------------------------------------------------------------
+// positional encoding in registers (nerf.py:28-41)
+// ------------------------------------------------------------------------------------------
+// sin/cos with a 3-term Cody-Waite reduction by pi/2 (|x| up to a few thousand) and degree-7/8
+// minimax polynomials: max abs error 9e-8 (checked against float64 over [-400, 400]).
+__device__ __forceinline__ void sincos_cw(float x, float& s, float& c) {
+  float k = rintf(x * 0.6366197466850281f);
+  float r = fmaf(k, -1.5707963705062866f, x);
+  r = fmaf(k, 4.371138828673793e-08f, r);
+  r = fmaf(k, 1.7151245100058819e-15f, r);
+  int q = (int)k;
+  float r2 = r * r;
+  float sp = fmaf(r * r2, fmaf(r2, fmaf(r2, -1.9515295891e-4f, 8.3321608736e-3f), -1.6666654611e-1f), r);
+  float cp = fmaf(r2 * r2, fmaf(r2, fmaf(r2, 2.443315711809948e-5f, -1.388731625493765e-3f), 4.166664568298827e-2f),
+                  fmaf(-0.5f, r2, 1.0f));
+  float ss = (q & 1) ? cp : sp;
+  float cc = (q & 1) ? sp : cp;
+  s = (q & 2) ? -ss : ss;
+  c = ((q + 1) & 2) ? -cc : cc;
+}
+
+// e[0..2] = v, e[3+6l+c] = sin(2^l v_c), e[3+6l+3+c] = cos(2^l v_c); octaves 0 and 5 are evaluated
+// directly, the others by angle doubling (abs error < 2e-6, two orders below a bf16 ulp).
+template <int L, int N>
+__device__ __forceinline__ void encode3(float v0, float v1, float v2, float (&e)[N]) {
+  static_assert(3 + 6 * L <= N, "encoding does not fit the operand slab");
+#pragma unroll
+  for (int i = 0; i < N; ++i) e[i] = 0.f;
+  float v[3] = {v0, v1, v2};
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    e[c] = v[c];
+    float s = 0.f, co = 1.f;
+#pragma unroll
+    for (int l = 0; l < L; ++l) {
+      if (l % 5 == 0) {
+        sincos_cw(v[c] * (float)(1 << l), s, co);
+      } else {
+        float s2 = 2.0f * s * co;
+        float c2 = (co - s) * (co + s);
+        s = s2;
+        co = c2;
+      }
+      e[3 + 6 * l + c] = s;
+      e[3 + 6 * l + 3 + c] = co;
+    }
+  }
+}
+
+template <int N>
+__device__ __forceinline__ void store_operand_row(uint32_t slab, int row, const float (&e)[N]) {
+#pragma unroll
+  for (int g = 0; g < N / 8; ++g) {
+    st_shared_v4(slab + sw128_chunk_off(row, g), pack_bf16x2(e[8 * g], e[8 * g + 1]),
+                 pack_bf16x2(e[8 * g + 2], e[8 * g + 3]), pack_bf16x2(e[8 * g + 4], e[8 * g + 5]),
+                 pack_bf16x2(e[8 * g + 6], e[8 * g + 7]));
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// epilogues: TMEM accumulator row -> bias (+relu) -> bf16 -> next layer's A operand in SMEM
+// ------------------------------------------------------------------------------------------
+// MODE 0: relu hidden layer; 1: relu hidden layer + fp32 sigma head; 2: linear (feature layer)
+template <int MODE>
+__device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __restrict__ bias,
+                                                const float* __restrict__ alpha_w, uint32_t act, int row,
+                                                float& sigma, __nv_bfloat16* __restrict__ save) {
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    uint32_t v[32];
+    tmem_ld32(taddr + c * 32, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 8; j += 4) {
+        float4 b = *reinterpret_cast<const float4*>(bias + c * 32 + g * 8 + j);
+        f[j] = __uint_as_float(v[g * 8 + j]) + b.x;
+        f[j + 1] = __uint_as_float(v[g * 8 + j + 1]) + b.y;
+        f[j + 2] = __uint_as_float(v[g * 8 + j + 2]) + b.z;
+        f[j + 3] = __uint_as_float(v[g * 8 + j + 3]) + b.w;
+      }
+      if (MODE == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; j += 4) {
+          float4 a = *reinterpret_cast<const float4*>(alpha_w + c * 32 + g * 8 + j);
+          sigma = fmaf(fmaxf(f[j], 0.f), a.x, sigma);
+          sigma = fmaf(fmaxf(f[j + 1], 0.f), a.y, sigma);
+          sigma = fmaf(fmaxf(f[j + 2], 0.f), a.z, sigma);
+          sigma = fmaf(fmaxf(f[j + 3], 0.f), a.w, sigma);
+        }
+      }
+      uint32_t p0, p1, p2, p3;
+      if (MODE == 2) {
+        p0 = pack_bf16x2(f[0], f[1]); p1 = pack_bf16x2(f[2], f[3]);
+        p2 = pack_bf16x2(f[4], f[5]); p3 = pack_bf16x2(f[6], f[7]);
+      } else {
+        p0 = pack_bf16x2_relu(f[0], f[1]); p1 = pack_bf16x2_relu(f[2], f[3]);
+        p2 = pack_bf16x2_relu(f[4], f[5]); p3 = pack_bf16x2_relu(f[6], f[7]);
+      }
+      st_shared_v4(act + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g), p0, p1, p2, p3);
+      if (save) *reinterpret_cast<uint4*>(save + c * 32 + g * 8) = make_uint4(p0, p1, p2, p3);
+    }
+  }
+}
+
+// view branch: hv = relu(acc + b) (128 wide), rgb = hv . Wrgb^T + b_rgb in fp32 (nerf.py:125-129)
+__device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __restrict__ cst, float& r, float& g_,
+                                               float& b_, __nv_bfloat16* __restrict__ save) {
+  const float* bias = cst + kOffViewB;
+  const float* wr = cst + kOffRgbW;
+  r = cst[kOffRgbB]; g_ = cst[kOffRgbB + 1]; b_ = cst[kOffRgbB + 2];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    uint32_t v[32];
+    tmem_ld32(taddr + c * 32, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 8; j += 4) {
+        int col = c * 32 + g * 8 + j;
+        float4 b = *reinterpret_cast<const float4*>(bias + col);
+        float4 w0 = *reinterpret_cast<const float4*>(wr + col);
+        float4 w1 = *reinterpret_cast<const float4*>(wr + 128 + col);
+        float4 w2 = *reinterpret_cast<const float4*>(wr + 256 + col);
+        f[j] = fmaxf(__uint_as_float(v[g * 8 + j]) + b.x, 0.f);
+        f[j + 1] = fmaxf(__uint_as_float(v[g * 8 + j + 1]) + b.y, 0.f);
+        f[j + 2] = fmaxf(__uint_as_float(v[g * 8 + j + 2]) + b.z, 0.f);
+        f[j + 3] = fmaxf(__uint_as_float(v[g * 8 + j + 3]) + b.w, 0.f);
+        r = fmaf(f[j], w0.x, r); r = fmaf(f[j + 1], w0.y, r); r = fmaf(f[j + 2], w0.z, r); r = fmaf(f[j + 3], w0.w, r);
+        g_ = fmaf(f[j], w1.x, g_); g_ = fmaf(f[j + 1], w1.y, g_); g_ = fmaf(f[j + 2], w1.z, g_); g_ = fmaf(f[j + 3], w1.w, g_);
+        b_ = fmaf(f[j], w2.x, b_); b_ = fmaf(f[j + 1], w2.y, b_); b_ = fmaf(f[j + 2], w2.z, b_); b_ = fmaf(f[j + 3], w2.w, b_);
+      }
+      if (save)
+        *reinterpret_cast<uint4*>(save + c * 32 + g * 8) = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]),
+                                                                      pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// the fused forward kernel
+// ------------------------------------------------------------------------------------------
+template <int L_PTS, int L_DIRS>
+__global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __restrict__ blob,
+                                                            const float* __restrict__ pts,
+                                                            const float* __restrict__ viewdirs, int64_t M, int S,
+                                                            float* __restrict__ raw, __nv_bfloat16* __restrict__ acts,
+                                                            int num_pairs) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+  const float* cst = reinterpret_cast<const float*>(gbase + kSmConst);
+  const uint32_t bar_full = base + kSmBar, bar_empty = bar_full + 8 * kStages, bar_act = bar_empty + 8 * kStages,
+                 bar_acc = bar_act + 16, bar_const = bar_acc + 16;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(bar_full + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 1);
+    }
+    for (int x = 0; x < 2; ++x) {
+      mbar_init(bar_act + 8 * x, kTileM);  // every epilogue thread of the tile arrives
+      mbar_init(bar_acc + 8 * x, 1);       // tcgen05.commit
+    }
+    mbar_init(bar_const, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(base + kSmTmemPtr, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kSmTmemPtr);
+
+  if (warp == 0) {
+    // ---------------- weight producer ----------------
+    if (lane == 0) {
+      mbar_expect_tx(bar_const, kConstFloats * 4);
+      bulk_g2s(base + kSmConst, blob + (size_t)kNumSlabs * kSlabBytes, kConstFloats * 4, bar_const);
+      uint32_t stage = 0, phase = 0;
+      for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+        for (int layer = 0; layer < 10; ++layer) {
+          const int n = ks_count(layer) * nh_count(layer), sb = slab_base(layer);
+          for (int x = 0; x < 2; ++x) {
+            for (int i = 0; i < n; ++i) {
+              mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+              mbar_expect_tx(bar_full + 8 * stage, kSlabBytes);
+              bulk_g2s(base + kSmRing + stage * kSlabBytes, blob + (size_t)(sb + i) * kSlabBytes, kSlabBytes,
+                       bar_full + 8 * stage);
+              if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------- MMA issuer ----------------
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, 128);
+      uint32_t stage = 0, phase = 0, par_act0 = 0, par_act1 = 0;
+      for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+        for (int layer = 0; layer < 10; ++layer) {
+          const int nks = ks_count(layer), nnh = nh_count(layer);
+          for (int x = 0; x < 2; ++x) {
+            const uint32_t sAct = base + (x ? kSmAct1 : kSmAct0), sEnc = base + (x ? kSmEnc1 : kSmEnc0);
+            if (x == 0) { mbar_wait(bar_act, par_act0); par_act0 ^= 1; }
+            else { mbar_wait(bar_act + 8, par_act1); par_act1 ^= 1; }
+            tc_fence_after();
+            const uint32_t d = tmem + x * 256;
+            for (int ks = 0; ks < nks; ++ks) {
+              uint32_t a_addr;
+              if (layer == 0) a_addr = sEnc;
+              else if (layer == 5) a_addr = ks == 0 ? sEnc : sAct + (ks - 1) * kSlabBytes;  // cat[input_pts, h]
+              else if (layer == 9 && ks == 4) a_addr = sEnc;                              // cat[feature, dirs]
+              else a_addr = sAct + ks * kSlabBytes;
+              const int nk16 = (layer == 9 && ks == 4) ? 2 : 4;
+              const uint64_t adesc = make_desc_kmajor_sw128(a_addr);
+              for (int nh = 0; nh < nnh; ++nh) {
+                mbar_wait(bar_full + 8 * stage, phase);
+                tc_fence_after();
+                const uint64_t bdesc = make_desc_kmajor_sw128(base + kSmRing + stage * kSlabBytes);
+                for (int k16 = 0; k16 < nk16; ++k16)
+                  umma_bf16(d + nh * 128, adesc + 2 * k16, bdesc + 2 * k16, idesc, (ks | k16) != 0);
+                umma_commit(bar_empty + 8 * stage);  // slab is free once these MMAs retire
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+              }
+            }
+            umma_commit(bar_acc + 8 * x);  // accumulator of (tile x, layer) complete
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ---------------- epilogue warps: tile x, row = TMEM lane ----------------
+    const int x = (warp - 4) >> 2;
+    const int row = ((warp & 3) << 5) | lane;
+    const uint32_t sAct = base + (x ? kSmAct1 : kSmAct0), sEnc = base + (x ? kSmEnc1 : kSmEnc0);
+    const uint32_t taddr = tmem + x * 256 + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t my_act = bar_act + 8 * x, my_acc = bar_acc + 8 * x;
+    uint32_t par_acc = 0;
+    mbar_wait(bar_const, 0);
+    for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+      const int64_t m = ((int64_t)pair * 2 + x) * kTileM + row;
+      const bool valid = m < M;
+      {
+        float p0 = 0.f, p1 = 0.f, p2 = 0.f;
+        if (valid) { p0 = pts[m * 3]; p1 = pts[m * 3 + 1]; p2 = pts[m * 3 + 2]; }
+        float e[64];
+        encode3<L_PTS>(p0, p1, p2, e);
+        store_operand_row(sEnc, row, e);
+      }
+      fence_proxy_async();
+      mbar_arrive(my_act);
+      float sigma = cst[kOffAlphaB];
+      __nv_bfloat16* save = (acts && valid) ? acts + m * kActStride : nullptr;
+#pragma unroll 1
+      for (int layer = 0; layer < 9; ++layer) {
+        mbar_wait(my_acc, par_acc);
+        par_acc ^= 1;
+        tc_fence_after();
+        __nv_bfloat16* sv = save ? save + layer * 256 : nullptr;
+        if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, sigma, sv);
+        else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, sigma, sv);
+        else {
+          epilogue_hidden<2>(taddr, cst + kOffFeatB, nullptr, sAct, row, sigma, sv);
+          // view-direction encoding replaces the position encoding in the auxiliary slab
+          // (its last reader, layer 5's MMA, retired before layer 5's accumulator was signalled)
+          float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+          if (valid) {
+            const int64_t ray = m / S;
+            v0 = viewdirs[ray * 3]; v1 = viewdirs[ray * 3 + 1]; v2 = viewdirs[ray * 3 + 2];
+          }
+          float e[32];
+          encode3<L_DIRS>(v0, v1, v2, e);
+          store_operand_row(sEnc, row, e);
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        mbar_arrive(my_act);
+      }
+      mbar_wait(my_acc, par_acc);
+      par_acc ^= 1;
+      tc_fence_after();
+      float r, g, b;
+      epilogue_views(taddr, cst, r, g, b, save ? save + 2304 : nullptr);
+      if (valid) *reinterpret_cast<float4*>(raw + m * 4) = make_float4(r, g, b, sigma);
+      tc_fence_before();
+    }
+  }
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
+static int build_pack_args(const NbMlpWeights* w, PackArgs& a) {
+  const int in_ch = 3 + 6 * w->L_pts, in_views = 3 + 6 * w->L_dirs;
+  if (in_ch > 64 || in_views > 32 || w->L_pts < 0 || w->L_dirs < 0) {
+    set_error("tensor-core MLP supports multires <= 10 and multires_views <= 4 (got %d, %d); use the fp32 path",
+              w->L_pts, w->L_dirs);
+    return NB_E_UNSUPPORTED;
+  }
+  int s = 0;
+  for (int layer = 0; layer < 10; ++layer) {
+    const float* mat;
+    int ld;
+    if (layer < 8) { mat = w->pts_w[layer]; ld = layer == 0 ? in_ch : (layer == 5 ? 256 + in_ch : 256); }
+    else if (layer == 8) { mat = w->feature_w; ld = 256; }
+    else { mat = w->views_w; ld = 256 + in_views; }
+    for (int ks = 0; ks < ks_count(layer); ++ks) {
+      int k0, kvalid;
+      if (layer == 0) { k0 = 0; kvalid = in_ch; }
+      else if (layer == 5) { k0 = ks == 0 ? 0 : in_ch + 64 * (ks - 1); kvalid = ks == 0 ? in_ch : 64; }
+      else if (layer == 9 && ks == 4) { k0 = 256; kvalid = in_views; }
+      else { k0 = 64 * ks; kvalid = 64; }
+      for (int nh = 0; nh < nh_count(layer); ++nh) a.slab[s++] = SlabSrc{mat, ld, nh * 128, k0, kvalid};
+    }
+  }
+  return s == kNumSlabs ? 0 : NB_E_ARG;
+}
+
+int init_mlp_tc(int) {
+  cudaError_t e = cudaFuncSetAttribute(mlp_fwd_tc_kernel<10, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)kSmemBytes);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * kSlabBytes + 2048);
+  if (e != cudaSuccess) {
+    set_error("init_mlp_tc: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" {
+
+int64_t nb_mlp_packed_bytes(int L_pts, int L_dirs) {
+  (void)L_pts; (void)L_dirs;
+  return (int64_t)kNumSlabs * kSlabBytes + kConstFloats * 4;
+}
+
+int nb_mlp_act_stride(void) { return kActStride; }
+
+int nb_mlp_pack(const NbMlpWeights* w, void* packed, void* stream) {
+  NB_REQUIRE(w && packed, "nb_mlp_pack: null pointer");
+  NB_REQUIRE(((uintptr_t)packed & 15) == 0, "nb_mlp_pack: packed buffer must be 16-byte aligned");
+  PackArgs a;
+  int rc = build_pack_args(w, a);
+  if (rc) return rc;
+  const int threads = kNumSlabs * 128 * 8;
+  pack_weights_kernel<<<(threads + 255) / 256, 256, 0, as_stream(stream)>>>(a, *w, (uint8_t*)packed);
+  return check_launch("nb_mlp_pack");
+}
+
+int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, const float* viewdirs, int64_t M,
+                  int S, float* raw, void* acts, void* stream) {
+  NB_REQUIRE(packed && pts && viewdirs && raw && S >= 1, "nb_mlp_fwd_tc: bad arguments");
+  NB_REQUIRE(M % S == 0, "nb_mlp_fwd_tc: M=%lld is not a multiple of S=%d", (long long)M, S);
+  if (L_pts != 10 || L_dirs != 4) {
+    set_error("nb_mlp_fwd_tc: only multires=10 / multires_views=4 is instantiated (got %d, %d)", L_pts, L_dirs);
+    return NB_E_UNSUPPORTED;
+  }
+  if (M == 0) return 0;
+  const int64_t tiles = (M + kTileM - 1) / kTileM;
+  const int64_t pairs = (tiles + 1) / 2;
+  NB_REQUIRE(pairs < (1ll << 30), "nb_mlp_fwd_tc: M too large for one launch");
+  const int grid = (int)(pairs < kNumSMs ? pairs : kNumSMs);
+  mlp_fwd_tc_kernel<10, 4><<<grid, 384, kSmemBytes, as_stream(stream)>>>(
+      (const uint8_t*)packed, pts, viewdirs, M, S, raw, (__nv_bfloat16*)acts, (int)pairs);
+  return check_launch("nb_mlp_fwd_tc");
+}
+
+// test hook: D[128,128] = A[128,K] B[128,K]^T with bf16-rounded operands (K in {64,128,192,256})
+int nb_debug_umma(const float* A, const float* B, int K, float* D, void* stream) {
+  NB_REQUIRE(A && B && D && K >= 64 && K <= 256 && K % 64 == 0, "nb_debug_umma: bad arguments");
+  umma_selftest_kernel<<<1, 128, 2 * (K / 64) * kSlabBytes + 2048, as_stream(stream)>>>(A, B, K, D);
+  return check_launch("nb_debug_umma");
+}
+
+}  // extern "C"

@@ -1,0 +1,341 @@
+// Ray generation, NDC warp, stratified sampling and sample positions.
+//
+// All of these are streaming (HBM-bound) kernels: one thread per output element group,
+// consecutive threads touch consecutive addresses.  Where BASELINE.json asks for bit-exact
+// results (get_rays, ndc_rays, z values) every fp32 op of the reference is issued as its own
+// IEEE round-to-nearest intrinsic (__fmul_rn / __fadd_rn / __fdiv_rn): the compiler must not
+// contract them into FMAs, because ATen rounds after every op.
+#include "common.cuh"
+
+namespace nb {
+
+// dirs of pixel (x, y): utils.py:37
+__device__ __forceinline__ void pixel_dir(int x, int y, float fx, float fy, float cx, float cy, float& d0,
+                                          float& d1, float& d2) {
+  d0 = __fdiv_rn(__fsub_rn((float)x, cx), fx);
+  d1 = -__fdiv_rn(__fsub_rn((float)y, cy), fy);
+  d2 = -1.0f;
+}
+
+// rays_d[k] = (d0*R[k][0] + d1*R[k][1]) + d2*R[k][2]: utils.py:39 (ATen sums 3 terms left to right)
+__device__ __forceinline__ float rot_row(float d0, float d1, float d2, float r0, float r1, float r2) {
+  return __fadd_rn(__fadd_rn(__fmul_rn(d0, r0), __fmul_rn(d1, r1)), __fmul_rn(d2, r2));
+}
+
+__global__ void __launch_bounds__(256) get_rays_kernel(int H, int W, float fx, float fy, float cx, float cy,
+                                                       const float* __restrict__ c2w, int ld,
+                                                       const int64_t* __restrict__ pix, int64_t n,
+                                                       float* __restrict__ rays_o, float* __restrict__ rays_d,
+                                                       float* __restrict__ viewdirs) {
+  __shared__ float R[12];
+  if (threadIdx.x < 12) R[threadIdx.x] = c2w[(threadIdx.x / 4) * ld + (threadIdx.x % 4)];
+  __syncthreads();
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t p = pix ? pix[i] : i;
+    int y = (int)(p / W), x = (int)(p - (int64_t)y * W);
+    float d0, d1, d2;
+    pixel_dir(x, y, fx, fy, cx, cy, d0, d1, d2);
+    float r0 = rot_row(d0, d1, d2, R[0], R[1], R[2]);
+    float r1 = rot_row(d0, d1, d2, R[4], R[5], R[6]);
+    float r2 = rot_row(d0, d1, d2, R[8], R[9], R[10]);
+    float* o = rays_o + i * 3;
+    float* d = rays_d + i * 3;
+    o[0] = R[3]; o[1] = R[7]; o[2] = R[11];
+    d[0] = r0; d[1] = r1; d[2] = r2;
+    if (viewdirs) {
+      float nrm = sqrtf(r0 * r0 + r1 * r1 + r2 * r2);
+      float* v = viewdirs + i * 3;
+      v[0] = __fdiv_rn(r0, nrm); v[1] = __fdiv_rn(r1, nrm); v[2] = __fdiv_rn(r2, nrm);
+    }
+  }
+}
+
+// d_c2w[k][m] += sum_pix dirs[m] * d_rays_d[pix][k] ; d_c2w[k][3] += sum_pix d_rays_o[pix][k]
+__global__ void __launch_bounds__(256) get_rays_bwd_kernel(int H, int W, float fx, float fy, float cx, float cy,
+                                                           const int64_t* __restrict__ pix, int64_t n,
+                                                           const float* __restrict__ g_o,
+                                                           const float* __restrict__ g_d, float* __restrict__ d_c2w) {
+  float acc[12];
+#pragma unroll
+  for (int k = 0; k < 12; ++k) acc[k] = 0.f;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t p = pix ? pix[i] : i;
+    int y = (int)(p / W), x = (int)(p - (int64_t)y * W);
+    float d0, d1, d2;
+    pixel_dir(x, y, fx, fy, cx, cy, d0, d1, d2);
+    if (g_d) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        float g = g_d[i * 3 + k];
+        acc[k * 4 + 0] += d0 * g;
+        acc[k * 4 + 1] += d1 * g;
+        acc[k * 4 + 2] += d2 * g;
+      }
+    }
+    if (g_o) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) acc[k * 4 + 3] += g_o[i * 3 + k];
+    }
+  }
+  __shared__ float red[8][12];
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 12; ++k) {
+    float v = warp_sum(acc[k]);
+    if (lane == 0) red[warp][k] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 12) {
+    float v = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) v += red[w][threadIdx.x];
+    atomicAdd(d_c2w + threadIdx.x, v);
+  }
+}
+
+__global__ void __launch_bounds__(256) normalize_fwd_kernel(const float* __restrict__ v, int64_t n,
+                                                            float* __restrict__ out) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float a = v[i * 3], b = v[i * 3 + 1], c = v[i * 3 + 2];
+    float nrm = sqrtf(a * a + b * b + c * c);
+    out[i * 3] = __fdiv_rn(a, nrm); out[i * 3 + 1] = __fdiv_rn(b, nrm); out[i * 3 + 2] = __fdiv_rn(c, nrm);
+  }
+}
+
+__global__ void __launch_bounds__(256) normalize_bwd_kernel(const float* __restrict__ v,
+                                                            const float* __restrict__ g, int64_t n,
+                                                            float* __restrict__ dv) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float a = v[i * 3], b = v[i * 3 + 1], c = v[i * 3 + 2];
+    float inv = 1.0f / sqrtf(a * a + b * b + c * c);
+    float ua = a * inv, ub = b * inv, uc = c * inv;
+    float ga = g[i * 3], gb = g[i * 3 + 1], gc = g[i * 3 + 2];
+    float dot = ua * ga + ub * gb + uc * gc;
+    dv[i * 3] = (ga - ua * dot) * inv; dv[i * 3 + 1] = (gb - ub * dot) * inv; dv[i * 3 + 2] = (gc - uc * dot) * inv;
+  }
+}
+
+// utils.py:54-71, op by op.
+__global__ void __launch_bounds__(256) ndc_fwd_kernel(float sx, float sy, float near_, float two_near,
+                                                      float neg_two_near, const float* __restrict__ ro,
+                                                      const float* __restrict__ rd, int64_t n,
+                                                      float* __restrict__ oo, float* __restrict__ od) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float ox = ro[i * 3], oy = ro[i * 3 + 1], oz = ro[i * 3 + 2];
+    float dx = rd[i * 3], dy = rd[i * 3 + 1], dz = rd[i * 3 + 2];
+    float t = __fdiv_rn(-__fadd_rn(near_, oz), dz);
+    float px = __fadd_rn(ox, __fmul_rn(t, dx));
+    float py = __fadd_rn(oy, __fmul_rn(t, dy));
+    float pz = __fadd_rn(oz, __fmul_rn(t, dz));
+    oo[i * 3 + 0] = __fdiv_rn(__fmul_rn(sx, px), pz);
+    oo[i * 3 + 1] = __fdiv_rn(__fmul_rn(sy, py), pz);
+    oo[i * 3 + 2] = __fadd_rn(1.0f, __fdiv_rn(two_near, pz));
+    od[i * 3 + 0] = __fmul_rn(sx, __fsub_rn(__fdiv_rn(dx, dz), __fdiv_rn(px, pz)));
+    od[i * 3 + 1] = __fmul_rn(sy, __fsub_rn(__fdiv_rn(dy, dz), __fdiv_rn(py, pz)));
+    od[i * 3 + 2] = __fdiv_rn(neg_two_near, pz);
+  }
+}
+
+__global__ void __launch_bounds__(256) ndc_bwd_kernel(float sx, float sy, float near_, const float* __restrict__ ro,
+                                                      const float* __restrict__ rd, const float* __restrict__ gO,
+                                                      const float* __restrict__ gD, int64_t n,
+                                                      float* __restrict__ g_ro, float* __restrict__ g_rd) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float ox = ro[i * 3], oy = ro[i * 3 + 1], oz = ro[i * 3 + 2];
+    float dx = rd[i * 3], dy = rd[i * 3 + 1], dz = rd[i * 3 + 2];
+    float t = -(near_ + oz) / dz;
+    float px = ox + t * dx, py = oy + t * dy, pz = oz + t * dz;
+    float gO0 = gO ? gO[i * 3] : 0.f, gO1 = gO ? gO[i * 3 + 1] : 0.f, gO2 = gO ? gO[i * 3 + 2] : 0.f;
+    float gD0 = gD ? gD[i * 3] : 0.f, gD1 = gD ? gD[i * 3 + 1] : 0.f, gD2 = gD ? gD[i * 3 + 2] : 0.f;
+    float ipz = 1.0f / pz, idz = 1.0f / dz;
+    float a0 = (gO0 - gD0) * sx, a1 = (gO1 - gD1) * sy;  // d/d(px/pz), d/d(py/pz)
+    float gpx = a0 * ipz, gpy = a1 * ipz;
+    float gpz = -(a0 * px + a1 * py) * ipz * ipz + (gD2 - gO2) * 2.0f * near_ * ipz * ipz;
+    float gdx = gD0 * sx * idz, gdy = gD1 * sy * idz;
+    float gdz = -(gD0 * sx * dx + gD1 * sy * dy) * idz * idz;
+    float gt = gpx * dx + gpy * dy + gpz * dz;
+    gdx += t * gpx; gdy += t * gpy; gdz += t * gpz;
+    float gox = gpx, goy = gpy, goz = gpz - gt * idz;
+    gdz += gt * (near_ + oz) * idz * idz;
+    g_ro[i * 3] = gox; g_ro[i * 3 + 1] = goy; g_ro[i * 3 + 2] = goz;
+    g_rd[i * 3] = gdx; g_rd[i * 3 + 1] = gdy; g_rd[i * 3 + 2] = gdz;
+  }
+}
+
+// ---- stratified sampling: render_utils.py:105-131 ------------------------------------------
+__device__ __forceinline__ float z_at(float near_, float far_, float t, int lindisp) {
+  float omt = __fsub_rn(1.0f, t);
+  if (!lindisp) return __fadd_rn(__fmul_rn(near_, omt), __fmul_rn(far_, t));
+  float a = __fmul_rn(__fdiv_rn(1.0f, near_), omt);
+  float b = __fmul_rn(__fdiv_rn(1.0f, far_), t);
+  return __fdiv_rn(1.0f, __fadd_rn(a, b));
+}
+
+__global__ void __launch_bounds__(256) sample_coarse_kernel(const float* __restrict__ rays, int64_t n, int ld,
+                                                            const float* __restrict__ t_vals,
+                                                            const float* __restrict__ t_rand, int S, int lindisp,
+                                                            float* __restrict__ z_out, float* __restrict__ pts) {
+  int64_t total = n * S;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / S;
+    int s = (int)(i - r * S);
+    const float* ray = rays + r * ld;
+    float near_ = ray[6], far_ = ray[7];
+    float z = z_at(near_, far_, t_vals[s], lindisp);
+    if (t_rand) {
+      float lower = z, upper = z;
+      if (s > 0) lower = __fmul_rn(0.5f, __fadd_rn(z, z_at(near_, far_, t_vals[s - 1], lindisp)));
+      if (s < S - 1) upper = __fmul_rn(0.5f, __fadd_rn(z_at(near_, far_, t_vals[s + 1], lindisp), z));
+      z = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), t_rand[i]));
+    }
+    z_out[i] = z;
+    if (pts) {
+      pts[i * 3 + 0] = __fadd_rn(ray[0], __fmul_rn(ray[3], z));
+      pts[i * 3 + 1] = __fadd_rn(ray[1], __fmul_rn(ray[4], z));
+      pts[i * 3 + 2] = __fadd_rn(ray[2], __fmul_rn(ray[5], z));
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) ray_points_fwd_kernel(const float* __restrict__ ro,
+                                                             const float* __restrict__ rd,
+                                                             const float* __restrict__ z, int64_t n, int S,
+                                                             float* __restrict__ pts) {
+  int64_t total = n * S;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / S;
+    float zz = z[i];
+    pts[i * 3 + 0] = __fadd_rn(ro[r * 3 + 0], __fmul_rn(rd[r * 3 + 0], zz));
+    pts[i * 3 + 1] = __fadd_rn(ro[r * 3 + 1], __fmul_rn(rd[r * 3 + 1], zz));
+    pts[i * 3 + 2] = __fadd_rn(ro[r * 3 + 2], __fmul_rn(rd[r * 3 + 2], zz));
+  }
+}
+
+// one warp per ray: d_o = sum_s g, d_d = sum_s z*g
+__global__ void __launch_bounds__(256) ray_points_bwd_kernel(const float* __restrict__ z,
+                                                             const float* __restrict__ g, int64_t n, int S,
+                                                             float* __restrict__ d_o, float* __restrict__ d_d) {
+  int lane = threadIdx.x & 31;
+  int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < n; r += nwarps) {
+    float so[3] = {0.f, 0.f, 0.f}, sd[3] = {0.f, 0.f, 0.f};
+    for (int s = lane; s < S; s += 32) {
+      int64_t i = r * S + s;
+      float zz = z[i];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        float gv = g[i * 3 + k];
+        so[k] += gv;
+        sd[k] += zz * gv;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      so[k] = warp_sum(so[k]);
+      sd[k] = warp_sum(sd[k]);
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (d_o) d_o[r * 3 + k] = so[k];
+        if (d_d) d_d[r * 3 + k] = sd[k];
+      }
+    }
+  }
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" {
+
+int nb_get_rays_fwd(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, int c2w_ld,
+                    float* rays_o, float* rays_d, float* viewdirs, void* stream) {
+  return nb_get_rays_sel_fwd(H, W, fx, fy, cx, cy, c2w, c2w_ld, nullptr, (int64_t)H * W, rays_o, rays_d, viewdirs,
+                             stream);
+}
+
+int nb_get_rays_sel_fwd(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, int c2w_ld,
+                        const int64_t* pix, int64_t n, float* rays_o, float* rays_d, float* viewdirs, void* stream) {
+  NB_REQUIRE(H > 0 && W > 0 && c2w && rays_o && rays_d && c2w_ld >= 4, "nb_get_rays: bad arguments");
+  if (n == 0) return 0;
+  get_rays_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(H, W, fx, fy, cx, cy, c2w, c2w_ld, pix, n, rays_o,
+                                                                    rays_d, viewdirs);
+  return check_launch("nb_get_rays");
+}
+
+int nb_get_rays_bwd(int H, int W, float fx, float fy, float cx, float cy, const int64_t* pix, int64_t n,
+                    const float* d_rays_o, const float* d_rays_d, float* d_c2w, void* stream) {
+  NB_REQUIRE(H > 0 && W > 0 && d_c2w, "nb_get_rays_bwd: bad arguments");
+  if (n == 0 || (!d_rays_o && !d_rays_d)) return 0;
+  get_rays_bwd_kernel<<<grid_for(n, 256 * 8, 4), 256, 0, as_stream(stream)>>>(H, W, fx, fy, cx, cy, pix, n, d_rays_o,
+                                                                               d_rays_d, d_c2w);
+  return check_launch("nb_get_rays_bwd");
+}
+
+int nb_normalize_fwd(const float* v, int64_t n, float* out, void* stream) {
+  NB_REQUIRE(v && out, "nb_normalize_fwd: null pointer");
+  if (n == 0) return 0;
+  normalize_fwd_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(v, n, out);
+  return check_launch("nb_normalize_fwd");
+}
+
+int nb_normalize_bwd(const float* v, const float* d_out, int64_t n, float* d_v, void* stream) {
+  NB_REQUIRE(v && d_out && d_v, "nb_normalize_bwd: null pointer");
+  if (n == 0) return 0;
+  normalize_bwd_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(v, d_out, n, d_v);
+  return check_launch("nb_normalize_bwd");
+}
+
+int nb_ndc_rays_fwd(int H, int W, double focal, double near_, const float* rays_o, const float* rays_d, int64_t n,
+                    float* out_o, float* out_d, void* stream) {
+  NB_REQUIRE(rays_o && rays_d && out_o && out_d, "nb_ndc_rays_fwd: null pointer");
+  if (n == 0) return 0;
+  // the Python-scalar sub-expressions of utils.py:60-66 are evaluated in double, then enter fp32
+  float sx = (float)(-1.0 / (W / (2.0 * focal)));
+  float sy = (float)(-1.0 / (H / (2.0 * focal)));
+  ndc_fwd_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(sx, sy, (float)near_, (float)(2.0 * near_),
+                                                                   (float)(-2.0 * near_), rays_o, rays_d, n, out_o,
+                                                                   out_d);
+  return check_launch("nb_ndc_rays_fwd");
+}
+
+int nb_ndc_rays_bwd(int H, int W, double focal, double near_, const float* rays_o, const float* rays_d,
+                    const float* d_out_o, const float* d_out_d, int64_t n, float* d_rays_o, float* d_rays_d,
+                    void* stream) {
+  NB_REQUIRE(rays_o && rays_d && d_rays_o && d_rays_d, "nb_ndc_rays_bwd: null pointer");
+  if (n == 0) return 0;
+  float sx = (float)(-1.0 / (W / (2.0 * focal)));
+  float sy = (float)(-1.0 / (H / (2.0 * focal)));
+  ndc_bwd_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(sx, sy, (float)near_, rays_o, rays_d, d_out_o,
+                                                                   d_out_d, n, d_rays_o, d_rays_d);
+  return check_launch("nb_ndc_rays_bwd");
+}
+
+int nb_sample_coarse(const float* rays, int64_t n, int ld, const float* t_vals, const float* t_rand, int S,
+                     int lindisp, float* z, float* pts, void* stream) {
+  NB_REQUIRE(rays && t_vals && z && ld >= 8 && S >= 1, "nb_sample_coarse: bad arguments");
+  if (n == 0) return 0;
+  sample_coarse_kernel<<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays, n, ld, t_vals, t_rand, S, lindisp,
+                                                                             z, pts);
+  return check_launch("nb_sample_coarse");
+}
+
+int nb_ray_points_fwd(const float* rays_o, const float* rays_d, const float* z, int64_t n, int S, float* pts,
+                      void* stream) {
+  NB_REQUIRE(rays_o && rays_d && z && pts && S >= 1, "nb_ray_points_fwd: bad arguments");
+  if (n == 0) return 0;
+  ray_points_fwd_kernel<<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, z, n, S, pts);
+  return check_launch("nb_ray_points_fwd");
+}
+
+int nb_ray_points_bwd(const float* z, const float* d_pts, int64_t n, int S, float* d_rays_o, float* d_rays_d,
+                      void* stream) {
+  NB_REQUIRE(z && d_pts && S >= 1, "nb_ray_points_bwd: bad arguments");
+  if (n == 0) return 0;
+  ray_points_bwd_kernel<<<grid_for(n, 8), 256, 0, as_stream(stream)>>>(z, d_pts, n, S, d_rays_o, d_rays_d);
+  return check_launch("nb_ray_points_bwd");
+}
+
+}  // extern "C"

@@ -1,0 +1,204 @@
+// Hierarchical resampling: per-ray CDF, searchsorted and merge in shared memory.
+// replaces utils.sample_pdf (utils.py:74-117) plus sort/cat/std (render_utils.py:141-147,168).
+//
+// One warp per ray.  The ray's bins, cdf and the (S+I)-entry merge buffer live in shared
+// memory; nothing of the reference's [n,I,63] gather expansion is materialised.  Algorithmic
+// HBM traffic: read z + weights (2*S*4 B) [+ u: I*4 B], write z_out ((S+I)*4 B) + z_std.
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace nb {
+
+// searchsorted(cdf, u, right=True): number of entries <= u  (utils.py:101)
+__device__ __forceinline__ int upper_bound(const float* cdf, int B, float u) {
+  int lo = 0, hi = B;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (cdf[mid] <= u) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// utils.py:102-115 with the reference's rounding order
+__device__ __forceinline__ float invert_one(const float* bins, const float* cdf, int B, float u, int& inds) {
+  inds = upper_bound(cdf, B, u);
+  int below = max(inds - 1, 0);
+  int above = min(B - 1, inds);
+  float cb = cdf[below], ca = cdf[above];
+  float bb = bins[below], ba = bins[above];
+  float denom = __fsub_rn(ca, cb);
+  if (denom < 1e-5f) denom = 1.0f;
+  float t = __fdiv_rn(__fsub_rn(u, cb), denom);
+  return __fadd_rn(bb, __fmul_rn(t, __fsub_rn(ba, bb)));
+}
+
+__global__ void __launch_bounds__(256) invert_cdf_kernel(const float* __restrict__ bins, const float* __restrict__ cdf,
+                                                         const float* __restrict__ u, int64_t n, int B, int I,
+                                                         float* __restrict__ samples, int64_t* __restrict__ inds) {
+  int64_t total = n * I;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / I;
+    int k;
+    float s = invert_one(bins + r * B, cdf + r * B, B, u[i], k);
+    if (samples) samples[i] = s;
+    if (inds) inds[i] = k;
+  }
+}
+
+// cdf[0] = 0, cdf[m] = sum_{j<m} (w[j]+1e-5)/sum(w+1e-5), m < B  (utils.py:76-79); w has B-1 entries
+__device__ __forceinline__ void build_cdf(const float* __restrict__ w, int B, float* cdf, int lane) {
+  float part = 0.f;
+  for (int m = lane; m < B - 1; m += 32) {
+    float v = __fadd_rn(w[m], 1e-5f);
+    cdf[m + 1] = v;  // staged, normalised below
+    part += v;
+  }
+  float wsum = warp_sum(part);
+  __syncwarp();
+  if (lane == 0) {
+    float c = 0.f;
+    cdf[0] = 0.f;
+    for (int m = 1; m < B; ++m) {  // torch.cumsum is a sequential fp32 sum
+      c = __fadd_rn(c, __fdiv_rn(cdf[m], wsum));
+      cdf[m] = c;
+    }
+  }
+  __syncwarp();
+}
+
+// utils.sample_pdf on explicit bins: one warp per row, cdf in shared memory
+__global__ void __launch_bounds__(256) sample_pdf_kernel(const float* __restrict__ bins_g,
+                                                         const float* __restrict__ weights,
+                                                         const float* __restrict__ u,
+                                                         const float* __restrict__ u_det, int64_t n, int B, int I,
+                                                         int Bp, float* __restrict__ samples) {
+  extern __shared__ float smem[];
+  int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float* bins = smem + (size_t)wib * 2 * Bp;
+  float* cdf = bins + Bp;
+  int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < n; r += nwarps) {
+    for (int m = lane; m < B; m += 32) bins[m] = bins_g[r * B + m];
+    build_cdf(weights + r * (B - 1), B, cdf, lane);
+    for (int i = lane; i < I; i += 32) {
+      int k;
+      samples[r * I + i] = invert_one(bins, cdf, B, u ? u[r * I + i] : u_det[i], k);
+    }
+    __syncwarp();
+  }
+}
+
+// smem per warp: bins[Bp] cdf[Bp] buf[P]   (Bp = S rounded up to 32, P = pow2 >= S+I)
+__global__ void __launch_bounds__(256) sample_pdf_merge_kernel(const float* __restrict__ z,
+                                                               const float* __restrict__ weights,
+                                                               const float* __restrict__ u,
+                                                               const float* __restrict__ u_det, int64_t n, int S, int I,
+                                                               int Bp, int P, float* __restrict__ z_out,
+                                                               float* __restrict__ z_std, float* __restrict__ z_samples) {
+  extern __shared__ float smem[];
+  int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float* bins = smem + (size_t)wib * (2 * Bp + P);
+  float* cdf = bins + Bp;
+  float* buf = cdf + Bp;
+  const int B = S - 1;  // number of bins / cdf entries (63)
+  int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < n; r += nwarps) {
+    const float* zr = z + r * S;
+    const float* wr = weights + r * S;
+    // coarse depths go straight into the merge buffer; mid-points into bins
+    for (int s = lane; s < S; s += 32) buf[s] = zr[s];
+    __syncwarp();
+    for (int m = lane; m < B; m += 32) bins[m] = __fmul_rn(0.5f, __fadd_rn(buf[m + 1], buf[m]));
+    build_cdf(wr + 1, B, cdf, lane);
+    float sum = 0.f;
+    for (int i = lane; i < I; i += 32) {
+      float uu = u ? u[r * I + i] : u_det[i];
+      int k;
+      float smp = invert_one(bins, cdf, B, uu, k);
+      buf[S + i] = smp;
+      sum += smp;
+      if (z_samples) z_samples[r * I + i] = smp;
+    }
+    for (int i = S + I + lane; i < P; i += 32) buf[i] = CUDART_INF_F;
+    __syncwarp();
+    if (z_std) {
+      float mean = warp_sum(sum) / (float)I;
+      float var = 0.f;
+      for (int i = lane; i < I; i += 32) {
+        float d = buf[S + i] - mean;
+        var += d * d;
+      }
+      var = warp_sum(var) / (float)I;
+      if (lane == 0) z_std[r] = sqrtf(var);
+    }
+    // bitonic sort of the P-entry buffer (ascending); value-deterministic like torch.sort
+    for (int k = 2; k <= P; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = lane; t < (P >> 1); t += 32) {
+          int i = ((t / j) * (j << 1)) + (t % j);
+          int l = i + j;
+          float a = buf[i], b = buf[l];
+          bool up = ((i & k) == 0);
+          if ((a > b) == up) { buf[i] = b; buf[l] = a; }
+        }
+        __syncwarp();
+      }
+    }
+    for (int i = lane; i < S + I; i += 32) z_out[r * (int64_t)(S + I) + i] = buf[i];
+    __syncwarp();
+  }
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" {
+
+int nb_invert_cdf(const float* bins, const float* cdf, const float* u, int64_t n, int B, int I, float* samples,
+                  int64_t* inds, void* stream) {
+  NB_REQUIRE(bins && cdf && u && B >= 1 && I >= 1, "nb_invert_cdf: bad arguments");
+  if (n == 0) return 0;
+  invert_cdf_kernel<<<grid_for(n * I, 256), 256, 0, as_stream(stream)>>>(bins, cdf, u, n, B, I, samples, inds);
+  return check_launch("nb_invert_cdf");
+}
+
+int nb_sample_pdf(const float* bins, const float* weights, const float* u, const float* u_det, int64_t n, int B, int I,
+                  float* samples, void* stream) {
+  NB_REQUIRE(bins && weights && samples && B >= 2 && I >= 1 && (u || u_det), "nb_sample_pdf: bad arguments");
+  if (n == 0) return 0;
+  int Bp = (B + 31) / 32 * 32;
+  if (Bp > 1024) {
+    set_error("nb_sample_pdf: %d bins > 1024 is not implemented", B);
+    return NB_E_UNSUPPORTED;
+  }
+  sample_pdf_kernel<<<grid_for(n, 4), 128, 4 * 2 * Bp * sizeof(float), as_stream(stream)>>>(bins, weights, u, u_det, n,
+                                                                                         B, I, Bp, samples);
+  return check_launch("nb_sample_pdf");
+}
+
+int nb_sample_pdf_merge(const float* z, const float* weights, const float* u, const float* u_det, int64_t n, int S,
+                        int I, float* z_out, float* z_std, float* z_samples, void* stream) {
+  NB_REQUIRE(z && weights && z_out && S >= 3 && I >= 1, "nb_sample_pdf_merge: bad arguments");
+  NB_REQUIRE(u || u_det, "nb_sample_pdf_merge: need u or u_det");
+  if (n == 0) return 0;
+  int P = 2;
+  while (P < S + I) P <<= 1;
+  int Bp = (S + 31) / 32 * 32;
+  if (P > 4096) {
+    set_error("nb_sample_pdf_merge: S+I=%d > 4096 is not implemented", S + I);
+    return NB_E_UNSUPPORTED;
+  }
+  // warps per block chosen so that the merge buffers fit the default 48 KB dynamic smem
+  int per_warp = (2 * Bp + P) * (int)sizeof(float);
+  int wpb = 8;
+  while (wpb > 1 && wpb * per_warp > 48 * 1024) wpb >>= 1;
+  sample_pdf_merge_kernel<<<grid_for(n, wpb), wpb * 32, wpb * per_warp, as_stream(stream)>>>(
+      z, weights, u, u_det, n, S, I, Bp, P, z_out, z_std, z_samples);
+  return check_launch("nb_sample_pdf_merge");
+}
+
+}  // extern "C"

@@ -1,0 +1,161 @@
+"""Volume renderer behind the reference's API (nerf_shared/render_utils.py:13-319).
+
+`Renderer` keeps the reference's constructor, method names, argument orders, defaults and return
+structures; every stage runs in libnerf_b200 (sm_100a CUDA) through the autograd wrappers in
+_ops.py:  rays -> stratified z -> fused encoding+MLP -> compositing -> inverse-CDF resampling ->
+fine MLP -> compositing.
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+import torch
+
+from . import _ops
+from . import nerf   # noqa: F401  (the reference module exposes it; demos star-import this file)
+from . import utils
+
+DEBUG = False
+
+try:  # only used to write PNG/MP4 files (render_from_batch_poses); not on the compute path
+    import imageio
+except Exception:  # pragma: no cover
+    imageio = None
+
+# rays per internal launch: `chunk` of the reference API is an upper bound on memory, results
+# do not depend on it (render_utils.py:184-185); the fused kernels need far less scratch per
+# ray, so small chunks are coalesced up to this many rays.
+MIN_CHUNK = 1 << 18
+
+
+def _write_image(path, rgb8):
+    if imageio is not None and hasattr(imageio, "imwrite"):
+        imageio.imwrite(path, rgb8)
+    else:
+        import cv2
+        cv2.imwrite(path, rgb8[..., ::-1])
+
+
+class Renderer(torch.nn.Module):
+    def __init__(self, perturb=True, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                 raw_noise_std=0.0, ndc=False, lindisp=False, near=0.0, far=1.0):
+        super().__init__()
+        self.perturb, self.N_importance, self.N_samples = perturb, N_importance, N_samples
+        self.use_viewdirs, self.white_bkgd, self.raw_noise_std = use_viewdirs, white_bkgd, raw_noise_std
+        self.ndc, self.lindisp, self.near, self.far = ndc, lindisp, near, far
+        print({k: v for k, v in self.__dict__.items() if not k.startswith("_") and k != "training"})
+
+    # ------------------------------------------------------------------ random draws
+    # The reference draws from the global torch RNG in this order: t_rand (render_utils.py:121),
+    # coarse noise (:264), u (utils.py:86), fine noise (:264).  Tests override these hooks to
+    # feed the oracle's draws.
+    def _uniform(self, shape, device, what):
+        return torch.rand(shape, device=device, dtype=torch.float32)
+
+    def _normal(self, shape, device, what):
+        return torch.randn(shape, device=device, dtype=torch.float32)
+
+    # ------------------------------------------------------------------ entry points
+    def render_from_pose(self, H, W, K, chunk, c2w, coarse_model, fine_model, retraw=True):
+        return tuple(self.render(H, W, K, coarse_model, fine_model, chunk=chunk, c2w=c2w, retraw=retraw))
+
+    def render_from_rays(self, H, W, K, chunk, rays, coarse_model, fine_model, retraw=True):
+        return tuple(self.render(H, W, K, coarse_model, fine_model, chunk=chunk, rays=rays, retraw=retraw))
+
+    def render_path(self):
+        pass
+
+    def render_batch(self, coarse_model, fine_model, rays_flat, chunk=1024 * 32, retraw=False):
+        step = max(int(chunk), MIN_CHUNK)
+        parts = [self.render_rays(rays_flat[i:i + step], coarse_model, fine_model, retraw)
+                 for i in range(0, rays_flat.shape[0], step)]
+        if len(parts) == 1:
+            return parts[0]
+        return {k: torch.cat([p[k] for p in parts], 0) for k in parts[0]}
+
+    def render_rays(self, ray_batch, coarse_model, fine_model, retraw=False, retweights=False, verbose=False,
+                    pytest=False):
+        """ray_batch rows: o(3) d(3) near far [viewdirs(3)] -> dict as the reference (render_utils.py:67-174)."""
+        if ray_batch.shape[-1] <= 8:
+            raise NotImplementedError("rays without view directions (use_viewdirs=False) are not implemented")
+        n = ray_batch.shape[0]
+        dev = ray_batch.device
+        rays_o, rays_d, viewdirs = ray_batch[:, 0:3], ray_batch[:, 3:6], ray_batch[:, 8:11]
+        S, I = int(self.N_samples), int(self.N_importance)
+
+        t_rand = self._uniform((n, S), dev, "t_rand") if self.perturb > 0.0 else None
+        z_vals = _ops.sample_coarse(ray_batch, S, t_rand, self.lindisp)
+        pts = _ops.RayPoints.apply(rays_o, rays_d, z_vals)
+        raw = coarse_model(pts, viewdirs)
+        rgb_map, disp_map, acc_map, weights, depth_map = self.raw2outputs(raw, z_vals, rays_d, _what="noise_c")
+
+        ret = {}
+        if I > 0:
+            ret["rgb0"], ret["disp0"], ret["acc0"] = rgb_map, disp_map, acc_map
+            u = self._uniform((n, I), dev, "u") if self.perturb != 0.0 else None   # det = (perturb == 0)
+            z_vals, z_std = _ops.sample_pdf_merge(z_vals, weights, I, u)
+            pts = _ops.RayPoints.apply(rays_o, rays_d, z_vals)
+            raw = (coarse_model if fine_model is None else fine_model)(pts, viewdirs)
+            rgb_map, disp_map, acc_map, weights, depth_map = self.raw2outputs(raw, z_vals, rays_d, _what="noise_f")
+            ret["z_std"] = z_std
+        ret["rgb_map"], ret["disp_map"], ret["acc_map"] = rgb_map, disp_map, acc_map
+        if retraw:
+            ret["raw"] = raw
+        if retweights:
+            ret["weights"], ret["z_vals"] = weights, z_vals
+        # (the reference's per-key isnan/isinf host syncs, render_utils.py:170-172, only feed a
+        #  DEBUG print and are dropped)
+        return ret
+
+    def render(self, H, W, K, coarse_model, fine_model, chunk=1024 * 32, rays=None, retraw=True, c2w=None,
+               c2w_staticcam=None):
+        """-> [rgb_map, disp_map, acc_map, extras] shaped like the rays (render_utils.py:176-238)."""
+        if c2w is not None:
+            rays_o, rays_d = utils.get_rays(H, W, K, c2w)
+        else:
+            rays_o, rays_d = rays
+        if not self.use_viewdirs:
+            raise NotImplementedError("use_viewdirs=False is not implemented by libnerf_b200")
+        viewdirs = rays_d
+        if c2w_staticcam is not None:
+            rays_o, rays_d = utils.get_rays(H, W, K, c2w_staticcam)
+        viewdirs = _ops.Normalize.apply(viewdirs).reshape(-1, 3)
+        out_shape = list(rays_d.shape[:-1])
+        if self.ndc:
+            rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
+        rays_o = rays_o.reshape(-1, 3).float()
+        rays_d = rays_d.reshape(-1, 3).float()
+        bounds = rays_d.new_empty((rays_d.shape[0], 2))
+        bounds[:, 0] = float(self.near)
+        bounds[:, 1] = float(self.far)
+        ray_rows = torch.cat([rays_o, rays_d, bounds, viewdirs], -1)
+
+        res = self.render_batch(coarse_model, fine_model, ray_rows, chunk, retraw)
+        res = {k: v.reshape(out_shape + list(v.shape[1:])) for k, v in res.items()}
+        head = ("rgb_map", "disp_map", "acc_map")
+        return [res[k] for k in head] + [{k: v for k, v in res.items() if k not in head}]
+
+    def raw2outputs(self, raw, z_vals, rays_d, pytest=False, _what="noise"):
+        """-> rgb_map, disp_map, acc_map, weights, depth_map (render_utils.py:241-290)."""
+        noise = None
+        if self.raw_noise_std > 0.0:
+            noise = self._normal(tuple(raw.shape[:-1]), raw.device, _what) * self.raw_noise_std
+        return _ops.Composite.apply(raw, z_vals, rays_d, noise, bool(self.white_bkgd))
+
+    def render_from_batch_poses(self, H, W, K, chunk, batch_c2w, coarse_model, fine_model, retraw, save_directory,
+                                b_combine_as_video=False, tb_writer=None):
+        """Render a list of poses to PNG files / a video / TensorBoard (render_utils.py:293-319)."""
+        os.makedirs(save_directory, exist_ok=True)
+        frames = []
+        with torch.no_grad():
+            for i, c2w in enumerate(batch_c2w):
+                c2w = torch.as_tensor(c2w, dtype=torch.float32)
+                rgb, _, _, _ = self.render_from_pose(H, W, K, chunk=chunk, c2w=c2w, coarse_model=coarse_model,
+                                                     fine_model=fine_model, retraw=False)
+                frames.append(utils.to8b(rgb.cpu().numpy()))
+                _write_image(os.path.join(save_directory, "{:03d}.png".format(i)), frames[-1])
+        if b_combine_as_video and imageio is not None and hasattr(imageio, "mimwrite"):
+            imageio.mimwrite(os.path.join(save_directory, "video.mp4"), frames, fps=30, quality=8)
+        if tb_writer is not None:
+            tb_writer.add_images("Test/Images", torch.from_numpy(np.stack(frames, 0)), dataformats="NHWC")

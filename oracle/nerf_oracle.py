@@ -204,7 +204,7 @@ def _bf16(x: Tensor) -> Tensor:
 
 
 def mlp(params: Dict[str, Tensor], enc_pts: Tensor, enc_dirs: Tensor, D: int = 8,
-        skips: Sequence[int] = (4,), bf16: bool = False) -> Tensor:
+        skips: Sequence[int] = (4,), bf16: bool = False, acts: Optional[list] = None) -> Tensor:
     """nerf.py:110-134 (use_viewdirs=True branch) -> [M,4] = (r,g,b,sigma) pre-activation.
 
     bf16=True emulates the CUDA kernel's numerics: every GEMM operand (weights and the
@@ -223,6 +223,8 @@ def mlp(params: Dict[str, Tensor], enc_pts: Tensor, enc_dirs: Tensor, D: int = 8
         h = F.relu(lin("pts_linears.%d" % i, h))
         h_full = h
         h = q(h)
+        if acts is not None:
+            acts.append(h)
         if i in skips:
             h = torch.cat([x_in, h], -1)
             h_full = torch.cat([x_in, h_full], -1)
@@ -232,6 +234,8 @@ def mlp(params: Dict[str, Tensor], enc_pts: Tensor, enc_dirs: Tensor, D: int = 8
         alpha = lin("alpha_linear", h)
     feat = q(lin("feature_linear", h))
     hv = F.relu(lin("views_linears.0", torch.cat([feat, q(enc_dirs)], -1)))
+    if acts is not None:
+        acts.extend([feat, q(hv)])
     if bf16:
         rgb = F.linear(hv, params["rgb_linear.weight"], params["rgb_linear.bias"])
     else:
