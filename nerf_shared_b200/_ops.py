@@ -319,9 +319,10 @@ class NerfMLP(torch.autograd.Function):
     def forward(ctx, pts, viewdirs, S, model, *params):
         need_grad = any(ctx.needs_input_grad)
         if model.precision == "fp32":
-            if need_grad:
-                raise _lib.NerfB200Error("precision='fp32' is an inference/parity path; training uses the bf16 kernels")
-            return mlp_forward_f32(model, pts, viewdirs, S)
+            # inference / parity path: exact fp32 operands, no backward kernels
+            raw = mlp_forward_f32(model, pts, viewdirs, S)
+            ctx.mark_non_differentiable(raw)
+            return raw
         raw, acts = mlp_forward_tc(model, pts, viewdirs, S, save_acts=need_grad)
         if need_grad:
             ctx.model, ctx.S = model, S

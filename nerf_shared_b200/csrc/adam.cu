@@ -25,8 +25,8 @@ using namespace nb;
 
 extern "C" int nb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                             float eps, int step, float grad_scale, void* stream) {
-  NB_REQUIRE(p && g && m && v && step >= 1, "nb_adam_step: bad arguments");
   if (n == 0) return 0;
+  NB_REQUIRE(p && g && m && v && step >= 1, "nb_adam_step: bad arguments");
   double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
   adam_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(p, g, m, v, n, (float)(lr / bc1), beta1, beta2, eps,
                                                               (float)(1.0 / sqrt(bc2)), grad_scale);

@@ -204,8 +204,8 @@ extern "C" {
 int nb_composite_fwd(const float* raw, const float* z, const float* rays_d, const float* noise, int64_t n, int S,
                      int white_bkgd, float* rgb_map, float* disp, float* acc, float* weights, float* depth,
                      void* stream) {
-  NB_REQUIRE(raw && z && rays_d && S >= 1, "nb_composite_fwd: bad arguments");
   if (n == 0) return 0;
+  NB_REQUIRE(raw && z && rays_d && S >= 1, "nb_composite_fwd: bad arguments");
   composite_fwd_kernel<<<grid_for(n, 8), 256, 0, as_stream(stream)>>>(raw, z, rays_d, noise, n, S, white_bkgd,
                                                                        rgb_map, disp, acc, weights, depth);
   return check_launch("nb_composite_fwd");
@@ -214,12 +214,12 @@ int nb_composite_fwd(const float* raw, const float* z, const float* rays_d, cons
 int nb_composite_bwd(const float* raw, const float* z, const float* rays_d, const float* noise, int64_t n, int S,
                      int white_bkgd, const float* d_rgb, const float* d_disp, const float* d_acc,
                      const float* d_depth, float* d_raw, float* d_rays_d, void* stream) {
+  if (n == 0) return 0;
   NB_REQUIRE(raw && z && rays_d && d_raw && S >= 1, "nb_composite_bwd: bad arguments");
   if (S > 512) {
     set_error("nb_composite_bwd: S=%d > 512 samples per ray is not implemented", S);
     return NB_E_UNSUPPORTED;
   }
-  if (n == 0) return 0;
   int grid = grid_for(n, 8);
   cudaStream_t st = as_stream(stream);
 #define NB_LAUNCH_BWD(C)                                                                                         \

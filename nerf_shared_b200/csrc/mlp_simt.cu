@@ -148,13 +148,13 @@ using namespace nb;
 
 extern "C" int nb_mlp_fwd_f32(const NbMlpWeights* w, const float* pts, const float* viewdirs, int64_t M, int S,
                               float* raw, void* stream) {
+  if (M == 0) return 0;
   NB_REQUIRE(w && pts && viewdirs && raw && S >= 1, "nb_mlp_fwd_f32: bad arguments");
   NB_REQUIRE(M % S == 0, "nb_mlp_fwd_f32: M=%lld is not a multiple of S=%d", (long long)M, S);
   if (w->L_pts < 0 || w->L_pts > 15 || w->L_dirs < 0 || w->L_dirs > 6) {
     set_error("nb_mlp_fwd_f32: encoding octaves (%d,%d) outside [0,15]x[0,6]", w->L_pts, w->L_dirs);
     return NB_E_UNSUPPORTED;
   }
-  if (M == 0) return 0;
   int64_t ntiles = (M + kTS - 1) / kTS;
   int grid = (int)(ntiles < (int64_t)kNumSMs ? ntiles : (int64_t)kNumSMs);
   mlp_fwd_f32_kernel<<<grid, 256, kSimtSmem, as_stream(stream)>>>(*w, pts, viewdirs, M, S, raw);

@@ -526,13 +526,13 @@ int nb_mlp_pack(const NbMlpWeights* w, void* packed, void* stream) {
 
 int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, const float* viewdirs, int64_t M,
                   int S, float* raw, void* acts, void* stream) {
+  if (M == 0) return 0;
   NB_REQUIRE(packed && pts && viewdirs && raw && S >= 1, "nb_mlp_fwd_tc: bad arguments");
   NB_REQUIRE(M % S == 0, "nb_mlp_fwd_tc: M=%lld is not a multiple of S=%d", (long long)M, S);
   if (L_pts != 10 || L_dirs != 4) {
     set_error("nb_mlp_fwd_tc: only multires=10 / multires_views=4 is instantiated (got %d, %d)", L_pts, L_dirs);
     return NB_E_UNSUPPORTED;
   }
-  if (M == 0) return 0;
   const int64_t tiles = (M + kTileM - 1) / kTileM;
   const int64_t pairs = (tiles + 1) / 2;
   NB_REQUIRE(pairs < (1ll << 30), "nb_mlp_fwd_tc: M too large for one launch");

@@ -258,8 +258,8 @@ int nb_get_rays_fwd(int H, int W, float fx, float fy, float cx, float cy, const 
 
 int nb_get_rays_sel_fwd(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, int c2w_ld,
                         const int64_t* pix, int64_t n, float* rays_o, float* rays_d, float* viewdirs, void* stream) {
-  NB_REQUIRE(H > 0 && W > 0 && c2w && rays_o && rays_d && c2w_ld >= 4, "nb_get_rays: bad arguments");
   if (n == 0) return 0;
+  NB_REQUIRE(H > 0 && W > 0 && c2w && rays_o && rays_d && c2w_ld >= 4, "nb_get_rays: bad arguments");
   get_rays_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(H, W, fx, fy, cx, cy, c2w, c2w_ld, pix, n, rays_o,
                                                                     rays_d, viewdirs);
   return check_launch("nb_get_rays");
@@ -267,31 +267,31 @@ int nb_get_rays_sel_fwd(int H, int W, float fx, float fy, float cx, float cy, co
 
 int nb_get_rays_bwd(int H, int W, float fx, float fy, float cx, float cy, const int64_t* pix, int64_t n,
                     const float* d_rays_o, const float* d_rays_d, float* d_c2w, void* stream) {
-  NB_REQUIRE(H > 0 && W > 0 && d_c2w, "nb_get_rays_bwd: bad arguments");
   if (n == 0 || (!d_rays_o && !d_rays_d)) return 0;
+  NB_REQUIRE(H > 0 && W > 0 && d_c2w, "nb_get_rays_bwd: bad arguments");
   get_rays_bwd_kernel<<<grid_for(n, 256 * 8, 4), 256, 0, as_stream(stream)>>>(H, W, fx, fy, cx, cy, pix, n, d_rays_o,
                                                                                d_rays_d, d_c2w);
   return check_launch("nb_get_rays_bwd");
 }
 
 int nb_normalize_fwd(const float* v, int64_t n, float* out, void* stream) {
-  NB_REQUIRE(v && out, "nb_normalize_fwd: null pointer");
   if (n == 0) return 0;
+  NB_REQUIRE(v && out, "nb_normalize_fwd: null pointer");
   normalize_fwd_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(v, n, out);
   return check_launch("nb_normalize_fwd");
 }
 
 int nb_normalize_bwd(const float* v, const float* d_out, int64_t n, float* d_v, void* stream) {
-  NB_REQUIRE(v && d_out && d_v, "nb_normalize_bwd: null pointer");
   if (n == 0) return 0;
+  NB_REQUIRE(v && d_out && d_v, "nb_normalize_bwd: null pointer");
   normalize_bwd_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(v, d_out, n, d_v);
   return check_launch("nb_normalize_bwd");
 }
 
 int nb_ndc_rays_fwd(int H, int W, double focal, double near_, const float* rays_o, const float* rays_d, int64_t n,
                     float* out_o, float* out_d, void* stream) {
-  NB_REQUIRE(rays_o && rays_d && out_o && out_d, "nb_ndc_rays_fwd: null pointer");
   if (n == 0) return 0;
+  NB_REQUIRE(rays_o && rays_d && out_o && out_d, "nb_ndc_rays_fwd: null pointer");
   // the Python-scalar sub-expressions of utils.py:60-66 are evaluated in double, then enter fp32
   float sx = (float)(-1.0 / (W / (2.0 * focal)));
   float sy = (float)(-1.0 / (H / (2.0 * focal)));
@@ -304,8 +304,8 @@ int nb_ndc_rays_fwd(int H, int W, double focal, double near_, const float* rays_
 int nb_ndc_rays_bwd(int H, int W, double focal, double near_, const float* rays_o, const float* rays_d,
                     const float* d_out_o, const float* d_out_d, int64_t n, float* d_rays_o, float* d_rays_d,
                     void* stream) {
-  NB_REQUIRE(rays_o && rays_d && d_rays_o && d_rays_d, "nb_ndc_rays_bwd: null pointer");
   if (n == 0) return 0;
+  NB_REQUIRE(rays_o && rays_d && d_rays_o && d_rays_d, "nb_ndc_rays_bwd: null pointer");
   float sx = (float)(-1.0 / (W / (2.0 * focal)));
   float sy = (float)(-1.0 / (H / (2.0 * focal)));
   ndc_bwd_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(sx, sy, (float)near_, rays_o, rays_d, d_out_o,
@@ -315,8 +315,8 @@ int nb_ndc_rays_bwd(int H, int W, double focal, double near_, const float* rays_
 
 int nb_sample_coarse(const float* rays, int64_t n, int ld, const float* t_vals, const float* t_rand, int S,
                      int lindisp, float* z, float* pts, void* stream) {
-  NB_REQUIRE(rays && t_vals && z && ld >= 8 && S >= 1, "nb_sample_coarse: bad arguments");
   if (n == 0) return 0;
+  NB_REQUIRE(rays && t_vals && z && ld >= 8 && S >= 1, "nb_sample_coarse: bad arguments");
   sample_coarse_kernel<<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays, n, ld, t_vals, t_rand, S, lindisp,
                                                                              z, pts);
   return check_launch("nb_sample_coarse");
@@ -324,16 +324,16 @@ int nb_sample_coarse(const float* rays, int64_t n, int ld, const float* t_vals, 
 
 int nb_ray_points_fwd(const float* rays_o, const float* rays_d, const float* z, int64_t n, int S, float* pts,
                       void* stream) {
-  NB_REQUIRE(rays_o && rays_d && z && pts && S >= 1, "nb_ray_points_fwd: bad arguments");
   if (n == 0) return 0;
+  NB_REQUIRE(rays_o && rays_d && z && pts && S >= 1, "nb_ray_points_fwd: bad arguments");
   ray_points_fwd_kernel<<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, z, n, S, pts);
   return check_launch("nb_ray_points_fwd");
 }
 
 int nb_ray_points_bwd(const float* z, const float* d_pts, int64_t n, int S, float* d_rays_o, float* d_rays_d,
                       void* stream) {
-  NB_REQUIRE(z && d_pts && S >= 1, "nb_ray_points_bwd: bad arguments");
   if (n == 0) return 0;
+  NB_REQUIRE(z && d_pts && S >= 1, "nb_ray_points_bwd: bad arguments");
   ray_points_bwd_kernel<<<grid_for(n, 8), 256, 0, as_stream(stream)>>>(z, d_pts, n, S, d_rays_o, d_rays_d);
   return check_launch("nb_ray_points_bwd");
 }

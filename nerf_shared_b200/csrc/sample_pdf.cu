@@ -160,16 +160,16 @@ extern "C" {
 
 int nb_invert_cdf(const float* bins, const float* cdf, const float* u, int64_t n, int B, int I, float* samples,
                   int64_t* inds, void* stream) {
-  NB_REQUIRE(bins && cdf && u && B >= 1 && I >= 1, "nb_invert_cdf: bad arguments");
   if (n == 0) return 0;
+  NB_REQUIRE(bins && cdf && u && B >= 1 && I >= 1, "nb_invert_cdf: bad arguments");
   invert_cdf_kernel<<<grid_for(n * I, 256), 256, 0, as_stream(stream)>>>(bins, cdf, u, n, B, I, samples, inds);
   return check_launch("nb_invert_cdf");
 }
 
 int nb_sample_pdf(const float* bins, const float* weights, const float* u, const float* u_det, int64_t n, int B, int I,
                   float* samples, void* stream) {
-  NB_REQUIRE(bins && weights && samples && B >= 2 && I >= 1 && (u || u_det), "nb_sample_pdf: bad arguments");
   if (n == 0) return 0;
+  NB_REQUIRE(bins && weights && samples && B >= 2 && I >= 1 && (u || u_det), "nb_sample_pdf: bad arguments");
   int Bp = (B + 31) / 32 * 32;
   if (Bp > 1024) {
     set_error("nb_sample_pdf: %d bins > 1024 is not implemented", B);
@@ -182,9 +182,9 @@ int nb_sample_pdf(const float* bins, const float* weights, const float* u, const
 
 int nb_sample_pdf_merge(const float* z, const float* weights, const float* u, const float* u_det, int64_t n, int S,
                         int I, float* z_out, float* z_std, float* z_samples, void* stream) {
+  if (n == 0) return 0;
   NB_REQUIRE(z && weights && z_out && S >= 3 && I >= 1, "nb_sample_pdf_merge: bad arguments");
   NB_REQUIRE(u || u_det, "nb_sample_pdf_merge: need u or u_det");
-  if (n == 0) return 0;
   int P = 2;
   while (P < S + I) P <<= 1;
   int Bp = (S + 31) / 32 * 32;

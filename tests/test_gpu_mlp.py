@@ -87,7 +87,8 @@ def test_tc_vs_bf16_oracle_and_fp32(n_rays, S):
     m = make_model(11)
     p = O.make_params(11)
     pts, vd = _inputs(n_rays, S, seed=S + n_rays)
-    out = m(pts.cuda(), vd.cuda())
+    with torch.no_grad():
+        out = m(pts.cuda(), vd.cuda())
     assert out.shape == (n_rays, S, 4)
     # fp32 device kernel as the reference at every size; CPU oracle on a bounded subset
     m32 = make_model(11, precision="fp32")
@@ -109,10 +110,10 @@ def test_tc_golden(golden):
 def test_tc_repacks_after_weight_update():
     m = make_model(11)
     pts, vd = _inputs(4, 64, seed=1)
-    a = m(pts.cuda(), vd.cuda()).clone()
     with torch.no_grad():
+        a = m(pts.cuda(), vd.cuda()).clone()
         m.rgb_linear.bias.add_(1.0)
-    b = m(pts.cuda(), vd.cuda())
+        b = m(pts.cuda(), vd.cuda())
     np.testing.assert_allclose((b - a)[..., :3].cpu().numpy(), 1.0, atol=1e-5)
     np.testing.assert_allclose((b - a)[..., 3].cpu().numpy(), 0.0, atol=1e-6)
 
@@ -124,8 +125,7 @@ def test_tc_linearity_in_last_layer_full_size():
     pts, vd = _inputs(1024, 192, seed=8)
     with torch.no_grad():
         m.rgb_linear.bias.zero_()
-    a = m(pts.cuda(), vd.cuda())[..., :3].clone()
-    with torch.no_grad():
+        a = m(pts.cuda(), vd.cuda())[..., :3].clone()
         m.rgb_linear.weight.mul_(2.0)
-    b = m(pts.cuda(), vd.cuda())[..., :3]
+        b = m(pts.cuda(), vd.cuda())[..., :3]
     assert torch.equal(b, 2.0 * a)
