@@ -245,7 +245,9 @@ def test_sample_pdf_merge_vs_oracle(mods, det, I):
     z_out, z_std, smp = _ops.sample_pdf_merge(z.cuda(), w.cuda(), I, None if u is None else u.cuda(), want_samples=True)
     _close_except_knife_edges(smp.cpu().numpy(), smp_ref.numpy(), 0.08)
     _close_except_knife_edges(z_out.cpu().numpy(), z_ref.numpy(), 0.08)
-    np.testing.assert_allclose(z_std.cpu().numpy(), std_ref.numpy(), rtol=1e-4, atol=1e-5)
+    # z_std inherits the knife-edge sample (one of I values may sit one bin over)
+    np.testing.assert_allclose(z_std.cpu().numpy(), std_ref.numpy(), rtol=0, atol=0.08 / np.sqrt(I) + 1e-5)
+    assert np.median(np.abs(z_std.cpu().numpy() - std_ref.numpy())) < 1e-5
     zo = z_out.cpu()
     assert (zo[:, 1:] >= zo[:, :-1]).all()                       # sortedness
     # idempotence / permutation property: merged = sort(cat(z, samples)) exactly
