@@ -1,0 +1,389 @@
+#!/usr/bin/env python
+"""bench.py -- the reference's headline workload on B200 (BASELINE.json).
+
+    python bench.py --gpus N --steps K --warmup W            # this framework (sm_100a kernels)
+    python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle port)
+
+A "step" is one training step of BASELINE.json configs[1]: lego-shaped synthetic Blender data,
+N_rand = 1024 rays per GPU, 64 coarse + 128 fine samples, coarse + fine forward/backward + Adam
+(reference main.py:72-112).  `value` is rays/s with the step's rays and targets already in HBM;
+`e2e` is the same step through the public API (utils.sample_random_ray_batch -> Renderer ->
+loss -> backward -> optimizer.step -> loss.item()), pinned-host -> device copies and the loss
+read-back inside the timed region.  One JSON line on stdout (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_FWD = 1186816        # per sample, SURVEY.md section 8d
+FLOP_TRAIN = 3489024      # fwd + wgrad + needed dgrad per sample
+H = W = 400
+N_IMAGES = 8
+S_COARSE, S_FINE = 64, 192
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--rays", type=int, default=1024, help="N_rand per GPU (weak scaling)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-render", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("bf16_tflops", 1590.0), d.get("bf16_tflops_sustained", 1400.0), d.get("hbm_gbs", 6650.0), "measured"
+    return 1590.0, 1400.0, 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.lines, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except Exception:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def synth_scene(seed=0):
+    """Blender-shaped synthetic data: poses on the standard orbit, random targets."""
+    from oracle import nerf_oracle as O   # pose / intrinsics generators only (no arithmetic on the timed path)
+    rng = np.random.default_rng(seed)
+    K = O.blender_intrinsics(H, W)
+    poses = np.stack([O.pose_spherical(float(t), -30.0, 4.0) for t in rng.uniform(-180, 180, N_IMAGES)], 0)
+    images = np.random.default_rng(seed + 1).random((N_IMAGES, H, W, 3), dtype=np.float32)
+    return K, poses.astype(np.float32), images
+
+
+class Args:  # the subset of config_parser flags the API helpers read (configs/lego.txt)
+    N_importance, N_samples, N_rand = 128, 64, 1024
+    netdepth = netdepth_fine = 8
+    netwidth = netwidth_fine = 256
+    use_viewdirs, multires, multires_views, i_embed = True, 10, 4, 0
+    perturb, raw_noise_std, white_bkgd, lindisp = 1.0, 0.0, True, False
+    dataset_type, no_ndc, lrate, no_batching = "blender", False, 5e-4, True
+    precrop_iters, precrop_frac, chunk = 0, 0.5, 32768
+
+
+def run_b200(a):
+    import torch.distributed as dist
+    from nerf_shared_b200 import _lib, _ops, utils
+    from oracle import nerf_oracle as O
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    utils.device = dev
+    args = Args()
+    args.N_rand = a.rays
+    torch.manual_seed(1234 + rank)
+    np.random.seed(1234 + rank)
+
+    K, poses, images = synth_scene()
+    coarse, fine = utils.create_nerf_models(args)
+    # identical random-init weights on every rank (seeded numpy stream)
+    coarse.load_state_dict(O.make_params(11)); fine.load_state_dict(O.make_params(12))
+    opt = utils.get_optimizer(coarse, fine, args)
+    opt.grad_scale = 1.0 / world
+    renderer = utils.get_renderer(args, {"near": 2.0, "far": 6.0})
+    renderer.train()
+    poses_d = torch.tensor(poses, device=dev)
+    images_pinned = torch.from_numpy(images).pin_memory()
+    hwf = [H, W, float(K[0][0])]
+    i_train = np.arange(N_IMAGES)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def train_step(batch_rays, target):
+        rgb, _, _, extras = renderer.render_from_rays(H, W, K, chunk=args.chunk, rays=batch_rays, coarse_model=coarse,
+                                                      fine_model=fine, retraw=True)
+        opt.zero_grad()
+        loss = utils.img2mse(rgb, target) + utils.img2mse(extras["rgb0"], target)
+        loss.backward()
+        if world > 1:
+            dist.all_reduce(opt.flat_g)
+        opt.step()
+        return loss
+
+    # ---- device-resident batches (value) ------------------------------------------------------
+    n_pool = 8
+    pool = []
+    for i in range(n_pool):
+        pix = torch.from_numpy(np.random.choice(H * W, a.rays, replace=False)).to(dev)
+        ro, rd = utils.get_rays_at(H, W, K, poses_d[i % N_IMAGES, :3, :4], pix)
+        tgt = torch.from_numpy(images[i % N_IMAGES].reshape(-1, 3)[pix.cpu().numpy()]).to(dev)
+        pool.append((torch.stack([ro, rd], 0), tgt))
+
+    for i in range(max(a.warmup, 3)):
+        train_step(*pool[i % n_pool])
+    sync_all()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    l0 = _lib.launch_count()
+    sync_all()
+    for i in range(a.steps):
+        flush.zero_()                        # L2 flush between timed iterations (outside the events)
+        ev[i][0].record()
+        train_step(*pool[i % n_pool])
+        ev[i][1].record()
+    sync_all()
+    launches = _lib.launch_count() - l0
+    clocks = sampler.stop()
+    ms = sum(s.elapsed_time(e) for s, e in ev) / a.steps
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item())
+    value = world * a.rays / (ms_step * 1e-3)
+
+    # ---- end to end through the public API (e2e) -----------------------------------------------
+    def e2e_step(i):
+        batch_rays, target, _, _ = utils.sample_random_ray_batch(args, images_pinned, poses_d, None, a.rays, False, None,
+                                                                 i_train, hwf, K, 0, i + 1)
+        return float(train_step(batch_rays, target).item())
+
+    for i in range(3):
+        e2e_step(i)
+    sync_all()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(a.steps):
+        e2e_step(i)
+    e1.record()
+    sync_all()
+    e2e_ms = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / a.steps
+    t = torch.tensor([e2e_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t.item())
+    h2d = a.rays * 8 + a.rays * 3 * 4      # int64 pixel ids + fp32 targets per step
+    e2e = {"value": world * a.rays / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+           "ms_per_step": e2e_ms}
+
+    out = {"metric": "train_rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": a.steps,
+           "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+           "config": {"workload": "lego-shaped synthetic Blender training step (BASELINE.json configs[1]): N_rand=%d rays/GPU, "
+                                  "64 coarse + 128 fine samples, D8 W256 coarse+fine fwd/bwd + Adam" % a.rays,
+                      "global_rays_per_step": world * a.rays, "parallelism": "dp%d (ray-sharded, flat-gradient all-reduce)" % world,
+                      "l2": "256 MiB flush between timed iterations", "timing": "CUDA events per step, max over ranks"},
+           "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+
+    if rank == 0:
+        out.update(kernel_breakdown(a, coarse, fine, pool[0], dev))
+        if not a.no_render and world == 1:
+            out["render"] = render_leg(renderer, coarse, fine, K, poses_d, dev)
+        if not a.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_train_baseline(budget_s=15.0)
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def kernel_breakdown(a, coarse, fine, batch, dev):
+    """Times the three tensor-core kernels of the fine pass alone (CUDA events on the launching
+    stream) and reports the roofline of the dominant one."""
+    import ctypes as C
+
+    from nerf_shared_b200 import _bwd, _lib, _ops
+    burst, sustained, hbm, src = peaks()
+    M = a.rays * S_FINE
+    pts = torch.rand(M, 3, device=dev) * 6 - 3
+    vd = torch.nn.functional.normalize(torch.randn(a.rays, 3, device=dev), dim=-1)
+    d_raw = torch.randn(M, 4, device=dev) * 1e-3
+    lib = _lib.load()
+
+    def timed(fn, reps=10):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    t_fwd = timed(lambda: _ops.mlp_forward_tc(fine, pts, vd, S_FINE, save_acts=True))
+    raw, acts = _ops.mlp_forward_tc(fine, pts, vd, S_FINE, save_acts=True)
+    offs, total = _bwd.grad_layout(fine)
+    grads = torch.zeros(total, device=dev)
+    dA = torch.empty(int(lib.nb_mlp_da_bytes(M)), dtype=torch.uint8, device=dev)
+    pk = _ops.packed_weights(fine, backward=True)
+    off_arr = (C.c_int64 * 24)(*offs)
+
+    def bwd(with_w):
+        _lib.check(lib.nb_mlp_bwd_tc(_lib.ptr(pk), 10, 4, _lib.ptr(acts), _lib.ptr(d_raw), M, _lib.ptr(dA), off_arr,
+                                     _lib.ptr(grads) if with_w else None, _lib.stream_ptr()))
+    t_dgrad = timed(lambda: bwd(False))
+    t_bwd = timed(lambda: bwd(True))
+    t_wgrad = max(t_bwd - t_dgrad, 1e-6)
+    flops = {"mlp_fwd_tc(fine)": FLOP_FWD * M, "mlp_dgrad(fine)": (FLOP_FWD - 2 * (63 * 256 * 2 + 27 * 128 + 256 + 384)) * M,
+             "mlp_wgrad+small(fine)": FLOP_FWD * M}
+    times = {"mlp_fwd_tc(fine)": t_fwd, "mlp_dgrad(fine)": t_dgrad, "mlp_wgrad+small(fine)": t_wgrad}
+    top = max(times, key=times.get)
+    ach = flops[top] / times[top] / 1e9
+    return {"roofline": {"bound": "tensor", "kernel": top, "achieved": ach, "peak": burst, "unit": "TFLOP/s", "frac": ach / burst,
+                         "traffic": None, "peak_source": src + " bf16 burst (kernel timed alone)",
+                         "per_kernel_ms": {k: round(v, 4) for k, v in times.items()},
+                         "per_kernel_tflops": {k: round(flops[k] / times[k] / 1e9, 1) for k in times}}}
+
+
+def render_leg(renderer, coarse, fine, K, poses_d, dev):
+    """800x800 full-res render (BASELINE.json configs[3] on one GPU): frames/s, inputs resident."""
+    from oracle import nerf_oracle as O
+    K8 = O.blender_intrinsics(800, 800)
+    renderer.eval()
+    perturb = renderer.perturb
+    renderer.perturb = 0.0
+    with torch.no_grad():
+        renderer.render_from_pose(800, 800, K8, 32768, poses_d[0, :3, :4], coarse, fine, retraw=False)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        n = 3
+        for i in range(n):
+            renderer.render_from_pose(800, 800, K8, 32768, poses_d[(i + 1) % N_IMAGES, :3, :4], coarse, fine, retraw=False)
+        e1.record()
+        torch.cuda.synchronize()
+    renderer.perturb = perturb
+    ms = e0.elapsed_time(e1) / n
+    burst, sustained, _, _ = peaks()
+    tf = 640000 * (64 + 192) * FLOP_FWD / ms / 1e9
+    return {"workload": "800x800 Blender render, 64+128 samples, 1 GPU", "fps": 1e3 / ms, "ms_per_frame": ms,
+            "mlp_tflops": tf, "frac_of_sustained_peak": tf / sustained}
+
+
+def cpu_step_fn():
+    """The reference's CPU path for the same step (oracle port: torch CPU fp32 autograd + Adam,
+    main.py:72-112), all host threads.  Returns step(n_rays) -> seconds."""
+    from oracle import nerf_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    pc, pf = O.make_params(11), O.make_params(12)
+    K = O.blender_intrinsics(H, W)
+    c2w = torch.from_numpy(O.pose_spherical(30.0, -30.0, 4.0))[:3, :4]
+    ro, rd = O.get_rays(H, W, K, c2w)
+    ro, rd = ro.reshape(-1, 3), rd.reshape(-1, 3)
+    state = {k: [torch.zeros_like(v), torch.zeros_like(v)] for p in (pc, pf) for k, v in p.items()}
+
+    def step(n, it=[0]):
+        it[0] += 1
+        idx = torch.from_numpy(np.random.default_rng(it[0]).choice(H * W, n, replace=False))
+        tgt = torch.rand(n, 3)
+        t0 = time.perf_counter()
+        loss, gc, gf, _ = O.train_step_grads(pc, pf, ro[idx].contiguous(), rd[idx].contiguous(), tgt, 2.0, 6.0,
+                                             t_rand=torch.rand(n, 64), u=torch.rand(n, 128))
+        for p, g in ((pc, gc), (pf, gf)):
+            for k in p:
+                p[k], state[k][0], state[k][1] = O.adam_step(p[k], g[k], state[k][0], state[k][1], it[0], 5e-4)
+        return time.perf_counter() - t0
+
+    return step
+
+
+def pick_rays(step, total_steps, budget_s):
+    probe = step(32)                                    # warm-up + calibration (time ~ linear in rays)
+    n = int(32 * budget_s / max(total_steps * probe, 1e-6))
+    n = max(32, min(1024, n))
+    return 1 << int(np.log2(n))
+
+
+def cpu_train_baseline(budget_s=15.0):
+    step = cpu_step_fn()
+    n = pick_rays(step, 3, budget_s)
+    best = min(step(n) for _ in range(3))
+    return {"value": n / best, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": "%d-ray training step (coarse+fine fwd/bwd + Adam) x3, best; oracle port, torch %s CPU fp32" % (n, torch.__version__),
+            "s_per_step": best}
+
+
+def run_reference(a):
+    """--impl reference: the reference's own CPU implementation of the step (oracle port) timed on
+    the host cores; rank 0 only.  Every step is a bounded sample (n rays) of the 1024-ray step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    step = cpu_step_fn()
+    n = pick_rays(step, a.steps + a.warmup, 150.0)
+    for _ in range(a.warmup):
+        step(n)
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        step(n)
+    per = (time.perf_counter() - t0) / a.steps
+    v = n / per
+    sample = "%d rays per step x %d steps; oracle port of main.py:72-112, torch %s CPU fp32" % (n, a.steps, torch.__version__)
+    out = {"impl": "reference", "metric": "train_rays_per_s", "value": v, "unit": "rays/s", "n_gpus": world, "steps": a.steps,
+           "warmup": a.warmup, "ms_per_step": per * 1e3, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": "lego-shaped synthetic Blender training step (BASELINE.json configs[1]), N_rand=1024; "
+                                  "timed on a bounded sample of %d rays per step" % n},
+           "cpu_baseline": {"kind": "port", "cores": torch.get_num_threads(), "sample": sample, "value": v, "unit": "rays/s"},
+           "e2e": {"value": v, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

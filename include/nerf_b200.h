@@ -142,10 +142,24 @@ NB_API int nb_mlp_pack(const NbMlpWeights* w, void* packed, void* stream);
 /* Persistent fused tcgen05/TMEM forward: encoding -> 10 GEMM layers -> raw, activations
  * never leave the SM.  bf16 operands, fp32 accumulation, sigma and rgb heads in fp32.
  * If `acts` is non-NULL the bf16 layer activations needed by the backward pass are stored
- * there ([M, NB_ACT_STRIDE] bf16, see nb_mlp_act_stride). */
+ * there (nb_mlp_act_bytes(M) bytes: per 128-sample tile 40 slabs of 16 KB in the kernels' own
+ * swizzled operand layout; opaque to the caller). */
 NB_API int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, const float* viewdirs, int64_t M,
                   int S, float* raw, void* acts, void* stream);
-NB_API int nb_mlp_act_stride(void);
+NB_API int64_t nb_mlp_act_bytes(int64_t M);
+
+/* Backward of the MLP from the activations nb_mlp_fwd_tc saved (autograd of nerf.py:110-134).
+ * packed_bwd: transposed bf16 weight slabs (nb_mlp_pack_bwd, nb_mlp_bwd_packed_bytes bytes).
+ * d_raw: [M,4] upstream gradient.  dA: scratch of nb_mlp_da_bytes(M) bytes (pre-activation
+ * gradients of every layer, tiled like the activations).  grads: flat fp32 buffer the weight /
+ * bias gradients are ACCUMULATED into (caller zeroes), laid out by grad_off_host24 (HOST array of
+ * 24 float offsets: pts_linears weights 0..7, their biases 8..15, feature w/b 16,17, alpha w/b
+ * 18,19, views w/b 20,21, rgb w/b 22,23); grads == NULL runs only the dgrad chain. */
+NB_API int64_t nb_mlp_bwd_packed_bytes(int L_pts, int L_dirs);
+NB_API int nb_mlp_pack_bwd(const NbMlpWeights* w, void* packed_bwd, void* stream);
+NB_API int64_t nb_mlp_da_bytes(int64_t M);
+NB_API int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
+                         void* dA, const int64_t* grad_off_host24, float* grads, void* stream);
 
 /* ---- optimizer ------------------------------------------------------------------------- */
 /* torch.optim.Adam (utils.py:170) on flat fp32 buffers; step is 1-based.
@@ -157,6 +171,8 @@ NB_API int nb_adam_step(float* p, const float* g, float* m, float* v, int64_t n,
 /* D[128,128] = A[128,K] * B[128,K]^T (bf16-rounded operands, fp32 accumulate) through the same
  * swizzle / descriptor / tcgen05 sequence as nb_mlp_fwd_tc; K in {64,128,192,256}. */
 NB_API int nb_debug_umma(const float* A, const float* B, int K, float* D, void* stream);
+/* D[128,128] = A[K,128]^T * B[K,128] with both operands MN-major (the wgrad operand mode); K in {64,128}. */
+NB_API int nb_debug_umma_mn(const float* A, const float* B, int K, float* D, void* stream);
 
 #ifdef __cplusplus
 }

@@ -59,7 +59,12 @@ SIGNATURES = {
     "nb_mlp_packed_bytes": (i64, [i32, i32]),
     "nb_mlp_pack": (i32, [C.POINTER(NbMlpWeights), vp, vp]),
     "nb_mlp_fwd_tc": (i32, [vp, i32, i32, vp, vp, i64, i32, vp, vp, vp]),
-    "nb_mlp_act_stride": (i32, []),
+    "nb_mlp_act_bytes": (i64, [i64]),
+    "nb_mlp_bwd_packed_bytes": (i64, [i32, i32]),
+    "nb_mlp_pack_bwd": (i32, [C.POINTER(NbMlpWeights), vp, vp]),
+    "nb_mlp_da_bytes": (i64, [i64]),
+    "nb_mlp_bwd_tc": (i32, [vp, i32, i32, vp, vp, i64, vp, C.POINTER(i64), vp, vp]),
+    "nb_debug_umma_mn": (i32, [vp, vp, i32, vp, vp]),
     "nb_adam_step": (i32, [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp]),
     "nb_debug_umma": (i32, [vp, vp, i32, vp, vp]),
 }

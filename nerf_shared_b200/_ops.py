@@ -263,9 +263,10 @@ def mlp_params(model):
              model.rgb_linear.weight, model.rgb_linear.bias])
 
 
-def packed_weights(model) -> torch.Tensor:
-    """bf16 operand blob + fp32 side table for the tensor-core kernels, re-packed whenever a
-    parameter changed (its autograd version counter or storage moved)."""
+def packed_weights(model, backward: bool = False) -> torch.Tensor:
+    """bf16 operand blob + fp32 side table for the tensor-core kernels (backward=True: the
+    transposed slabs of the dgrad chain), re-packed whenever a parameter changed (its autograd
+    version counter or storage moved)."""
     params = mlp_params(model)
     for p in params:
         if p.dtype != torch.float32 or not p.is_contiguous():
@@ -273,16 +274,21 @@ def packed_weights(model) -> torch.Tensor:
     dev = params[0].device
     lib = _lib_for(params[0])
     key = tuple((p.data_ptr(), p._version) for p in params)
-    cache = model.__dict__.get("_nb_packed")
+    slot = "_nb_packed_bwd" if backward else "_nb_packed"
+    cache = model.__dict__.get(slot)
     if cache is not None and cache[0] == key and cache[1].device == dev:
         return cache[1]
-    nbytes = int(lib.nb_mlp_packed_bytes(int(model.multires), int(model.multires_views)))
+    size_fn = lib.nb_mlp_bwd_packed_bytes if backward else lib.nb_mlp_packed_bytes
+    nbytes = int(size_fn(int(model.multires), int(model.multires_views)))
     buf = cache[1] if (cache is not None and cache[1].device == dev and cache[1].numel() == nbytes) else \
         torch.empty((nbytes,), device=dev, dtype=torch.uint8)
     w = mlp_weight_struct(model)
     with torch.cuda.device(dev):
-        check(lib.nb_mlp_pack(C.byref(w), ptr(buf), stream_ptr()), "nb_mlp_pack")
-    model.__dict__["_nb_packed"] = (key, buf)
+        if backward:
+            check(lib.nb_mlp_pack_bwd(C.byref(w), ptr(buf), stream_ptr()), "nb_mlp_pack_bwd")
+        else:
+            check(lib.nb_mlp_pack(C.byref(w), ptr(buf), stream_ptr()), "nb_mlp_pack")
+    model.__dict__[slot] = (key, buf)
     return buf
 
 
@@ -305,7 +311,7 @@ def mlp_forward_tc(model, pts, viewdirs, S, save_acts=False):
     raw = torch.empty((M, 4), device=p.device, dtype=torch.float32)
     acts = None
     if save_acts:
-        acts = torch.empty((M, int(lib.nb_mlp_act_stride())), device=p.device, dtype=torch.bfloat16)
+        acts = torch.empty((int(lib.nb_mlp_act_bytes(M)),), device=p.device, dtype=torch.uint8)
     with torch.cuda.device(p.device):
         check(lib.nb_mlp_fwd_tc(ptr(packed), int(model.multires), int(model.multires_views), ptr(p), ptr(v), M, S,
                                 ptr(raw), ptr(acts), stream_ptr()), "nb_mlp_fwd_tc")
@@ -333,6 +339,31 @@ class NerfMLP(torch.autograd.Function):
     def backward(ctx, g_raw):
         from . import _bwd
         return _bwd.nerf_mlp_backward(ctx, g_raw)
+
+
+ACT_SLABS, DA_SLABS = 40, 38
+
+
+def untile(buf: torch.Tensor, n_slabs: int, M: int) -> torch.Tensor:
+    """Decode a tiled/swizzled slab buffer (acts or dA) to a logical [M, n_slabs*64] bf16 matrix
+    (tests / debugging): chunk g of row r sits at physical chunk g ^ (r % 8)."""
+    tiles = (M + 127) // 128
+    x = buf.view(torch.bfloat16).view(tiles, n_slabs, 128, 8, 8)
+    r = torch.arange(128, device=buf.device)
+    g = torch.arange(8, device=buf.device)
+    phys = (g[None, :] ^ (r[:, None] % 8))                       # [128, 8]
+    idx = phys[None, None, :, :, None].expand(tiles, n_slabs, 128, 8, 8)
+    logical = torch.gather(x, 3, idx)                            # [tiles, slabs, 128, 8, 8]
+    return logical.permute(0, 2, 1, 3, 4).reshape(tiles * 128, n_slabs * 64)[:M]
+
+
+def debug_umma_mn(A: torch.Tensor, B: torch.Tensor) -> torch.Tensor:
+    lib = _lib_for(A)
+    a, b = f32c(A), f32c(B)
+    D = torch.empty((128, 128), device=a.device, dtype=torch.float32)
+    with torch.cuda.device(a.device):
+        check(lib.nb_debug_umma_mn(ptr(a), ptr(b), a.shape[0], ptr(D), stream_ptr()), "nb_debug_umma_mn")
+    return D
 
 
 def debug_umma(A: torch.Tensor, B: torch.Tensor) -> torch.Tensor:

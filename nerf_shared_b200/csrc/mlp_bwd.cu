@@ -1,0 +1,742 @@
+// Backward of the NeRF MLP on the tensor cores (autograd of nerf.py:110-134, main.py:103).
+//
+// Three kernels, all reading the tiled/swizzled activation slabs the forward kernel saved:
+//   1. dgrad chain  (mlp_dgrad_kernel): persistent fused tcgen05 kernel, mirror image of the
+//      forward: d_raw -> d(view hidden) -> d(feature) -> d(h7) ... -> d(h0) pre-activation
+//      gradients stay on the SM between layers; each layer's dA tile is also written to HBM
+//      (same slab image) for the weight-gradient pass.  Transposed bf16 weight slabs are
+//      streamed through a 5-stage bulk-copy ring.
+//   2. wgrad        (mlp_wgrad_kernel): dW_l = dA_l^T X_l as tcgen05 GEMMs whose reduction
+//      dimension is the sample axis.  Both operands are consumed MN-major straight from the
+//      saved slabs (a [128 samples x 64 features] swizzled slab is a valid MN-major operand),
+//      fp32 accumulation in TMEM (up to all 512 columns), partial results reduced into the
+//      fp32 gradient buffer with vector atomics.
+//   3. small grads  (mlp_small_grads_kernel): biases (column sums of dA) and the two CUDA-core
+//      heads (alpha_linear, rgb_linear).
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "mlp_common.cuh"
+#include "ptx.cuh"
+
+namespace nb {
+
+using namespace ptx;
+
+constexpr int kBwdSlabs = 68;         // views^T (4) + feature^T (8) + pts_linears[7..1]^T (7 x 8)
+constexpr int kBwdConstFloats = 640;  // rgb_w [3][128] | alpha_w [256]
+constexpr int kDaSlabs = 38;          // d_a0..d_a7 (4 each) | d_feature (4) | d_a(view hidden) (2)
+constexpr int kDaSlabFeat = 32, kDaSlabHv = 36;
+constexpr int kBwdStages = 5;
+
+// dgrad shared memory map
+constexpr uint32_t kBSmAct0 = 0, kBSmAct1 = 65536, kBSmRing = 131072;
+constexpr uint32_t kBSmConst = kBSmRing + kBwdStages * kSlabBytes;  // 212992
+constexpr uint32_t kBSmBar = kBSmConst + kBwdConstFloats * 4;       // 215552
+constexpr uint32_t kBSmTmemPtr = kBSmBar + 120;
+constexpr uint32_t kBSmemBytes = kBSmBar + 128 + 1024;
+
+__host__ __device__ constexpr int bwd_ks_count(int step) { return step == 0 ? 2 : 4; }
+__host__ __device__ constexpr int bwd_slab_base(int step) { return step == 0 ? 0 : 4 + 8 * (step - 1); }
+
+// ------------------------------------------------------------------------------------------
+// transposed weight packing: slab element (n, k) = W[out0 + k][in0 + n]
+// ------------------------------------------------------------------------------------------
+struct SlabSrcT {
+  const float* w;
+  int ld, in0, out0, kvalid;
+};
+struct PackArgsT {
+  SlabSrcT slab[kBwdSlabs];
+};
+
+__global__ void __launch_bounds__(256) pack_bwd_kernel(PackArgsT a, NbMlpWeights w, uint8_t* __restrict__ blob) {
+  int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx < kBwdSlabs * 128 * 8) {
+    int s = idx / 1024, rem = idx - s * 1024;
+    int n = rem >> 3, g = rem & 7;
+    const SlabSrcT src = a.slab[s];
+    uint32_t p[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int k = g * 8 + j * 2;
+      float lo = (k < src.kvalid) ? src.w[(size_t)(src.out0 + k) * src.ld + src.in0 + n] : 0.f;
+      float hi = (k + 1 < src.kvalid) ? src.w[(size_t)(src.out0 + k + 1) * src.ld + src.in0 + n] : 0.f;
+      p[j] = pack_bf16x2(lo, hi);
+    }
+    *reinterpret_cast<uint4*>(blob + (size_t)s * kSlabBytes + sw128_chunk_off(n, g)) = make_uint4(p[0], p[1], p[2], p[3]);
+  }
+  float* c = reinterpret_cast<float*>(blob + (size_t)kBwdSlabs * kSlabBytes);
+  if (idx < kBwdConstFloats) c[idx] = idx < 384 ? w.rgb_w[idx] : w.alpha_w[idx - 384];
+}
+
+// ------------------------------------------------------------------------------------------
+// dgrad chain
+// ------------------------------------------------------------------------------------------
+// d (bf16x2) * (h > 0): relu'(h) applied to a packed pair
+__device__ __forceinline__ uint32_t relu_mask2(uint32_t d, uint32_t h) {
+  __nv_bfloat162 d2 = *reinterpret_cast<__nv_bfloat162*>(&d);
+  __nv_bfloat162 h2 = *reinterpret_cast<__nv_bfloat162*>(&h);
+  __nv_bfloat162 m = __hgt2(h2, __float2bfloat162_rn(0.f));
+  __nv_bfloat162 r = __hmul2(d2, m);
+  return *reinterpret_cast<uint32_t*>(&r);
+}
+
+// MODE 0: plain copy (d_feature); 1: + d_sigma * alpha_w, masked by h7; 2: masked
+template <int MODE>
+__device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, bool write_smem, int row,
+                                               const uint8_t* __restrict__ mask_src, uint8_t* __restrict__ da_dst,
+                                               float d_sigma, const float* __restrict__ alpha_w) {
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    uint4 hm[4];
+    if (MODE != 0 && mask_src) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        hm[g] = *reinterpret_cast<const uint4*>(mask_src + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g));
+    }
+    uint32_t v[32];
+    tmem_ld32(taddr + c * 32, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      float f[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[g * 8 + j]);
+      if (MODE == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; j += 4) {
+          float4 a = *reinterpret_cast<const float4*>(alpha_w + c * 32 + g * 8 + j);
+          f[j] = fmaf(d_sigma, a.x, f[j]); f[j + 1] = fmaf(d_sigma, a.y, f[j + 1]);
+          f[j + 2] = fmaf(d_sigma, a.z, f[j + 2]); f[j + 3] = fmaf(d_sigma, a.w, f[j + 3]);
+        }
+      }
+      uint32_t p0 = pack_bf16x2(f[0], f[1]), p1 = pack_bf16x2(f[2], f[3]), p2 = pack_bf16x2(f[4], f[5]),
+               p3 = pack_bf16x2(f[6], f[7]);
+      if (MODE != 0) {
+        if (mask_src) {
+          p0 = relu_mask2(p0, hm[g].x); p1 = relu_mask2(p1, hm[g].y);
+          p2 = relu_mask2(p2, hm[g].z); p3 = relu_mask2(p3, hm[g].w);
+        } else {
+          p0 = p1 = p2 = p3 = 0u;
+        }
+      }
+      const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g);
+      if (write_smem) st_shared_v4(act + off, p0, p1, p2, p3);
+      if (da_dst) *reinterpret_cast<uint4*>(da_dst + off) = make_uint4(p0, p1, p2, p3);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(384, 1) mlp_dgrad_kernel(const uint8_t* __restrict__ blob,
+                                                           const uint8_t* __restrict__ acts,
+                                                           const float* __restrict__ d_raw, int64_t M,
+                                                           uint8_t* __restrict__ dA, int num_pairs) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+  const float* cst = reinterpret_cast<const float*>(gbase + kBSmConst);
+  const uint32_t bar_full = base + kBSmBar, bar_empty = bar_full + 8 * kBwdStages, bar_act = bar_empty + 8 * kBwdStages,
+                 bar_acc = bar_act + 16, bar_const = bar_acc + 16;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kBwdStages; ++i) {
+      mbar_init(bar_full + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 1);
+    }
+    for (int x = 0; x < 2; ++x) {
+      mbar_init(bar_act + 8 * x, kTileM);
+      mbar_init(bar_acc + 8 * x, 1);
+    }
+    mbar_init(bar_const, 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(base + kBSmTmemPtr, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kBSmTmemPtr);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(bar_const, kBwdConstFloats * 4);
+      bulk_g2s(base + kBSmConst, blob + (size_t)kBwdSlabs * kSlabBytes, kBwdConstFloats * 4, bar_const);
+      uint32_t stage = 0, phase = 0;
+      for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+        for (int step = 0; step < 9; ++step) {
+          const int n = bwd_ks_count(step) * 2, sb = bwd_slab_base(step);
+          for (int x = 0; x < 2; ++x) {
+            for (int i = 0; i < n; ++i) {
+              mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+              mbar_expect_tx(bar_full + 8 * stage, kSlabBytes);
+              bulk_g2s(base + kBSmRing + stage * kSlabBytes, blob + (size_t)(sb + i) * kSlabBytes, kSlabBytes,
+                       bar_full + 8 * stage);
+              if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(128, 128);
+      uint32_t stage = 0, phase = 0, par_act0 = 0, par_act1 = 0;
+      for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+        for (int step = 0; step < 9; ++step) {
+          const int nks = bwd_ks_count(step);
+          for (int x = 0; x < 2; ++x) {
+            const uint32_t sAct = base + (x ? kBSmAct1 : kBSmAct0);
+            if (x == 0) { mbar_wait(bar_act, par_act0); par_act0 ^= 1; }
+            else { mbar_wait(bar_act + 8, par_act1); par_act1 ^= 1; }
+            tc_fence_after();
+            const uint32_t d = tmem + x * 256;
+            for (int ks = 0; ks < nks; ++ks) {
+              const uint64_t adesc = make_desc_kmajor_sw128(sAct + ks * kSlabBytes);
+              for (int nh = 0; nh < 2; ++nh) {
+                mbar_wait(bar_full + 8 * stage, phase);
+                tc_fence_after();
+                const uint64_t bdesc = make_desc_kmajor_sw128(base + kBSmRing + stage * kSlabBytes);
+                for (int k16 = 0; k16 < 4; ++k16)
+                  umma_bf16(d + nh * 128, adesc + 2 * k16, bdesc + 2 * k16, idesc, (ks | k16) != 0);
+                umma_commit(bar_empty + 8 * stage);
+                if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
+              }
+            }
+            umma_commit(bar_acc + 8 * x);
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    const int x = (warp - 4) >> 2;
+    const int row = ((warp & 3) << 5) | lane;
+    const uint32_t sAct = base + (x ? kBSmAct1 : kBSmAct0);
+    const uint32_t taddr = tmem + x * 256 + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t my_act = bar_act + 8 * x, my_acc = bar_acc + 8 * x;
+    uint32_t par_acc = 0;
+    mbar_wait(bar_const, 0);
+    const float* wr = cst;
+    const float* wa = cst + 384;
+    for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+      const int64_t tile = (int64_t)pair * 2 + x;
+      const int64_t m = tile * kTileM + row;
+      const bool real = tile * kTileM < M;
+      const uint8_t* at = real ? acts + (size_t)tile * kActSlabs * kSlabBytes : nullptr;
+      uint8_t* dt = real ? dA + (size_t)tile * kDaSlabs * kSlabBytes : nullptr;
+      float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (m < M) g = *reinterpret_cast<const float4*>(d_raw + m * 4);
+      // prologue: d(view hidden) = (d_rgb . W_rgb) * relu'(hv)   (nerf.py:125-129 backwards)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int col = c * 32 + q * 8;
+          float f[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = g.x * wr[col + j] + g.y * wr[128 + col + j] + g.z * wr[256 + col + j];
+          uint32_t p0 = pack_bf16x2(f[0], f[1]), p1 = pack_bf16x2(f[2], f[3]), p2 = pack_bf16x2(f[4], f[5]),
+                   p3 = pack_bf16x2(f[6], f[7]);
+          const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + q);
+          if (at) {
+            const uint4 h = *reinterpret_cast<const uint4*>(at + (size_t)kActSlabHv * kSlabBytes + off);
+            p0 = relu_mask2(p0, h.x); p1 = relu_mask2(p1, h.y); p2 = relu_mask2(p2, h.z); p3 = relu_mask2(p3, h.w);
+          } else {
+            p0 = p1 = p2 = p3 = 0u;
+          }
+          st_shared_v4(sAct + off, p0, p1, p2, p3);
+          if (dt) *reinterpret_cast<uint4*>(dt + (size_t)kDaSlabHv * kSlabBytes + off) = make_uint4(p0, p1, p2, p3);
+        }
+      }
+      fence_proxy_async();
+      mbar_arrive(my_act);
+#pragma unroll 1
+      for (int step = 0; step < 9; ++step) {
+        mbar_wait(my_acc, par_acc);
+        par_acc ^= 1;
+        tc_fence_after();
+        if (step == 0) {
+          dgrad_epilogue<0>(taddr, sAct, true, row, nullptr, dt ? dt + (size_t)kDaSlabFeat * kSlabBytes : nullptr, 0.f,
+                            nullptr);
+        } else {
+          const int l = 8 - step;  // produces d_a_l, masked by h_l: step 1 -> l = 7 ... step 8 -> l = 0
+          const uint8_t* ms = at ? at + (size_t)l * 4 * kSlabBytes : nullptr;
+          uint8_t* dd = dt ? dt + (size_t)l * 4 * kSlabBytes : nullptr;
+          if (step == 1) dgrad_epilogue<1>(taddr, sAct, true, row, ms, dd, g.w, wa);
+          else dgrad_epilogue<2>(taddr, sAct, step < 8, row, ms, dd, 0.f, nullptr);
+        }
+        if (step < 8) {
+          fence_proxy_async();
+          tc_fence_before();
+          mbar_arrive(my_act);
+        } else {
+          tc_fence_before();
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------
+// wgrad: dW[out, in] += sum_samples dA[s, out] * X[s, in]
+// ------------------------------------------------------------------------------------------
+struct WJob {
+  int a_slab;     // first dA slab (out features), m_blocks*2 consecutive slabs
+  int m_blocks;   // out features / 128
+  int b_slab;     // first activation slab (in features)
+  int n_cols;     // in features rounded up to 64 (64 or 256)
+  int n_valid;    // in features actually present
+  int ld;         // row stride of the fp32 weight gradient
+  int64_t off;    // float offset of dW[0][first in-feature] in the flat gradient buffer
+};
+constexpr int kNumWJobs = 12;
+struct WJobs {
+  WJob job[kNumWJobs];
+};
+
+constexpr int kWStages = 3;
+constexpr uint32_t kWStageBytes = 65536;  // 64 samples x (256 + 256) features
+constexpr uint32_t kWSmBar = kWStages * kWStageBytes;
+constexpr uint32_t kWSmTmemPtr = kWSmBar + 120;
+constexpr uint32_t kWSmemBytes = kWSmBar + 128 + 1024;
+
+// MN-major operand, 128-byte swizzle: 64-feature blocks `lbo` bytes apart, 8-sample groups 1024 B apart
+__device__ __forceinline__ uint64_t make_desc_mnmajor_sw128(uint32_t smem_addr, uint32_t lbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)(lbo >> 4) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__host__ __device__ constexpr uint32_t make_idesc_bf16_mn(int M, int N) {
+  return make_idesc_bf16(M, N) | (1u << 15) | (1u << 16);  // A and B MN-major
+}
+
+__global__ void __launch_bounds__(256, 1) mlp_wgrad_kernel(WJobs jobs, const uint8_t* __restrict__ acts,
+                                                           const uint8_t* __restrict__ dA, int num_tiles,
+                                                           int tiles_per_unit, int num_units,
+                                                           float* __restrict__ grads) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t bar_full = base + kWSmBar, bar_empty = bar_full + 8 * kWStages, bar_acc = bar_empty + 8 * kWStages,
+                 bar_flush = bar_acc + 8;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kWStages; ++i) {
+      mbar_init(bar_full + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 1);
+    }
+    mbar_init(bar_acc, 1);
+    mbar_init(bar_flush, 128);
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(base + kWSmTmemPtr, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kWSmTmemPtr);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        const WJob j = jobs.job[u % kNumWJobs];
+        const int t0 = (u / kNumWJobs) * tiles_per_unit;
+        const int t1 = min(t0 + tiles_per_unit, num_tiles);
+        const int na = j.m_blocks * 2, nb_ = j.n_cols / 64;
+        for (int t = t0; t < t1; ++t) {
+          const uint8_t* da_t = dA + (size_t)t * kDaSlabs * kSlabBytes + (size_t)j.a_slab * kSlabBytes;
+          const uint8_t* ac_t = acts + (size_t)t * kActSlabs * kSlabBytes + (size_t)j.b_slab * kSlabBytes;
+          for (int half = 0; half < 2; ++half) {
+            mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+            mbar_expect_tx(bar_full + 8 * stage, (na + nb_) * 8192);
+            const uint32_t dst = base + stage * kWStageBytes;
+            for (int s = 0; s < na; ++s)
+              bulk_g2s(dst + s * 8192, da_t + (size_t)s * kSlabBytes + half * 8192, 8192, bar_full + 8 * stage);
+            for (int s = 0; s < nb_; ++s)
+              bulk_g2s(dst + (na + s) * 8192, ac_t + (size_t)s * kSlabBytes + half * 8192, 8192, bar_full + 8 * stage);
+            if (++stage == kWStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0, par_flush = 0;
+      bool first_unit = true;
+      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+        const WJob j = jobs.job[u % kNumWJobs];
+        const int t0 = (u / kNumWJobs) * tiles_per_unit;
+        const int t1 = min(t0 + tiles_per_unit, num_tiles);
+        const int na = j.m_blocks * 2;
+        const uint32_t idesc = make_idesc_bf16_mn(128, j.n_cols);
+        if (!first_unit) {  // the previous unit's accumulators must be drained before they are overwritten
+          mbar_wait(bar_flush, par_flush);
+          par_flush ^= 1;
+          tc_fence_after();
+        }
+        first_unit = false;
+        bool acc = false;
+        for (int t = t0; t < t1; ++t) {
+          for (int half = 0; half < 2; ++half) {
+            mbar_wait(bar_full + 8 * stage, phase);
+            tc_fence_after();
+            const uint32_t sa = base + stage * kWStageBytes, sb = sa + na * 8192;
+            for (int mb = 0; mb < j.m_blocks; ++mb) {
+              for (int k16 = 0; k16 < 4; ++k16) {
+                const uint64_t ad = make_desc_mnmajor_sw128(sa + mb * 2 * 8192 + k16 * 2048, 8192);
+                const uint64_t bd = make_desc_mnmajor_sw128(sb + k16 * 2048, 8192);
+                umma_bf16(tmem + mb * j.n_cols, ad, bd, idesc, (acc || k16 != 0) ? 1u : 0u);
+              }
+            }
+            acc = true;
+            umma_commit(bar_empty + 8 * stage);
+            if (++stage == kWStages) { stage = 0; phase ^= 1; }
+          }
+        }
+        umma_commit(bar_acc);
+      }
+    }
+  } else if (warp >= 4) {
+    // flush warps: TMEM lane = out feature within the 128-block
+    const int row = ((warp & 3) << 5) | lane;
+    uint32_t par_acc = 0;
+    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+      const WJob j = jobs.job[u % kNumWJobs];
+      mbar_wait(bar_acc, par_acc);
+      par_acc ^= 1;
+      tc_fence_after();
+      for (int mb = 0; mb < j.m_blocks; ++mb) {
+        float* grow = grads + j.off + (size_t)(mb * 128 + row) * j.ld;
+        for (int c = 0; c < j.n_cols; c += 32) {
+          uint32_t v[32];
+          tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + mb * j.n_cols + c, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 32; ++q)
+            if (c + q < j.n_valid) atomicAdd(grow + c + q, __uint_as_float(v[q]));
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(bar_flush);
+    }
+  }
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------------
+// biases and CUDA-core heads
+// ------------------------------------------------------------------------------------------
+struct SmallOffsets {
+  int64_t pts_b[8], feature_b, views_b, alpha_w, alpha_b, rgb_w, rgb_b;
+};
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    f[2 * j] = __uint_as_float(w[j] << 16);
+    f[2 * j + 1] = __uint_as_float(w[j] & 0xFFFF0000u);
+  }
+}
+
+// reduce acc[8] over the 32 threads that share the chunk column g, add 64 sums to dst[g*8 + j]
+__device__ __forceinline__ void reduce_cols(float (&acc)[8], float* red, float* dst, int n_valid) {
+  const int t = threadIdx.x;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[t * 8 + j] = acc[j];
+  __syncthreads();
+  if (t < 64) {
+    const int g = t >> 3, j = t & 7;
+    float s = 0.f;
+    for (int rg = 0; rg < 32; ++rg) s += red[(rg * 8 + g) * 8 + j];
+    if (t < n_valid) atomicAdd(dst + t, s);
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) mlp_small_grads_kernel(const uint8_t* __restrict__ acts,
+                                                              const uint8_t* __restrict__ dA,
+                                                              const float* __restrict__ d_raw, int64_t M,
+                                                              int num_tiles, int tiles_per_block, SmallOffsets o,
+                                                              float* __restrict__ grads) {
+  __shared__ float red[256 * 8];
+  const int t = threadIdx.x, g = t & 7, rg = t >> 3;
+  const int t0 = blockIdx.x * tiles_per_block, t1 = min(t0 + tiles_per_block, num_tiles);
+  if (t0 >= t1) return;
+  // biases: column sums of every dA slab
+  for (int s = 0; s < kDaSlabs; ++s) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int tile = t0; tile < t1; ++tile) {
+      const uint8_t* slab = dA + ((size_t)tile * kDaSlabs + s) * kSlabBytes;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float f[8];
+        unpack8(*reinterpret_cast<const uint4*>(slab + sw128_chunk_off(rg + 32 * i, g)), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    }
+    float* dst = s < 32 ? grads + o.pts_b[s >> 2] + (s & 3) * 64
+                        : (s < 36 ? grads + o.feature_b + (s - 32) * 64 : grads + o.views_b + (s - 36) * 64);
+    reduce_cols(acc, red, dst, 64);
+  }
+  // alpha_linear: dW = sum d_sigma * h7, db = sum d_sigma ; rgb_linear: dW[k] = sum d_rgb[k] * hv, db = sum d_rgb
+  for (int s = 0; s < 4; ++s) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int tile = t0; tile < t1; ++tile) {
+      const uint8_t* slab = acts + ((size_t)tile * kActSlabs + 28 + s) * kSlabBytes;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = rg + 32 * i;
+        const int64_t m = (int64_t)tile * kTileM + r;
+        const float ds = m < M ? d_raw[m * 4 + 3] : 0.f;
+        float f[8];
+        unpack8(*reinterpret_cast<const uint4*>(slab + sw128_chunk_off(r, g)), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(ds, f[j], acc[j]);
+      }
+    }
+    reduce_cols(acc, red, grads + o.alpha_w + s * 64, 64);
+  }
+  for (int k = 0; k < 3; ++k) {
+    for (int s = 0; s < 2; ++s) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int tile = t0; tile < t1; ++tile) {
+        const uint8_t* slab = acts + ((size_t)tile * kActSlabs + kActSlabHv + s) * kSlabBytes;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = rg + 32 * i;
+          const int64_t m = (int64_t)tile * kTileM + r;
+          const float dk = m < M ? d_raw[m * 4 + k] : 0.f;
+          float f[8];
+          unpack8(*reinterpret_cast<const uint4*>(slab + sw128_chunk_off(r, g)), f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = fmaf(dk, f[j], acc[j]);
+        }
+      }
+      reduce_cols(acc, red, grads + o.rgb_w + k * 128 + s * 64, 64);
+    }
+  }
+  // head biases: sums of d_raw columns
+  {
+    float a4[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int64_t m = (int64_t)t0 * kTileM + t; m < (int64_t)t1 * kTileM && m < M; m += 256) {
+      const float4 d = *reinterpret_cast<const float4*>(d_raw + m * 4);
+      a4[0] += d.x; a4[1] += d.y; a4[2] += d.z; a4[3] += d.w;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) a4[k] = warp_sum(a4[k]);
+    if ((t & 31) == 0) {
+      atomicAdd(grads + o.rgb_b + 0, a4[0]);
+      atomicAdd(grads + o.rgb_b + 1, a4[1]);
+      atomicAdd(grads + o.rgb_b + 2, a4[2]);
+      atomicAdd(grads + o.alpha_b, a4[3]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// MN-major UMMA self-test: D[128,128] = A[K,128]^T * B[K,128], K in {64, 128}
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) umma_mn_selftest_kernel(const float* __restrict__ A, const float* __restrict__ B,
+                                                                  int K, float* __restrict__ D) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t slab = K * 128;  // bytes of one [K samples x 64 features] block
+  const uint32_t sA = base, sB = base + 2 * slab, sBar = sB + 2 * slab, sPtr = sBar + 8;
+  const int warp = threadIdx.x >> 5;
+  // thread t fills sample row (t % K) for feature blocks
+  for (int idx = threadIdx.x; idx < K * 2 * 8; idx += 128) {
+    const int k = idx % K, fb = (idx / K) % 2, g = idx / (2 * K);
+    uint32_t pa[4], pb[4];
+    for (int j = 0; j < 4; ++j) {
+      const int f = fb * 64 + g * 8 + j * 2;
+      pa[j] = pack_bf16x2(A[k * 128 + f], A[k * 128 + f + 1]);
+      pb[j] = pack_bf16x2(B[k * 128 + f], B[k * 128 + f + 1]);
+    }
+    st_shared_v4(sA + fb * slab + sw128_chunk_off(k, g), pa[0], pa[1], pa[2], pa[3]);
+    st_shared_v4(sB + fb * slab + sw128_chunk_off(k, g), pb[0], pb[1], pb[2], pb[3]);
+  }
+  fence_proxy_async();
+  if (threadIdx.x == 0) {
+    mbar_init(sBar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(sPtr, 128);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + (sPtr - base));
+  if (threadIdx.x == 0) {
+    const uint32_t idesc = make_idesc_bf16_mn(128, 128);
+    for (int k16 = 0; k16 < K / 16; ++k16)
+      umma_bf16(tmem, make_desc_mnmajor_sw128(sA + k16 * 2048, slab), make_desc_mnmajor_sw128(sB + k16 * 2048, slab),
+                idesc, k16 != 0);
+    umma_commit(sBar);
+  }
+  mbar_wait(sBar, 0);
+  tc_fence_after();
+  const int row = threadIdx.x;
+  for (int c = 0; c < 4; ++c) {
+    uint32_t v[32];
+    tmem_ld32(tmem + ((uint32_t)(warp * 32) << 16) + c * 32, v);
+    tmem_ld_wait();
+    for (int j = 0; j < 32; ++j) D[row * 128 + c * 32 + j] = __uint_as_float(v[j]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 128);
+}
+
+int init_mlp_bwd(int) {
+  cudaError_t e = cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBSmemBytes);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemBytes);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(umma_mn_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 16384 + 2048);
+  if (e != cudaSuccess) {
+    set_error("init_mlp_bwd: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  return 0;
+}
+
+static int build_pack_args_t(const NbMlpWeights* w, PackArgsT& a) {
+  const int in_ch = 3 + 6 * w->L_pts, in_views = 3 + 6 * w->L_dirs;
+  if (in_ch > 64 || in_views > 32 || w->L_pts < 0 || w->L_dirs < 0) {
+    set_error("tensor-core MLP supports multires <= 10 and multires_views <= 4 (got %d, %d)", w->L_pts, w->L_dirs);
+    return NB_E_UNSUPPORTED;
+  }
+  int s = 0;
+  for (int step = 0; step < 9; ++step) {
+    const float* mat;
+    int ld, in_base = 0, kout;
+    if (step == 0) { mat = w->views_w; ld = 256 + in_views; kout = 128; }
+    else if (step == 1) { mat = w->feature_w; ld = 256; kout = 256; }
+    else {
+      const int l = 9 - step;  // pts_linears[7] ... pts_linears[1]
+      mat = w->pts_w[l];
+      ld = l == 5 ? 256 + in_ch : 256;
+      in_base = l == 5 ? in_ch : 0;  // the h part of cat[input_pts, h]
+      kout = 256;
+    }
+    for (int ks = 0; ks < bwd_ks_count(step); ++ks)
+      for (int nh = 0; nh < 2; ++nh) a.slab[s++] = SlabSrcT{mat, ld, in_base + nh * 128, ks * 64, kout - ks * 64 < 64 ? kout - ks * 64 : 64};
+  }
+  return s == kBwdSlabs ? 0 : NB_E_ARG;
+}
+
+}  // namespace nb
+
+using namespace nb;
+
+extern "C" {
+
+int64_t nb_mlp_bwd_packed_bytes(int L_pts, int L_dirs) {
+  (void)L_pts; (void)L_dirs;
+  return (int64_t)kBwdSlabs * kSlabBytes + kBwdConstFloats * 4;
+}
+
+int64_t nb_mlp_da_bytes(int64_t M) { return ((M + kTileM - 1) / kTileM) * (int64_t)kDaSlabs * kSlabBytes; }
+
+int nb_mlp_pack_bwd(const NbMlpWeights* w, void* packed_bwd, void* stream) {
+  NB_REQUIRE(w && packed_bwd, "nb_mlp_pack_bwd: null pointer");
+  NB_REQUIRE(((uintptr_t)packed_bwd & 15) == 0, "nb_mlp_pack_bwd: buffer must be 16-byte aligned");
+  PackArgsT a;
+  int rc = build_pack_args_t(w, a);
+  if (rc) return rc;
+  const int threads = kBwdSlabs * 128 * 8;
+  pack_bwd_kernel<<<(threads + 255) / 256, 256, 0, as_stream(stream)>>>(a, *w, (uint8_t*)packed_bwd);
+  return check_launch("nb_mlp_pack_bwd");
+}
+
+int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
+                  void* dA, const int64_t* grad_off_host24, float* grads, void* stream) {
+  if (M == 0) return 0;
+  NB_REQUIRE(packed_bwd && acts && d_raw && dA, "nb_mlp_bwd_tc: null pointer");
+  if (L_pts != 10 || L_dirs != 4) {
+    set_error("nb_mlp_bwd_tc: only multires=10 / multires_views=4 is instantiated (got %d, %d)", L_pts, L_dirs);
+    return NB_E_UNSUPPORTED;
+  }
+  const int in_ch = 3 + 6 * L_pts, in_views = 3 + 6 * L_dirs;
+  cudaStream_t st = as_stream(stream);
+  const int64_t tiles = (M + kTileM - 1) / kTileM;
+  const int64_t pairs = (tiles + 1) / 2;
+  NB_REQUIRE(pairs < (1ll << 30), "nb_mlp_bwd_tc: M too large for one launch");
+  {
+    const int grid = (int)(pairs < kNumSMs ? pairs : kNumSMs);
+    mlp_dgrad_kernel<<<grid, 384, kBSmemBytes, st>>>((const uint8_t*)packed_bwd, (const uint8_t*)acts, d_raw, M,
+                                                     (uint8_t*)dA, (int)pairs);
+    int rc = check_launch("mlp_dgrad_kernel");
+    if (rc) return rc;
+  }
+  if (!grads) return 0;  // frozen weights: only the dA chain was wanted
+  NB_REQUIRE(grad_off_host24, "nb_mlp_bwd_tc: gradient offsets missing");
+  const int64_t* off = grad_off_host24;  // 0..7 pts_w, 8..15 pts_b, 16 feat_w, 17 feat_b, 18 alpha_w, 19 alpha_b,
+                                         // 20 views_w, 21 views_b, 22 rgb_w, 23 rgb_b
+  {
+    WJobs jobs;
+    int n = 0;
+    jobs.job[n++] = WJob{0, 2, kActSlabEncP, 64, in_ch, in_ch, off[0]};                       // pts_linears[0]
+    for (int l = 1; l < 8; ++l) {
+      if (l == 5) {
+        jobs.job[n++] = WJob{20, 2, 16, 256, 256, 256 + in_ch, off[5] + in_ch};               // W5[:, in_ch:]  (h4)
+        jobs.job[n++] = WJob{20, 2, kActSlabEncP, 64, in_ch, 256 + in_ch, off[5]};            // W5[:, :in_ch]  (enc)
+      } else {
+        jobs.job[n++] = WJob{4 * l, 2, 4 * (l - 1), 256, 256, 256, off[l]};
+      }
+    }
+    jobs.job[n++] = WJob{kDaSlabFeat, 2, 28, 256, 256, 256, off[16]};                         // feature_linear (h7)
+    jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabFeat, 256, 256, 256 + in_views, off[20]};      // views[:, :256] (feature)
+    jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabEncD, 64, in_views, 256 + in_views, off[20] + 256};  // views[:, 256:]
+    NB_REQUIRE(n == kNumWJobs, "internal: wgrad job table");
+    int tpu = (int)((tiles * kNumWJobs + 2 * kNumSMs - 1) / (2 * kNumSMs));
+    if (tpu < 4) tpu = 4;
+    const int chunks = (int)((tiles + tpu - 1) / tpu);
+    const int units = chunks * kNumWJobs;
+    const int grid = units < kNumSMs ? units : kNumSMs;
+    mlp_wgrad_kernel<<<grid, 256, kWSmemBytes, st>>>(jobs, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, tpu,
+                                                     units, grads);
+    int rc = check_launch("mlp_wgrad_kernel");
+    if (rc) return rc;
+  }
+  {
+    SmallOffsets o;
+    for (int l = 0; l < 8; ++l) o.pts_b[l] = off[8 + l];
+    o.feature_b = off[17]; o.views_b = off[21]; o.alpha_w = off[18]; o.alpha_b = off[19];
+    o.rgb_w = off[22]; o.rgb_b = off[23];
+    int tpb = (int)((tiles + 2 * kNumSMs - 1) / (2 * kNumSMs));
+    if (tpb < 1) tpb = 1;
+    const int grid = (int)((tiles + tpb - 1) / tpb);
+    mlp_small_grads_kernel<<<grid, 256, 0, st>>>((const uint8_t*)acts, (const uint8_t*)dA, d_raw, M, (int)tiles, tpb, o,
+                                                 grads);
+    int rc = check_launch("mlp_small_grads_kernel");
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+int nb_debug_umma_mn(const float* A, const float* B, int K, float* D, void* stream) {
+  NB_REQUIRE(A && B && D && (K == 64 || K == 128), "nb_debug_umma_mn: bad arguments");
+  umma_mn_selftest_kernel<<<1, 128, 4 * K * 128 + 2048, as_stream(stream)>>>(A, B, K, D);
+  return check_launch("nb_debug_umma_mn");
+}
+
+}  // extern "C"

@@ -1,0 +1,20 @@
+// Constants shared by the tensor-core MLP kernels (forward: mlp_tc.cu, backward: mlp_bwd.cu).
+#pragma once
+#include <stdint.h>
+
+namespace nb {
+
+constexpr int kTileM = 128;
+constexpr int kSlabBytes = 16384;  // [128 x 64] bf16
+constexpr int kStages = 3;
+constexpr int kNumSlabs = 73;
+constexpr int kConstFloats = 3200;
+// Saved activations (training): per 128-sample tile, 40 slabs of 16 KB, each the same
+// [128 x 64] bf16 K-major SWIZZLE_128B image the kernels use in shared memory, so the backward
+// kernels can bulk-copy them straight into UMMA operands:
+//   slabs 4l..4l+3 = h_l (l = 0..7) | 32..35 = feature | 36,37 = view hidden | 38 = enc(pts) | 39 = enc(dirs)
+constexpr int kActSlabs = 40;
+constexpr int kActSlabFeat = 32, kActSlabHv = 36, kActSlabEncP = 38, kActSlabEncD = 39;
+
+
+}  // namespace nb

@@ -20,17 +20,11 @@
 // allocator, warps 4-7 = epilogue of tile A, warps 8-11 = epilogue of tile B.
 #include "common.cuh"
 #include "ptx.cuh"
+#include "mlp_common.cuh"
 
 namespace nb {
 
 using namespace ptx;
-
-constexpr int kTileM = 128;
-constexpr int kSlabBytes = 16384;  // [128 x 64] bf16
-constexpr int kStages = 3;
-constexpr int kNumSlabs = 73;
-constexpr int kConstFloats = 3200;
-constexpr int kActStride = 2432;  // bf16 per sample: h0..h7 (8*256) | feature (256) | view hidden (128)
 
 // fp32 side table offsets (floats)
 constexpr int kOffBias = 0;        // 8 x 256 trunk biases
@@ -212,12 +206,15 @@ __device__ __forceinline__ void encode3(float v0, float v1, float v2, float (&e)
 }
 
 template <int N>
-__device__ __forceinline__ void store_operand_row(uint32_t slab, int row, const float (&e)[N]) {
+__device__ __forceinline__ void store_operand_row(uint32_t slab, int row, const float (&e)[N],
+                                                  uint8_t* __restrict__ save_slab) {
 #pragma unroll
   for (int g = 0; g < N / 8; ++g) {
-    st_shared_v4(slab + sw128_chunk_off(row, g), pack_bf16x2(e[8 * g], e[8 * g + 1]),
-                 pack_bf16x2(e[8 * g + 2], e[8 * g + 3]), pack_bf16x2(e[8 * g + 4], e[8 * g + 5]),
-                 pack_bf16x2(e[8 * g + 6], e[8 * g + 7]));
+    const uint32_t p0 = pack_bf16x2(e[8 * g], e[8 * g + 1]), p1 = pack_bf16x2(e[8 * g + 2], e[8 * g + 3]),
+                   p2 = pack_bf16x2(e[8 * g + 4], e[8 * g + 5]), p3 = pack_bf16x2(e[8 * g + 6], e[8 * g + 7]);
+    const uint32_t off = sw128_chunk_off(row, g);
+    st_shared_v4(slab + off, p0, p1, p2, p3);
+    if (save_slab) *reinterpret_cast<uint4*>(save_slab + off) = make_uint4(p0, p1, p2, p3);
   }
 }
 
@@ -228,7 +225,7 @@ __device__ __forceinline__ void store_operand_row(uint32_t slab, int row, const 
 template <int MODE>
 __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __restrict__ bias,
                                                 const float* __restrict__ alpha_w, uint32_t act, int row,
-                                                float& sigma, __nv_bfloat16* __restrict__ save) {
+                                                float& sigma, uint8_t* __restrict__ save) {
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
     uint32_t v[32];
@@ -263,15 +260,16 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
         p0 = pack_bf16x2_relu(f[0], f[1]); p1 = pack_bf16x2_relu(f[2], f[3]);
         p2 = pack_bf16x2_relu(f[4], f[5]); p3 = pack_bf16x2_relu(f[6], f[7]);
       }
-      st_shared_v4(act + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g), p0, p1, p2, p3);
-      if (save) *reinterpret_cast<uint4*>(save + c * 32 + g * 8) = make_uint4(p0, p1, p2, p3);
+      const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g);
+      st_shared_v4(act + off, p0, p1, p2, p3);
+      if (save) *reinterpret_cast<uint4*>(save + off) = make_uint4(p0, p1, p2, p3);
     }
   }
 }
 
 // view branch: hv = relu(acc + b) (128 wide), rgb = hv . Wrgb^T + b_rgb in fp32 (nerf.py:125-129)
 __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __restrict__ cst, float& r, float& g_,
-                                               float& b_, __nv_bfloat16* __restrict__ save) {
+                                               float& b_, int row, uint8_t* __restrict__ save) {
   const float* bias = cst + kOffViewB;
   const float* wr = cst + kOffRgbW;
   r = cst[kOffRgbB]; g_ = cst[kOffRgbB + 1]; b_ = cst[kOffRgbB + 2];
@@ -299,8 +297,8 @@ __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __re
         b_ = fmaf(f[j], w2.x, b_); b_ = fmaf(f[j + 1], w2.y, b_); b_ = fmaf(f[j + 2], w2.z, b_); b_ = fmaf(f[j + 3], w2.w, b_);
       }
       if (save)
-        *reinterpret_cast<uint4*>(save + c * 32 + g * 8) = make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]),
-                                                                      pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+        *reinterpret_cast<uint4*>(save + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g)) =
+            make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
     }
   }
 }
@@ -312,7 +310,7 @@ template <int L_PTS, int L_DIRS>
 __global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __restrict__ blob,
                                                             const float* __restrict__ pts,
                                                             const float* __restrict__ viewdirs, int64_t M, int S,
-                                                            float* __restrict__ raw, __nv_bfloat16* __restrict__ acts,
+                                                            float* __restrict__ raw, uint8_t* __restrict__ acts,
                                                             int num_pairs) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -411,25 +409,27 @@ __global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __res
     uint32_t par_acc = 0;
     mbar_wait(bar_const, 0);
     for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
-      const int64_t m = ((int64_t)pair * 2 + x) * kTileM + row;
+      const int64_t tile = (int64_t)pair * 2 + x;
+      const int64_t m = tile * kTileM + row;
       const bool valid = m < M;
+      // whole tiles are saved (rows past M hold finite values computed from zero inputs)
+      uint8_t* save = (acts && tile * kTileM < M) ? acts + (size_t)tile * kActSlabs * kSlabBytes : nullptr;
       {
         float p0 = 0.f, p1 = 0.f, p2 = 0.f;
         if (valid) { p0 = pts[m * 3]; p1 = pts[m * 3 + 1]; p2 = pts[m * 3 + 2]; }
         float e[64];
         encode3<L_PTS>(p0, p1, p2, e);
-        store_operand_row(sEnc, row, e);
+        store_operand_row(sEnc, row, e, save ? save + kActSlabEncP * kSlabBytes : nullptr);
       }
       fence_proxy_async();
       mbar_arrive(my_act);
       float sigma = cst[kOffAlphaB];
-      __nv_bfloat16* save = (acts && valid) ? acts + m * kActStride : nullptr;
 #pragma unroll 1
       for (int layer = 0; layer < 9; ++layer) {
         mbar_wait(my_acc, par_acc);
         par_acc ^= 1;
         tc_fence_after();
-        __nv_bfloat16* sv = save ? save + layer * 256 : nullptr;
+        uint8_t* sv = save ? save + (size_t)layer * 4 * kSlabBytes : nullptr;
         if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, sigma, sv);
         else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, sigma, sv);
         else {
@@ -441,9 +441,9 @@ __global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __res
             const int64_t ray = m / S;
             v0 = viewdirs[ray * 3]; v1 = viewdirs[ray * 3 + 1]; v2 = viewdirs[ray * 3 + 2];
           }
-          float e[32];
+          float e[64];   // columns 32..63 are zero: the wgrad kernel reads the whole 64-wide slab
           encode3<L_DIRS>(v0, v1, v2, e);
-          store_operand_row(sEnc, row, e);
+          store_operand_row(sEnc, row, e, save ? save + kActSlabEncD * kSlabBytes : nullptr);
         }
         fence_proxy_async();
         tc_fence_before();
@@ -453,7 +453,7 @@ __global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __res
       par_acc ^= 1;
       tc_fence_after();
       float r, g, b;
-      epilogue_views(taddr, cst, r, g, b, save ? save + 2304 : nullptr);
+      epilogue_views(taddr, cst, r, g, b, row, save ? save + (size_t)kActSlabHv * kSlabBytes : nullptr);
       if (valid) *reinterpret_cast<float4*>(raw + m * 4) = make_float4(r, g, b, sigma);
       tc_fence_before();
     }
@@ -511,7 +511,7 @@ int64_t nb_mlp_packed_bytes(int L_pts, int L_dirs) {
   return (int64_t)kNumSlabs * kSlabBytes + kConstFloats * 4;
 }
 
-int nb_mlp_act_stride(void) { return kActStride; }
+int64_t nb_mlp_act_bytes(int64_t M) { return ((M + kTileM - 1) / kTileM) * (int64_t)kActSlabs * kSlabBytes; }
 
 int nb_mlp_pack(const NbMlpWeights* w, void* packed, void* stream) {
   NB_REQUIRE(w && packed, "nb_mlp_pack: null pointer");
@@ -538,7 +538,7 @@ int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, c
   NB_REQUIRE(pairs < (1ll << 30), "nb_mlp_fwd_tc: M too large for one launch");
   const int grid = (int)(pairs < kNumSMs ? pairs : kNumSMs);
   mlp_fwd_tc_kernel<10, 4><<<grid, 384, kSmemBytes, as_stream(stream)>>>(
-      (const uint8_t*)packed, pts, viewdirs, M, S, raw, (__nv_bfloat16*)acts, (int)pairs);
+      (const uint8_t*)packed, pts, viewdirs, M, S, raw, (uint8_t*)acts, (int)pairs);
   return check_launch("nb_mlp_fwd_tc");
 }
 

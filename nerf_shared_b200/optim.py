@@ -1,0 +1,136 @@
+"""Flat fused Adam (torch.optim.Adam semantics, reference utils.py:163-172 / main.py:104-112).
+
+All parameters, gradients and both moment buffers live in four flat fp32 tensors; one sm_100a
+kernel (nb_adam_step) updates everything.  The models' weight-gradient kernels accumulate
+straight into the flat gradient buffer (every `p.grad` is a view of it), which is also the single
+buffer the multi-GPU path all-reduces.  state_dict()/load_state_dict() keep torch.optim.Adam's
+format so reference checkpoints load both ways.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import check, ptr, stream_ptr
+
+
+class FlatAdam(torch.optim.Optimizer):
+    def __init__(self, params, lr=5e-4, betas=(0.9, 0.999), eps=1e-8):
+        params = list(params)
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=0, amsgrad=False, maximize=False, foreach=None,
+                        capturable=False, differentiable=False, fused=None)
+        super().__init__(params, defaults)
+        ps = [p for g in self.param_groups for p in g["params"]]
+        if not ps:
+            raise ValueError("FlatAdam got no parameters")
+        dev = ps[0].device
+        for p in ps:
+            if p.dtype != torch.float32 or p.device != dev:
+                raise ValueError("FlatAdam needs fp32 parameters on one device")
+        self._params = ps
+        self._offsets, total = [], 0
+        for p in ps:
+            self._offsets.append(total)
+            total += p.numel()
+        self._n = total
+        self.flat_p = torch.empty(total, device=dev, dtype=torch.float32)
+        self.flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.exp_avg = torch.zeros(total, device=dev, dtype=torch.float32)
+        self.exp_avg_sq = torch.zeros(total, device=dev, dtype=torch.float32)
+        self._step = 0
+        self.grad_scale = 1.0      # e.g. 1/world_size after a SUM all-reduce of flat_g
+        with torch.no_grad():
+            for p, o in zip(ps, self._offsets):
+                n = p.numel()
+                self.flat_p[o:o + n].copy_(p.detach().reshape(-1))
+                p.data = self.flat_p[o:o + n].view(p.shape)
+                p.grad = self.flat_g[o:o + n].view(p.shape)
+        self._by_id = {id(p): o for p, o in zip(ps, self._offsets)}
+
+    # the weight-gradient kernels look this up to accumulate in place (see _bwd.py)
+    def grad_offset(self, p):
+        return self._by_id.get(id(p))
+
+    def _grads_are_flat(self):
+        for p, o in zip(self._params, self._offsets):
+            g = p.grad
+            if g is None or g.data_ptr() != self.flat_g.data_ptr() + 4 * o:
+                return False
+        return True
+
+    def zero_grad(self, set_to_none: bool = False):
+        # gradients stay views of the flat buffer; one memset
+        if not self._grads_are_flat():
+            self._regather()
+        self.flat_g.zero_()
+
+    def _regather(self):
+        """Someone replaced a p.grad (set_to_none, external assignment): copy back into the flat buffer."""
+        with torch.no_grad():
+            for p, o in zip(self._params, self._offsets):
+                view = self.flat_g[o:o + p.numel()].view(p.shape)
+                if p.grad is None:
+                    view.zero_()
+                elif p.grad.data_ptr() != view.data_ptr():
+                    view.copy_(p.grad)
+                p.grad = view
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        if not self._grads_are_flat():
+            self._regather()
+        g0 = self.param_groups[0]
+        if any(g["lr"] != g0["lr"] for g in self.param_groups):
+            raise NotImplementedError("FlatAdam uses one learning rate for all parameter groups")
+        self._step += 1
+        b1, b2 = g0["betas"]
+        lib = _lib.load()
+        _lib.ensure_device(self.flat_p.device)
+        with torch.cuda.device(self.flat_p.device):
+            check(lib.nb_adam_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq), self._n,
+                                   float(g0["lr"]), float(b1), float(b2), float(g0["eps"]), int(self._step),
+                                   float(self.grad_scale), stream_ptr()), "nb_adam_step")
+        # the kernel wrote the parameters through raw pointers: bump their autograd version
+        # counters (no kernel launch) so that caches keyed on p._version (packed bf16 weights,
+        # _ops.packed_weights) see the update
+        try:
+            torch.autograd.graph.increment_version(self._params)
+        except TypeError:
+            for p in self._params:
+                torch.autograd.graph.increment_version(p)
+        return loss
+
+    # ---- torch.optim.Adam-compatible (de)serialisation -------------------------------------
+    def state_dict(self):
+        state = {}
+        for i, (p, o) in enumerate(zip(self._params, self._offsets)):
+            n = p.numel()
+            state[i] = {"step": torch.tensor(float(self._step)),
+                        "exp_avg": self.exp_avg[o:o + n].view(p.shape).clone(),
+                        "exp_avg_sq": self.exp_avg_sq[o:o + n].view(p.shape).clone()}
+        groups, k = [], 0
+        for g in self.param_groups:
+            d = {key: val for key, val in g.items() if key != "params"}
+            d["params"] = list(range(k, k + len(g["params"])))
+            k += len(g["params"])
+            groups.append(d)
+        return {"state": state if self._step > 0 else {}, "param_groups": groups}
+
+    def load_state_dict(self, sd):
+        for g, saved in zip(self.param_groups, sd["param_groups"]):
+            for key, val in saved.items():
+                if key != "params":
+                    g[key] = val
+        st = sd.get("state", {})
+        steps = []
+        with torch.no_grad():
+            for i, (p, o) in enumerate(zip(self._params, self._offsets)):
+                s = st.get(i, st.get(str(i)))
+                if s is None:
+                    continue
+                n = p.numel()
+                self.exp_avg[o:o + n].copy_(torch.as_tensor(s["exp_avg"]).reshape(-1).to(self.exp_avg.device))
+                self.exp_avg_sq[o:o + n].copy_(torch.as_tensor(s["exp_avg_sq"]).reshape(-1).to(self.exp_avg.device))
+                steps.append(int(float(s["step"])))
+        self._step = max(steps) if steps else 0

@@ -113,8 +113,17 @@ def get_renderer(args, bds_dict):
 
 
 def get_optimizer(coarse_model, fine_model, args):
+    """Adam(lr=args.lrate, betas=(0.9, 0.999)) over both models (utils.py:163-172) as one flat fused
+    sm_100a kernel; falls back to nothing: parameters must live on the GPU."""
+    from . import optim
     params = list(coarse_model.parameters()) + (list(fine_model.parameters()) if fine_model is not None else [])
-    return torch.optim.Adam(params=params, lr=args.lrate, betas=(0.9, 0.999))
+    opt = optim.FlatAdam(params, lr=args.lrate, betas=(0.9, 0.999))
+    for m in (coarse_model, fine_model):
+        if m is not None and getattr(m, "use_viewdirs", False):
+            offs = [opt.grad_offset(p) for p in _ops.mlp_params(m)]
+            if all(o is not None for o in offs):
+                m.__dict__["_nb_grad_target"] = (opt.flat_g, offs)
+    return opt
 
 
 # ----------------------------------------------------------------------------- checkpoints (utils.py:174-214,444-456)

@@ -33,6 +33,22 @@ def test_umma_selftest(K):
     assert err <= 1e-3, err
 
 
+@pytest.mark.parametrize("K", [64, 128])
+def test_umma_mn_major_selftest(K):
+    """the wgrad operand mode: D = A^T B with both operands MN-major (reduction over rows)"""
+    from nerf_shared_b200 import _ops
+    g = torch.Generator().manual_seed(K + 1)
+    A, B = torch.randn(K, 128, generator=g), torch.randn(K, 128, generator=g)
+    D = _ops.debug_umma_mn(A.cuda(), B.cuda()).cpu()
+    ref = A.bfloat16().float().t() @ B.bfloat16().float()
+    err = (D - ref).abs().max().item()
+    if err > 1e-3:
+        ok = ((D - ref).abs() < 1e-3)
+        print("rows ok:", ok.all(1).nonzero().flatten().tolist()[:32], "cols ok:", ok.all(0).nonzero().flatten().tolist()[:32])
+        print("D[0,:8]", D[0, :8].tolist(), "ref", ref[0, :8].tolist(), "D^T?", float((D.t() - ref).abs().max()))
+    assert err <= 1e-3, err
+
+
 def test_fp32_kernel_vs_golden(golden):
     m = make_model(11, precision="fp32")
     raw = m(cuda(golden["mlp/pts"]), cuda(golden["mlp/viewdirs"]))
@@ -69,9 +85,13 @@ def test_tc_layers_vs_bf16_oracle():
     flat = pts.reshape(-1, 3)
     dirs = vd[:, None].expand(pts.shape).reshape(-1, 3)
     ref = O.mlp(p, O.positional_encoding(flat, 10), O.positional_encoding(dirs, 4), bf16=True, acts=ref_acts)
-    acts = acts.float().cpu()
+    acts = _ops.untile(acts, _ops.ACT_SLABS, flat.shape[0]).float().cpu()
     names = ["h%d" % i for i in range(8)] + ["feature", "hv"]
     offs = [i * 256 for i in range(8)] + [2048, 2304]
+    enc = torch.cat([O.positional_encoding(flat, 10), torch.zeros(flat.shape[0], 1)], -1)
+    assert (acts[:, 2432:2496] - enc.bfloat16().float()).abs().max() < 1.6e-2     # enc(pts) slab, 1 bf16 ulp at |x|<4
+    encd = O.positional_encoding(dirs, 4).bfloat16().float()
+    assert (acts[:, 2496:2523] - encd).abs().max() < 8e-3 and acts[:, 2523:2560].abs().max() == 0
     report = []
     for nm, off, r in zip(names, offs, ref_acts):
         got = acts[:, off:off + r.shape[1]]

