@@ -27,9 +27,9 @@ def nerf_mlp_backward(ctx, g_raw):
         raise NotImplementedError("gradients wrt sample positions / view directions (pose estimation path) are not "
                                   "implemented yet in libnerf_b200")
     params = _ops.mlp_params(model)
-    need_w = any(ctx.needs_input_grad[4:])
+    need_w = any(ctx.needs_input_grad[5:])
     if not need_w:
-        return (None, None, None, None) + (None,) * len(params)
+        return (None, None, None, None, None) + (None,) * len(params)
     dev = pts.device
     # a FlatAdam optimizer registers its flat gradient buffer on the model: the wgrad kernels then
     # accumulate in place (every p.grad is a view of that buffer) and autograd gets no tensors
@@ -49,7 +49,7 @@ def nerf_mlp_backward(ctx, g_raw):
                                 ptr(dA), off_arr, ptr(grads), stream_ptr()), "nb_mlp_bwd_tc")
     out = []
     for i, p in enumerate(params):
-        use = ctx.needs_input_grad[4 + i] and not in_place
+        use = ctx.needs_input_grad[5 + i] and not in_place
         out.append(grads[offs[i]:offs[i] + p.numel()].view_as(p) if use else None)
     ctx.model._nb_last_dA = dA if getattr(ctx.model, "_nb_keep_dA", False) else None
-    return (None, None, None, None) + tuple(out)
+    return (None, None, None, None, None) + tuple(out)

@@ -322,8 +322,9 @@ class NerfMLP(torch.autograd.Function):
     """NeRF.forward (nerf.py:96-134): pts [M,3], viewdirs [M/S,3] -> raw [M,4]."""
 
     @staticmethod
-    def forward(ctx, pts, viewdirs, S, model, *params):
-        need_grad = any(ctx.needs_input_grad)
+    def forward(ctx, pts, viewdirs, S, model, track, *params):
+        # `track` = torch.is_grad_enabled() at the call site (grad mode is always off in here)
+        need_grad = bool(track) and any(ctx.needs_input_grad)
         if model.precision == "fp32":
             # inference / parity path: exact fp32 operands, no backward kernels
             raw = mlp_forward_f32(model, pts, viewdirs, S)

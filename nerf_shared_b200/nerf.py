@@ -105,7 +105,7 @@ class NeRF(nn.Module):
         if pts.shape[0] % max(n_rays, 1) != 0:
             raise ValueError("inputs %s do not broadcast against viewdirs %s" % (tuple(inputs.shape), tuple(viewdirs.shape)))
         S = pts.shape[0] // max(n_rays, 1)
-        raw = _ops.NerfMLP.apply(pts, viewdirs.reshape(-1, 3), S, self, *_ops.mlp_params(self))
+        raw = _ops.NerfMLP.apply(pts, viewdirs.reshape(-1, 3), S, self, torch.is_grad_enabled(), *_ops.mlp_params(self))
         return raw.reshape(list(inputs.shape[:-1]) + [4])
 
     def MLP(self, x):

@@ -126,8 +126,13 @@ def test_mlp_grads_vs_fp32_autograd(n_rays, S):
     # bf16 operands round every layer's activation and pre-activation gradient (2^-9 relative);
     # the error compounds with depth, so the bound is per layer: heads tight, layer 0 loosest
     for k, (rel, cos) in report.items():
-        head = k.split(".")[0] in ("rgb_linear", "alpha_linear", "views_linears", "feature_linear")
-        assert rel < (0.03 if head else 0.2) and cos > (0.999 if head else 0.98), (k, rel, cos, report)
+        # what dominates is not rounding of values but relu-mask flips: a pre-activation within the
+        # forward's bf16 error of zero flips its relu' (fraction f of elements -> relative L2 error
+        # sqrt(f)); measured profile: heads <1 %, feature/views 1-5 %, trunk 7-14 %, cosine > 0.99
+        grp = k.split(".")[0]
+        lim = {"rgb_linear": (0.01, 0.9999), "alpha_linear": (0.02, 0.9995), "views_linears": (0.08, 0.995),
+               "feature_linear": (0.08, 0.995)}.get(grp, (0.2, 0.985))
+        assert rel < lim[0] and cos > lim[1], (k, rel, cos, report)
 
 
 def test_training_step_golden(golden):
@@ -157,7 +162,10 @@ def test_training_step_golden(golden):
         for nm, key in (("alpha_linear.weight", "g_alpha_w"), ("rgb_linear.weight", "g_rgb_w"), ("pts_linears.0.weight", "g_l0_w")):
             g = dict(m.named_parameters())[nm].grad.cpu()
             e = T(golden["train/%s/%s" % (tag, key)])
-            assert float((g - e).norm() / e.norm()) < (0.2 if nm.startswith("pts") else 0.03), (tag, nm)
+            if float(e.norm()) == 0.0:      # e.g. fine sigma head at random init: relu(sigma) == 0 everywhere
+                assert float(g.norm()) == 0.0, (tag, nm)
+            else:
+                assert float((g - e).norm() / e.norm()) < (0.2 if nm.startswith("pts") else 0.03), (tag, nm)
     opt.step()
     for tag, m in (("coarse", mc), ("fine", mf)):
         # Adam's first step moves every weight by ~lr * sign(g): compare where |g| is not tiny
