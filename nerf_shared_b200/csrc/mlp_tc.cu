@@ -21,6 +21,7 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "mlp_common.cuh"
+#include "tmap.cuh"
 
 namespace nb {
 
@@ -206,15 +207,13 @@ __device__ __forceinline__ void encode3(float v0, float v1, float v2, float (&e)
 }
 
 template <int N>
-__device__ __forceinline__ void store_operand_row(uint32_t slab, int row, const float (&e)[N],
-                                                  uint8_t* __restrict__ save_slab) {
+__device__ __forceinline__ void store_operand_row(uint32_t slab, int row, const float (&e)[N]) {
 #pragma unroll
   for (int g = 0; g < N / 8; ++g) {
     const uint32_t p0 = pack_bf16x2(e[8 * g], e[8 * g + 1]), p1 = pack_bf16x2(e[8 * g + 2], e[8 * g + 3]),
                    p2 = pack_bf16x2(e[8 * g + 4], e[8 * g + 5]), p3 = pack_bf16x2(e[8 * g + 6], e[8 * g + 7]);
     const uint32_t off = sw128_chunk_off(row, g);
     st_shared_v4(slab + off, p0, p1, p2, p3);
-    if (save_slab) *reinterpret_cast<uint4*>(save_slab + off) = make_uint4(p0, p1, p2, p3);
   }
 }
 
@@ -225,7 +224,7 @@ __device__ __forceinline__ void store_operand_row(uint32_t slab, int row, const 
 template <int MODE>
 __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __restrict__ bias,
                                                 const float* __restrict__ alpha_w, uint32_t act, int row,
-                                                float& sigma, uint8_t* __restrict__ save) {
+                                                float& sigma) {
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
     uint32_t v[32];
@@ -262,14 +261,13 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
       }
       const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g);
       st_shared_v4(act + off, p0, p1, p2, p3);
-      if (save) *reinterpret_cast<uint4*>(save + off) = make_uint4(p0, p1, p2, p3);
     }
   }
 }
 
 // view branch: hv = relu(acc + b) (128 wide), rgb = hv . Wrgb^T + b_rgb in fp32 (nerf.py:125-129)
 __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __restrict__ cst, float& r, float& g_,
-                                               float& b_, int row, uint8_t* __restrict__ save) {
+                                               float& b_, int row, uint32_t act, bool save) {
   const float* bias = cst + kOffViewB;
   const float* wr = cst + kOffRgbW;
   r = cst[kOffRgbB]; g_ = cst[kOffRgbB + 1]; b_ = cst[kOffRgbB + 2];
@@ -297,21 +295,32 @@ __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __re
         b_ = fmaf(f[j], w2.x, b_); b_ = fmaf(f[j + 1], w2.y, b_); b_ = fmaf(f[j + 2], w2.z, b_); b_ = fmaf(f[j + 3], w2.w, b_);
       }
       if (save)
-        *reinterpret_cast<uint4*>(save + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g)) =
-            make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+        st_shared_v4(act + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g), pack_bf16x2(f[0], f[1]),
+                     pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
     }
   }
 }
 
 // ------------------------------------------------------------------------------------------
-// the fused forward kernel
+// the fused forward kernel (CTA pairs, tcgen05 cta_group::2)
 // ------------------------------------------------------------------------------------------
+// Two CTAs of a cluster work as one MMA unit: M = 256 samples (128 per CTA), N = 256 output
+// features, each CTA holding its own 128 activation rows and HALF of every weight slab (the
+// leader the output features 0..127, the peer 128..255), so a 16 KB ring stage feeds twice the
+// MMA work of the single-CTA form and the L2 -> SMEM weight traffic per SM halves.  Each CTA
+// still ping-pongs two 128-sample tiles (x = 0/1) so that epilogues overlap the other tile's MMAs;
+// a cluster therefore works on a "quad" of four tiles per iteration.
+//
+// Barriers (same shared-memory offsets in both CTAs):
+//   full[s]   leader only: weight stage s landed in BOTH CTAs (TMA complete_tx from both + expect_tx)
+//   empty[s]  per CTA: the MMAs reading stage s retired (tcgen05.commit multicast to both CTAs)
+//   act[x]    leader only: tile x's A operand is written in both CTAs (8 warp arrivals, 4 remote)
+//   acc[x]    per CTA: tile x's accumulator is complete (tcgen05.commit multicast)
 template <int L_PTS, int L_DIRS>
-__global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __restrict__ blob,
-                                                            const float* __restrict__ pts,
-                                                            const float* __restrict__ viewdirs, int64_t M, int S,
-                                                            float* __restrict__ raw, uint8_t* __restrict__ acts,
-                                                            int num_pairs) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
+    mlp_fwd_tc_kernel(const __grid_constant__ CUtensorMap wmap, const uint8_t* __restrict__ blob,
+                      const float* __restrict__ pts, const float* __restrict__ viewdirs, int64_t M, int S,
+                      float* __restrict__ raw, uint8_t* __restrict__ acts, int num_quads) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
@@ -319,43 +328,51 @@ __global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __res
   const uint32_t bar_full = base + kSmBar, bar_empty = bar_full + 8 * kStages, bar_act = bar_empty + 8 * kStages,
                  bar_acc = bar_act + 16, bar_const = bar_acc + 16;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int cluster = (int)cluster_id_x(), num_clusters = (int)cluster_count_x();
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kStages; ++i) {
-      mbar_init(bar_full + 8 * i, 1);
-      mbar_init(bar_empty + 8 * i, 1);
+      mbar_init(bar_full + 8 * i, 1);   // leader producer's arrive.expect_tx
+      mbar_init(bar_empty + 8 * i, 1);  // tcgen05.commit
     }
     for (int x = 0; x < 2; ++x) {
-      mbar_init(bar_act + 8 * x, kTileM);  // every epilogue thread of the tile arrives
-      mbar_init(bar_acc + 8 * x, 1);       // tcgen05.commit
+      mbar_init(bar_act + 8 * x, 8);    // one arrival per epilogue warp of the tile, both CTAs
+      mbar_init(bar_acc + 8 * x, 1);    // tcgen05.commit
     }
     mbar_init(bar_const, 1);
     fence_mbar_init();
   }
   if (warp == 2) {
-    tmem_alloc(base + kSmTmemPtr, 512);
-    tmem_relinquish();
+    tmem_alloc_2sm(base + kSmTmemPtr, 512);
+    tmem_relinquish_2sm();
   }
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&wmap);
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();  // barriers of both CTAs initialised before any remote arrive / TMA signal
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kSmTmemPtr);
 
   if (warp == 0) {
-    // ---------------- weight producer ----------------
+    // ---------------- weight producer: this CTA's half of every slab ----------------
     if (lane == 0) {
       mbar_expect_tx(bar_const, kConstFloats * 4);
       bulk_g2s(base + kSmConst, blob + (size_t)kNumSlabs * kSlabBytes, kConstFloats * 4, bar_const);
       uint32_t stage = 0, phase = 0;
-      for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+      for (int quad = cluster; quad < num_quads; quad += num_clusters) {
         for (int layer = 0; layer < 10; ++layer) {
-          const int n = ks_count(layer) * nh_count(layer), sb = slab_base(layer);
+          const int nks = ks_count(layer), sb = slab_base(layer);
+          const uint32_t half_bytes = layer == 9 ? 8192u : 16384u;
           for (int x = 0; x < 2; ++x) {
-            for (int i = 0; i < n; ++i) {
-              mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-              mbar_expect_tx(bar_full + 8 * stage, kSlabBytes);
-              bulk_g2s(base + kSmRing + stage * kSlabBytes, blob + (size_t)(sb + i) * kSlabBytes, kSlabBytes,
-                       bar_full + 8 * stage);
+            for (int ks = 0; ks < nks; ++ks) {
+              mbar_wait_cluster(bar_empty + 8 * stage, phase ^ 1);
+              if (rank == 0) mbar_expect_tx(bar_full + 8 * stage, 2 * half_bytes);
+              const uint32_t full_leader = mapa(bar_full + 8 * stage, 0);
+              const uint32_t dst = base + kSmRing + stage * kSlabBytes;
+              // layers 0..8: slab (ks, nh = rank), 128 rows; layer 9 (N = 128): rows 64*rank.. of slab ks
+              const int row0 = layer == 9 ? (sb + ks) * 128 + 64 * (int)rank : (sb + ks * 2 + (int)rank) * 128;
+              tma_load_2d_2sm(dst, &wmap, 0, row0, full_leader);
+              if (layer != 9) tma_load_2d_2sm(dst + 8192, &wmap, 0, row0 + 64, full_leader);
               if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
           }
@@ -363,17 +380,18 @@ __global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __res
       }
     }
   } else if (warp == 1) {
-    // ---------------- MMA issuer ----------------
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(128, 128);
+    // ---------------- MMA issuer (leader CTA only) ----------------
+    if (lane == 0 && rank == 0) {
+      const uint32_t idesc256 = make_idesc_bf16(256, 256), idesc128 = make_idesc_bf16(256, 128);
       uint32_t stage = 0, phase = 0, par_act0 = 0, par_act1 = 0;
-      for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+      for (int quad = cluster; quad < num_quads; quad += num_clusters) {
         for (int layer = 0; layer < 10; ++layer) {
-          const int nks = ks_count(layer), nnh = nh_count(layer);
+          const int nks = ks_count(layer);
+          const uint32_t idesc = layer == 9 ? idesc128 : idesc256;
           for (int x = 0; x < 2; ++x) {
             const uint32_t sAct = base + (x ? kSmAct1 : kSmAct0), sEnc = base + (x ? kSmEnc1 : kSmEnc0);
-            if (x == 0) { mbar_wait(bar_act, par_act0); par_act0 ^= 1; }
-            else { mbar_wait(bar_act + 8, par_act1); par_act1 ^= 1; }
+            if (x == 0) { mbar_wait_cluster(bar_act, par_act0); par_act0 ^= 1; }
+            else { mbar_wait_cluster(bar_act + 8, par_act1); par_act1 ^= 1; }
             tc_fence_after();
             const uint32_t d = tmem + x * 256;
             for (int ks = 0; ks < nks; ++ks) {
@@ -384,17 +402,15 @@ __global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __res
               else a_addr = sAct + ks * kSlabBytes;
               const int nk16 = (layer == 9 && ks == 4) ? 2 : 4;
               const uint64_t adesc = make_desc_kmajor_sw128(a_addr);
-              for (int nh = 0; nh < nnh; ++nh) {
-                mbar_wait(bar_full + 8 * stage, phase);
-                tc_fence_after();
-                const uint64_t bdesc = make_desc_kmajor_sw128(base + kSmRing + stage * kSlabBytes);
-                for (int k16 = 0; k16 < nk16; ++k16)
-                  umma_bf16(d + nh * 128, adesc + 2 * k16, bdesc + 2 * k16, idesc, (ks | k16) != 0);
-                umma_commit(bar_empty + 8 * stage);  // slab is free once these MMAs retire
-                if (++stage == kStages) { stage = 0; phase ^= 1; }
-              }
+              mbar_wait_cluster(bar_full + 8 * stage, phase);
+              tc_fence_after();
+              const uint64_t bdesc = make_desc_kmajor_sw128(base + kSmRing + stage * kSlabBytes);
+              for (int k16 = 0; k16 < nk16; ++k16)
+                umma_bf16_2sm(d, adesc + 2 * k16, bdesc + 2 * k16, idesc, (ks | k16) != 0);
+              umma_commit_2sm(bar_empty + 8 * stage);  // frees the stage in both CTAs
+              if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
-            umma_commit(bar_acc + 8 * x);  // accumulator of (tile x, layer) complete
+            umma_commit_2sm(bar_acc + 8 * x);  // accumulator of (tile x, layer) complete in both CTAs
           }
         }
       }
@@ -405,35 +421,54 @@ __global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __res
     const int row = ((warp & 3) << 5) | lane;
     const uint32_t sAct = base + (x ? kSmAct1 : kSmAct0), sEnc = base + (x ? kSmEnc1 : kSmEnc0);
     const uint32_t taddr = tmem + x * 256 + ((uint32_t)((warp & 3) * 32) << 16);
-    const uint32_t my_act = bar_act + 8 * x, my_acc = bar_acc + 8 * x;
+    const uint32_t act_leader = mapa(bar_act + 8 * x, 0), my_acc = bar_acc + 8 * x;
     uint32_t par_acc = 0;
     mbar_wait(bar_const, 0);
-    for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
-      const int64_t tile = (int64_t)pair * 2 + x;
+    for (int quad = cluster; quad < num_quads; quad += num_clusters) {
+      const int64_t tile = (int64_t)quad * 4 + rank * 2 + x;
       const int64_t m = tile * kTileM + row;
       const bool valid = m < M;
-      // whole tiles are saved (rows past M hold finite values computed from zero inputs)
+      // whole tiles are saved (rows past M hold finite values computed from zero inputs).  The SMEM
+      // operand image IS the saved image, so every warp streams its own 32 rows (4 KB of each slab)
+      // to HBM with bulk async stores; `flush` follows the fence that publishes the rows to the MMA.
       uint8_t* save = (acts && tile * kTileM < M) ? acts + (size_t)tile * kActSlabs * kSlabBytes : nullptr;
+      const uint32_t wrow = (uint32_t)(warp & 3) * 4096u;
+      auto flush = [&](uint32_t src_slab0, int dst_slab0, int nslabs) {
+        if (save && lane == 0) {
+          for (int j = 0; j < nslabs; ++j)
+            bulk_s2g(save + (size_t)(dst_slab0 + j) * kSlabBytes + wrow, src_slab0 + j * kSlabBytes + wrow, 4096);
+          bulk_commit();
+        }
+      };
+      auto reuse = [&]() {  // before overwriting SMEM that earlier bulk stores may still be reading
+        if (save) {
+          if (lane == 0) bulk_wait_read_all();
+          __syncwarp();
+        }
+      };
+      reuse();
       {
         float p0 = 0.f, p1 = 0.f, p2 = 0.f;
         if (valid) { p0 = pts[m * 3]; p1 = pts[m * 3 + 1]; p2 = pts[m * 3 + 2]; }
         float e[64];
         encode3<L_PTS>(p0, p1, p2, e);
-        store_operand_row(sEnc, row, e, save ? save + kActSlabEncP * kSlabBytes : nullptr);
+        store_operand_row(sEnc, row, e);
       }
       fence_proxy_async();
-      mbar_arrive(my_act);
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(act_leader);
+      flush(sEnc, kActSlabEncP, 1);
       float sigma = cst[kOffAlphaB];
 #pragma unroll 1
       for (int layer = 0; layer < 9; ++layer) {
-        mbar_wait(my_acc, par_acc);
+        mbar_wait_cluster(my_acc, par_acc);
         par_acc ^= 1;
         tc_fence_after();
-        uint8_t* sv = save ? save + (size_t)layer * 4 * kSlabBytes : nullptr;
-        if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, sigma, sv);
-        else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, sigma, sv);
+        reuse();
+        if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, sigma);
+        else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, sigma);
         else {
-          epilogue_hidden<2>(taddr, cst + kOffFeatB, nullptr, sAct, row, sigma, sv);
+          epilogue_hidden<2>(taddr, cst + kOffFeatB, nullptr, sAct, row, sigma);
           // view-direction encoding replaces the position encoding in the auxiliary slab
           // (its last reader, layer 5's MMA, retired before layer 5's accumulator was signalled)
           float v0 = 0.f, v1 = 0.f, v2 = 0.f;
@@ -443,23 +478,36 @@ __global__ void __launch_bounds__(384, 1) mlp_fwd_tc_kernel(const uint8_t* __res
           }
           float e[64];   // columns 32..63 are zero: the wgrad kernel reads the whole 64-wide slab
           encode3<L_DIRS>(v0, v1, v2, e);
-          store_operand_row(sEnc, row, e, save ? save + kActSlabEncD * kSlabBytes : nullptr);
+          store_operand_row(sEnc, row, e);
         }
         fence_proxy_async();
         tc_fence_before();
-        mbar_arrive(my_act);
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(act_leader);
+        flush(sAct, layer * 4, 4);
+        if (layer == 8) flush(sEnc, kActSlabEncD, 1);
       }
-      mbar_wait(my_acc, par_acc);
+      mbar_wait_cluster(my_acc, par_acc);
       par_acc ^= 1;
       tc_fence_after();
+      reuse();
       float r, g, b;
-      epilogue_views(taddr, cst, r, g, b, row, save ? save + (size_t)kActSlabHv * kSlabBytes : nullptr);
+      // the view-branch hidden layer is staged in the (now idle) activation buffer only to be saved
+      epilogue_views(taddr, cst, r, g, b, row, sAct, save != nullptr);
       if (valid) *reinterpret_cast<float4*>(raw + m * 4) = make_float4(r, g, b, sigma);
       tc_fence_before();
+      if (save) {
+        fence_proxy_async();
+        __syncwarp();
+        flush(sAct, kActSlabHv, 2);
+      }
     }
+    if (acts && lane == 0) bulk_wait_all();
   }
-  __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem, 512);
+  // no CTA may exit (or free TMEM) while its peer can still signal its barriers or read its SMEM
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) tmem_dealloc_2sm(tmem, 512);
 }
 
 static int build_pack_args(const NbMlpWeights* w, PackArgs& a) {
@@ -534,11 +582,14 @@ int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, c
     return NB_E_UNSUPPORTED;
   }
   const int64_t tiles = (M + kTileM - 1) / kTileM;
-  const int64_t pairs = (tiles + 1) / 2;
-  NB_REQUIRE(pairs < (1ll << 30), "nb_mlp_fwd_tc: M too large for one launch");
-  const int grid = (int)(pairs < kNumSMs ? pairs : kNumSMs);
-  mlp_fwd_tc_kernel<10, 4><<<grid, 384, kSmemBytes, as_stream(stream)>>>(
-      (const uint8_t*)packed, pts, viewdirs, M, S, raw, (uint8_t*)acts, (int)pairs);
+  const int64_t quads = (tiles + 3) / 4;  // a CTA pair works on four 128-sample tiles at a time
+  NB_REQUIRE(quads < (1ll << 30), "nb_mlp_fwd_tc: M too large for one launch");
+  CUtensorMap wmap;
+  int rc = make_slab_tmap(&wmap, packed, kNumSlabs);
+  if (rc) return rc;
+  const int clusters = (int)(quads < kNumSMs / 2 ? quads : kNumSMs / 2);
+  mlp_fwd_tc_kernel<10, 4><<<2 * clusters, 384, kSmemBytes, as_stream(stream)>>>(
+      wmap, (const uint8_t*)packed, pts, viewdirs, M, S, raw, (uint8_t*)acts, (int)quads);
   return check_launch("nb_mlp_fwd_tc");
 }
 
