@@ -25,6 +25,7 @@ import torch
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+_real_stdout = sys.stdout
 FLOP_FWD = 1186816        # per sample, SURVEY.md section 8d
 FLOP_TRAIN = 3489024      # fwd + wgrad + needed dgrad per sample
 H = W = 400
@@ -147,7 +148,11 @@ def run_b200(a):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def train_step(batch_rays, target):
+    from nerf_shared_b200 import train
+    step = train.GraphedTrainStep(renderer, coarse, fine, opt, H, W, K, a.rays, chunk=args.chunk)
+
+    def eager_step(batch_rays, target):
+        """main.py:77-104 call by call (what the unmodified main.py executes)."""
         rgb, _, _, extras = renderer.render_from_rays(H, W, K, chunk=args.chunk, rays=batch_rays, coarse_model=coarse,
                                                       fine_model=fine, retraw=True)
         opt.zero_grad()
@@ -168,20 +173,19 @@ def run_b200(a):
         pool.append((torch.stack([ro, rd], 0), tgt))
 
     for i in range(max(a.warmup, 3)):
-        train_step(*pool[i % n_pool])
+        step(*pool[i % n_pool])
     sync_all()
     sampler = ClockSampler(local)
     sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
-    l0 = _lib.launch_count()
     sync_all()
     for i in range(a.steps):
         flush.zero_()                        # L2 flush between timed iterations (outside the events)
         ev[i][0].record()
-        train_step(*pool[i % n_pool])
+        step(*pool[i % n_pool])
         ev[i][1].record()
     sync_all()
-    launches = _lib.launch_count() - l0
+    launches = step.launches_per_replay * a.steps
     clocks = sampler.stop()
     ms = sum(s.elapsed_time(e) for s, e in ev) / a.steps
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
@@ -191,29 +195,37 @@ def run_b200(a):
     value = world * a.rays / (ms_step * 1e-3)
 
     # ---- end to end through the public API (e2e) -----------------------------------------------
-    def e2e_step(i):
+    # host images (pinned) -> utils.sample_random_ray_batch (pixel ids + targets H2D) -> graphed step ->
+    # loss.item() (D2H) every step
+    def e2e_step(i, fn):
         batch_rays, target, _, _ = utils.sample_random_ray_batch(args, images_pinned, poses_d, None, a.rays, False, None,
                                                                  i_train, hwf, K, 0, i + 1)
-        return float(train_step(batch_rays, target).item())
+        out = fn(batch_rays, target)
+        return float((out[0] if isinstance(out, tuple) else out).item())
 
-    for i in range(3):
-        e2e_step(i)
-    sync_all()
-    t0 = time.perf_counter()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(a.steps):
-        e2e_step(i)
-    e1.record()
-    sync_all()
-    e2e_ms = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / a.steps
-    t = torch.tensor([e2e_ms], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_ms = float(t.item())
+    def time_e2e(fn):
+        for i in range(3):
+            e2e_step(i, fn)
+        sync_all()
+        t0 = time.perf_counter()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(a.steps):
+            e2e_step(i, fn)
+        e1.record()
+        sync_all()
+        ms = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / a.steps
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    e2e_ms = time_e2e(step)
+    eager_ms = time_e2e(eager_step)
     h2d = a.rays * 8 + a.rays * 3 * 4      # int64 pixel ids + fp32 targets per step
     e2e = {"value": world * a.rays / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-           "ms_per_step": e2e_ms}
+           "ms_per_step": e2e_ms, "api": "utils.sample_random_ray_batch -> train.GraphedTrainStep -> loss.item()",
+           "eager_main_py_loop": {"value": world * a.rays / (eager_ms * 1e-3), "ms_per_step": eager_ms}}
 
     out = {"metric": "train_rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": a.steps,
            "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -221,7 +233,8 @@ def run_b200(a):
            "config": {"workload": "lego-shaped synthetic Blender training step (BASELINE.json configs[1]): N_rand=%d rays/GPU, "
                                   "64 coarse + 128 fine samples, D8 W256 coarse+fine fwd/bwd + Adam" % a.rays,
                       "global_rays_per_step": world * a.rays, "parallelism": "dp%d (ray-sharded, flat-gradient all-reduce)" % world,
-                      "l2": "256 MiB flush between timed iterations", "timing": "CUDA events per step, max over ranks"},
+                      "l2": "256 MiB flush between timed iterations", "timing": "CUDA events per step, max over ranks",
+                      "launch": "one CUDA graph per step (train.GraphedTrainStep)"},
            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
 
     if rank == 0:
@@ -230,7 +243,7 @@ def run_b200(a):
             out["render"] = render_leg(renderer, coarse, fine, K, poses_d, dev)
         if not a.no_cpu_baseline:
             out["cpu_baseline"] = cpu_train_baseline(budget_s=15.0)
-        print(json.dumps(out))
+        print(json.dumps(out), file=_real_stdout, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -378,11 +391,13 @@ def run_reference(a):
                                   "timed on a bounded sample of %d rays per step" % n},
            "cpu_baseline": {"kind": "port", "cores": torch.get_num_threads(), "sample": sample, "value": v, "unit": "rays/s"},
            "e2e": {"value": v, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out))
+    print(json.dumps(out), file=_real_stdout, flush=True)
 
 
 if __name__ == "__main__":
     a = parse()
+    _real_stdout = sys.stdout
+    sys.stdout = sys.stderr          # the library prints its configuration; stdout carries ONE JSON line
     if a.impl == "reference":
         run_reference(a)
     else:

@@ -167,6 +167,14 @@ NB_API int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const vo
 NB_API int nb_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                  float eps, int step, float grad_scale, void* stream);
 
+/* CUDA-graph form of the same update: nb_adam_hyper (outside the graph, once per step) writes the
+ * step's scalars -- lr/bias_correction1, beta1, beta2, eps, 1/sqrt(bias_correction2), grad_scale --
+ * into `hyper` (8 device floats); nb_adam_step_dev (inside the graph) reads them from there.
+ * replaces: Adam.step + the per-iteration lr write main.py:104-112. */
+NB_API int nb_adam_hyper(float* hyper, float lr, float beta1, float beta2, float eps, int step, float grad_scale,
+                         void* stream);
+NB_API int nb_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, const float* hyper, void* stream);
+
 /* ---- self test ------------------------------------------------------------------------- */
 /* D[128,128] = A[128,K] * B[128,K]^T (bf16-rounded operands, fp32 accumulate) through the same
  * swizzle / descriptor / tcgen05 sequence as nb_mlp_fwd_tc; K in {64,128,192,256}. */

@@ -242,25 +242,37 @@ class Composite(torch.autograd.Function):
 
 
 # ------------------------------------------------------------------------------------------ MLP
+def mlp_params(model):
+    """The 24 parameters in the C ABI's order (cached on the module: ModuleList indexing is slow)."""
+    cached = model.__dict__.get("_nb_params")
+    if cached is not None and cached[0] is model.pts_linears[0].weight and cached[-1] is model.rgb_linear.bias:
+        return cached
+    pl = list(model.pts_linears)
+    ps = ([l.weight for l in pl] + [l.bias for l in pl] +
+          [model.feature_linear.weight, model.feature_linear.bias, model.alpha_linear.weight,
+           model.alpha_linear.bias, model.views_linears[0].weight, model.views_linears[0].bias,
+           model.rgb_linear.weight, model.rgb_linear.bias])
+    model.__dict__["_nb_params"] = ps
+    return ps
+
+
 def mlp_weight_struct(model) -> _lib.NbMlpWeights:
-    """Fill NbMlpWeights from a nerf.NeRF module's fp32 parameters (no copies)."""
+    """Fill NbMlpWeights from a nerf.NeRF module's fp32 parameters (no copies); cached per set of
+    parameter storages."""
+    ps = mlp_params(model)
+    key = tuple(p.data_ptr() for p in ps)
+    cached = model.__dict__.get("_nb_wstruct")
+    if cached is not None and cached[0] == key:
+        return cached[1]
     w = _lib.NbMlpWeights()
     for i in range(8):
-        w.pts_w[i] = model.pts_linears[i].weight.data_ptr()
-        w.pts_b[i] = model.pts_linears[i].bias.data_ptr()
-    w.feature_w, w.feature_b = model.feature_linear.weight.data_ptr(), model.feature_linear.bias.data_ptr()
-    w.alpha_w, w.alpha_b = model.alpha_linear.weight.data_ptr(), model.alpha_linear.bias.data_ptr()
-    w.views_w, w.views_b = model.views_linears[0].weight.data_ptr(), model.views_linears[0].bias.data_ptr()
-    w.rgb_w, w.rgb_b = model.rgb_linear.weight.data_ptr(), model.rgb_linear.bias.data_ptr()
+        w.pts_w[i] = key[i]
+        w.pts_b[i] = key[8 + i]
+    w.feature_w, w.feature_b, w.alpha_w, w.alpha_b = key[16], key[17], key[18], key[19]
+    w.views_w, w.views_b, w.rgb_w, w.rgb_b = key[20], key[21], key[22], key[23]
     w.L_pts, w.L_dirs = int(model.multires), int(model.multires_views)
+    model.__dict__["_nb_wstruct"] = (key, w)
     return w
-
-
-def mlp_params(model):
-    return ([model.pts_linears[i].weight for i in range(8)] + [model.pts_linears[i].bias for i in range(8)] +
-            [model.feature_linear.weight, model.feature_linear.bias, model.alpha_linear.weight,
-             model.alpha_linear.bias, model.views_linears[0].weight, model.views_linears[0].bias,
-             model.rgb_linear.weight, model.rgb_linear.bias])
 
 
 def packed_weights(model, backward: bool = False) -> torch.Tensor:

@@ -18,6 +18,7 @@
 #include "common.cuh"
 #include "mlp_common.cuh"
 #include "ptx.cuh"
+#include "tmap.cuh"
 
 namespace nb {
 
@@ -84,9 +85,9 @@ __device__ __forceinline__ uint32_t relu_mask2(uint32_t d, uint32_t h) {
 
 // MODE 0: plain copy (d_feature); 1: + d_sigma * alpha_w, masked by h7; 2: masked
 template <int MODE>
-__device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, bool write_smem, int row,
-                                               const uint8_t* __restrict__ mask_src, uint8_t* __restrict__ da_dst,
-                                               float d_sigma, const float* __restrict__ alpha_w) {
+__device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, int row,
+                                               const uint8_t* __restrict__ mask_src, float d_sigma,
+                                               const float* __restrict__ alpha_w) {
 #pragma unroll
   for (int c = 0; c < 8; ++c) {
     uint4 hm[4];
@@ -122,16 +123,18 @@ __device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, boo
         }
       }
       const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g);
-      if (write_smem) st_shared_v4(act + off, p0, p1, p2, p3);
-      if (da_dst) *reinterpret_cast<uint4*>(da_dst + off) = make_uint4(p0, p1, p2, p3);
+      st_shared_v4(act + off, p0, p1, p2, p3);
     }
   }
 }
 
-__global__ void __launch_bounds__(384, 1) mlp_dgrad_kernel(const uint8_t* __restrict__ blob,
-                                                           const uint8_t* __restrict__ acts,
-                                                           const float* __restrict__ d_raw, int64_t M,
-                                                           uint8_t* __restrict__ dA, int num_pairs) {
+// CTA-pair form (tcgen05 cta_group::2), same protocol as the forward kernel (mlp_tc.cu): M = 256
+// samples per MMA (128 per CTA), each CTA streams its half (128 of the 256 output columns) of every
+// transposed weight slab, a cluster works on a quad of four tiles per iteration.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
+    mlp_dgrad_kernel(const __grid_constant__ CUtensorMap wmap, const uint8_t* __restrict__ blob,
+                     const uint8_t* __restrict__ acts, const float* __restrict__ d_raw, int64_t M,
+                     uint8_t* __restrict__ dA, int num_quads) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
@@ -139,6 +142,8 @@ __global__ void __launch_bounds__(384, 1) mlp_dgrad_kernel(const uint8_t* __rest
   const uint32_t bar_full = base + kBSmBar, bar_empty = bar_full + 8 * kBwdStages, bar_act = bar_empty + 8 * kBwdStages,
                  bar_acc = bar_act + 16, bar_const = bar_acc + 16;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int cluster = (int)cluster_id_x(), num_clusters = (int)cluster_count_x();
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBwdStages; ++i) {
@@ -146,18 +151,19 @@ __global__ void __launch_bounds__(384, 1) mlp_dgrad_kernel(const uint8_t* __rest
       mbar_init(bar_empty + 8 * i, 1);
     }
     for (int x = 0; x < 2; ++x) {
-      mbar_init(bar_act + 8 * x, kTileM);
+      mbar_init(bar_act + 8 * x, 8);  // one arrival per epilogue warp of the tile, both CTAs
       mbar_init(bar_acc + 8 * x, 1);
     }
     mbar_init(bar_const, 1);
     fence_mbar_init();
   }
   if (warp == 2) {
-    tmem_alloc(base + kBSmTmemPtr, 512);
-    tmem_relinquish();
+    tmem_alloc_2sm(base + kBSmTmemPtr, 512);
+    tmem_relinquish_2sm();
   }
+  if (warp == 0 && lane == 0) tma_prefetch_desc(&wmap);
   tc_fence_before();
-  __syncthreads();
+  cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kBSmTmemPtr);
 
@@ -166,15 +172,18 @@ __global__ void __launch_bounds__(384, 1) mlp_dgrad_kernel(const uint8_t* __rest
       mbar_expect_tx(bar_const, kBwdConstFloats * 4);
       bulk_g2s(base + kBSmConst, blob + (size_t)kBwdSlabs * kSlabBytes, kBwdConstFloats * 4, bar_const);
       uint32_t stage = 0, phase = 0;
-      for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+      for (int quad = cluster; quad < num_quads; quad += num_clusters) {
         for (int step = 0; step < 9; ++step) {
-          const int n = bwd_ks_count(step) * 2, sb = bwd_slab_base(step);
+          const int nks = bwd_ks_count(step), sb = bwd_slab_base(step);
           for (int x = 0; x < 2; ++x) {
-            for (int i = 0; i < n; ++i) {
-              mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-              mbar_expect_tx(bar_full + 8 * stage, kSlabBytes);
-              bulk_g2s(base + kBSmRing + stage * kSlabBytes, blob + (size_t)(sb + i) * kSlabBytes, kSlabBytes,
-                       bar_full + 8 * stage);
+            for (int ks = 0; ks < nks; ++ks) {
+              mbar_wait_cluster(bar_empty + 8 * stage, phase ^ 1);
+              if (rank == 0) mbar_expect_tx(bar_full + 8 * stage, 2 * kSlabBytes);
+              const uint32_t full_leader = mapa(bar_full + 8 * stage, 0);
+              const uint32_t dst = base + kBSmRing + stage * kSlabBytes;
+              const int row0 = (sb + ks * 2 + (int)rank) * 128;  // this CTA's 128 output columns
+              tma_load_2d_2sm(dst, &wmap, 0, row0, full_leader);
+              tma_load_2d_2sm(dst + 8192, &wmap, 0, row0 + 64, full_leader);
               if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
             }
           }
@@ -182,31 +191,29 @@ __global__ void __launch_bounds__(384, 1) mlp_dgrad_kernel(const uint8_t* __rest
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_bf16(128, 128);
+    if (lane == 0 && rank == 0) {
+      const uint32_t idesc = make_idesc_bf16(256, 256);
       uint32_t stage = 0, phase = 0, par_act0 = 0, par_act1 = 0;
-      for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
+      for (int quad = cluster; quad < num_quads; quad += num_clusters) {
         for (int step = 0; step < 9; ++step) {
           const int nks = bwd_ks_count(step);
           for (int x = 0; x < 2; ++x) {
             const uint32_t sAct = base + (x ? kBSmAct1 : kBSmAct0);
-            if (x == 0) { mbar_wait(bar_act, par_act0); par_act0 ^= 1; }
-            else { mbar_wait(bar_act + 8, par_act1); par_act1 ^= 1; }
+            if (x == 0) { mbar_wait_cluster(bar_act, par_act0); par_act0 ^= 1; }
+            else { mbar_wait_cluster(bar_act + 8, par_act1); par_act1 ^= 1; }
             tc_fence_after();
             const uint32_t d = tmem + x * 256;
             for (int ks = 0; ks < nks; ++ks) {
               const uint64_t adesc = make_desc_kmajor_sw128(sAct + ks * kSlabBytes);
-              for (int nh = 0; nh < 2; ++nh) {
-                mbar_wait(bar_full + 8 * stage, phase);
-                tc_fence_after();
-                const uint64_t bdesc = make_desc_kmajor_sw128(base + kBSmRing + stage * kSlabBytes);
-                for (int k16 = 0; k16 < 4; ++k16)
-                  umma_bf16(d + nh * 128, adesc + 2 * k16, bdesc + 2 * k16, idesc, (ks | k16) != 0);
-                umma_commit(bar_empty + 8 * stage);
-                if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
-              }
+              mbar_wait_cluster(bar_full + 8 * stage, phase);
+              tc_fence_after();
+              const uint64_t bdesc = make_desc_kmajor_sw128(base + kBSmRing + stage * kSlabBytes);
+              for (int k16 = 0; k16 < 4; ++k16)
+                umma_bf16_2sm(d, adesc + 2 * k16, bdesc + 2 * k16, idesc, (ks | k16) != 0);
+              umma_commit_2sm(bar_empty + 8 * stage);
+              if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
             }
-            umma_commit(bar_acc + 8 * x);
+            umma_commit_2sm(bar_acc + 8 * x);
           }
         }
       }
@@ -216,19 +223,33 @@ __global__ void __launch_bounds__(384, 1) mlp_dgrad_kernel(const uint8_t* __rest
     const int row = ((warp & 3) << 5) | lane;
     const uint32_t sAct = base + (x ? kBSmAct1 : kBSmAct0);
     const uint32_t taddr = tmem + x * 256 + ((uint32_t)((warp & 3) * 32) << 16);
-    const uint32_t my_act = bar_act + 8 * x, my_acc = bar_acc + 8 * x;
+    const uint32_t act_leader = mapa(bar_act + 8 * x, 0), my_acc = bar_acc + 8 * x;
+    const uint32_t wrow = (uint32_t)(warp & 3) * 4096u;
     uint32_t par_acc = 0;
     mbar_wait(bar_const, 0);
     const float* wr = cst;
     const float* wa = cst + 384;
-    for (int pair = blockIdx.x; pair < num_pairs; pair += gridDim.x) {
-      const int64_t tile = (int64_t)pair * 2 + x;
+    for (int quad = cluster; quad < num_quads; quad += num_clusters) {
+      const int64_t tile = (int64_t)quad * 4 + rank * 2 + x;
       const int64_t m = tile * kTileM + row;
       const bool real = tile * kTileM < M;
       const uint8_t* at = real ? acts + (size_t)tile * kActSlabs * kSlabBytes : nullptr;
       uint8_t* dt = real ? dA + (size_t)tile * kDaSlabs * kSlabBytes : nullptr;
+      // every warp streams its own 32 rows (4 KB of each slab) of the freshly written dA tile to HBM
+      auto flush = [&](int dst_slab0, int nslabs) {
+        if (dt && lane == 0) {
+          for (int j = 0; j < nslabs; ++j)
+            bulk_s2g(dt + (size_t)(dst_slab0 + j) * kSlabBytes + wrow, sAct + j * kSlabBytes + wrow, 4096);
+          bulk_commit();
+        }
+      };
+      auto reuse = [&]() {
+        if (lane == 0) bulk_wait_read_all();
+        __syncwarp();
+      };
       float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
       if (m < M) g = *reinterpret_cast<const float4*>(d_raw + m * 4);
+      reuse();
       // prologue: d(view hidden) = (d_rgb . W_rgb) * relu'(hv)   (nerf.py:125-129 backwards)
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
@@ -248,38 +269,41 @@ __global__ void __launch_bounds__(384, 1) mlp_dgrad_kernel(const uint8_t* __rest
             p0 = p1 = p2 = p3 = 0u;
           }
           st_shared_v4(sAct + off, p0, p1, p2, p3);
-          if (dt) *reinterpret_cast<uint4*>(dt + (size_t)kDaSlabHv * kSlabBytes + off) = make_uint4(p0, p1, p2, p3);
         }
       }
       fence_proxy_async();
-      mbar_arrive(my_act);
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(act_leader);
+      flush(kDaSlabHv, 2);
 #pragma unroll 1
       for (int step = 0; step < 9; ++step) {
-        mbar_wait(my_acc, par_acc);
+        mbar_wait_cluster(my_acc, par_acc);
         par_acc ^= 1;
         tc_fence_after();
+        reuse();
+        int dst_slab;
         if (step == 0) {
-          dgrad_epilogue<0>(taddr, sAct, true, row, nullptr, dt ? dt + (size_t)kDaSlabFeat * kSlabBytes : nullptr, 0.f,
-                            nullptr);
+          dgrad_epilogue<0>(taddr, sAct, row, nullptr, 0.f, nullptr);
+          dst_slab = kDaSlabFeat;
         } else {
           const int l = 8 - step;  // produces d_a_l, masked by h_l: step 1 -> l = 7 ... step 8 -> l = 0
           const uint8_t* ms = at ? at + (size_t)l * 4 * kSlabBytes : nullptr;
-          uint8_t* dd = dt ? dt + (size_t)l * 4 * kSlabBytes : nullptr;
-          if (step == 1) dgrad_epilogue<1>(taddr, sAct, true, row, ms, dd, g.w, wa);
-          else dgrad_epilogue<2>(taddr, sAct, step < 8, row, ms, dd, 0.f, nullptr);
+          if (step == 1) dgrad_epilogue<1>(taddr, sAct, row, ms, g.w, wa);
+          else dgrad_epilogue<2>(taddr, sAct, row, ms, 0.f, nullptr);
+          dst_slab = l * 4;
         }
-        if (step < 8) {
-          fence_proxy_async();
-          tc_fence_before();
-          mbar_arrive(my_act);
-        } else {
-          tc_fence_before();
-        }
+        fence_proxy_async();
+        tc_fence_before();
+        __syncwarp();
+        if (step < 8 && lane == 0) mbar_arrive_cluster(act_leader);
+        flush(dst_slab, 4);
       }
     }
+    if (lane == 0) bulk_wait_all();
   }
-  __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem, 512);
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) tmem_dealloc_2sm(tmem, 512);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -678,13 +702,16 @@ int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* act
   const int in_ch = 3 + 6 * L_pts, in_views = 3 + 6 * L_dirs;
   cudaStream_t st = as_stream(stream);
   const int64_t tiles = (M + kTileM - 1) / kTileM;
-  const int64_t pairs = (tiles + 1) / 2;
-  NB_REQUIRE(pairs < (1ll << 30), "nb_mlp_bwd_tc: M too large for one launch");
+  const int64_t quads = (tiles + 3) / 4;
+  NB_REQUIRE(quads < (1ll << 30), "nb_mlp_bwd_tc: M too large for one launch");
   {
-    const int grid = (int)(pairs < kNumSMs ? pairs : kNumSMs);
-    mlp_dgrad_kernel<<<grid, 384, kBSmemBytes, st>>>((const uint8_t*)packed_bwd, (const uint8_t*)acts, d_raw, M,
-                                                     (uint8_t*)dA, (int)pairs);
-    int rc = check_launch("mlp_dgrad_kernel");
+    CUtensorMap wmap;
+    int rc = make_slab_tmap(&wmap, packed_bwd, kBwdSlabs);
+    if (rc) return rc;
+    const int clusters = (int)(quads < kNumSMs / 2 ? quads : kNumSMs / 2);
+    mlp_dgrad_kernel<<<2 * clusters, 384, kBSmemBytes, st>>>(wmap, (const uint8_t*)packed_bwd, (const uint8_t*)acts, d_raw,
+                                                             M, (uint8_t*)dA, (int)quads);
+    rc = check_launch("mlp_dgrad_kernel");
     if (rc) return rc;
   }
   if (!grads) return 0;  // frozen weights: only the dA chain was wanted

@@ -39,6 +39,10 @@ class FlatAdam(torch.optim.Optimizer):
         self.exp_avg_sq = torch.zeros(total, device=dev, dtype=torch.float32)
         self._step = 0
         self.grad_scale = 1.0      # e.g. 1/world_size after a SUM all-reduce of flat_g
+        # CUDA-graph mode (train.GraphedTrainStep): step() launches the kernel that reads its scalars
+        # from this device buffer and does no host bookkeeping; push_hyper() advances the step
+        self._hyper = torch.zeros(8, device=dev, dtype=torch.float32)
+        self.in_graph = False
         with torch.no_grad():
             for p, o in zip(ps, self._offsets):
                 n = p.numel()
@@ -75,14 +79,45 @@ class FlatAdam(torch.optim.Optimizer):
                     view.copy_(p.grad)
                 p.grad = view
 
-    @torch.no_grad()
-    def step(self, closure=None):
-        loss = closure() if closure is not None else None
-        if not self._grads_are_flat():
-            self._regather()
+    def _lr(self):
         g0 = self.param_groups[0]
         if any(g["lr"] != g0["lr"] for g in self.param_groups):
             raise NotImplementedError("FlatAdam uses one learning rate for all parameter groups")
+        return g0
+
+    def push_hyper(self):
+        """Advance the step counter and write this step's scalars (lr from param_groups, bias corrections,
+        grad_scale) to the device buffer the graph-captured update reads; one 1-thread kernel whose
+        arguments are taken at launch, so there is no host buffer to race with."""
+        g0 = self._lr()
+        self._step += 1
+        b1, b2 = g0["betas"]
+        lib = _lib.load()
+        with torch.cuda.device(self.flat_p.device):
+            check(lib.nb_adam_hyper(ptr(self._hyper), float(g0["lr"]), float(b1), float(b2), float(g0["eps"]),
+                                    int(self._step), float(self.grad_scale), stream_ptr()), "nb_adam_hyper")
+
+    def bump_versions(self):
+        """The kernels write parameters through raw pointers: bump the autograd version counters (no
+        launch) so caches keyed on p._version (_ops.packed_weights) see the update."""
+        try:
+            torch.autograd.graph.increment_version(self._params)
+        except TypeError:
+            for p in self._params:
+                torch.autograd.graph.increment_version(p)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        if self.in_graph:
+            lib = _lib.load()
+            with torch.cuda.device(self.flat_p.device):
+                check(lib.nb_adam_step_dev(ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq),
+                                           self._n, ptr(self._hyper), stream_ptr()), "nb_adam_step_dev")
+            return loss
+        if not self._grads_are_flat():
+            self._regather()
+        g0 = self._lr()
         self._step += 1
         b1, b2 = g0["betas"]
         lib = _lib.load()
@@ -91,14 +126,7 @@ class FlatAdam(torch.optim.Optimizer):
             check(lib.nb_adam_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq), self._n,
                                    float(g0["lr"]), float(b1), float(b2), float(g0["eps"]), int(self._step),
                                    float(self.grad_scale), stream_ptr()), "nb_adam_step")
-        # the kernel wrote the parameters through raw pointers: bump their autograd version
-        # counters (no kernel launch) so that caches keyed on p._version (packed bf16 weights,
-        # _ops.packed_weights) see the update
-        try:
-            torch.autograd.graph.increment_version(self._params)
-        except TypeError:
-            for p in self._params:
-                torch.autograd.graph.increment_version(p)
+        self.bump_versions()
         return loss
 
     # ---- torch.optim.Adam-compatible (de)serialisation -------------------------------------

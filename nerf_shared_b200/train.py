@@ -1,0 +1,98 @@
+"""The training step of the reference's main loop as ONE CUDA graph.
+
+`GraphedTrainStep` captures main.py:77-112 -- Renderer.render_from_rays (coarse + fine), the two
+MSE terms, loss.backward(), the optional gradient all-reduce and Adam -- through the same public
+objects main.py uses (Renderer, NeRF, the optimizer from utils.get_optimizer).  A replay launches
+every kernel of the step with no Python between them; the per-step host work is copying the ray
+batch into the static input buffers and one 1-thread kernel that writes Adam's scalars.
+
+    step = train.GraphedTrainStep(renderer, coarse, fine, optimizer, H, W, K, N_rand)
+    for i in range(N_iters):
+        batch_rays, target_s, *_ = utils.sample_random_ray_batch(...)
+        loss, psnr = step(batch_rays, target_s)          # device scalars, no sync
+        for g in optimizer.param_groups: g['lr'] = new_lrate   # main.py:108-112, read at the next call
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from . import utils
+
+
+class GraphedTrainStep:
+    def __init__(self, renderer, coarse_model, fine_model, optimizer, H, W, K, n_rays, chunk=1024 * 32, group=None,
+                 warmup=2):
+        self.renderer, self.coarse, self.fine, self.opt = renderer, coarse_model, fine_model, optimizer
+        self.H, self.W, self.K, self.chunk = H, W, K, chunk
+        self.group = group
+        self.world = torch.distributed.get_world_size(group) if (
+            torch.distributed.is_available() and torch.distributed.is_initialized()) else 1
+        dev = optimizer.flat_p.device
+        self.rays = torch.zeros((2, n_rays, 3), device=dev, dtype=torch.float32)
+        self.target = torch.zeros((n_rays, 3), device=dev, dtype=torch.float32)
+        self.graph = None
+        self._warmup = warmup
+        self.loss = self.psnr = None
+        self.launches_per_replay = 0
+
+    # main.py:77-104 with the optimizer in graph mode
+    def _step(self):
+        opt = self.opt
+        rgb, _, _, extras = self.renderer.render_from_rays(self.H, self.W, self.K, chunk=self.chunk, rays=self.rays,
+                                                           coarse_model=self.coarse, fine_model=self.fine, retraw=True)
+        opt.zero_grad()
+        img_loss = utils.img2mse(rgb, self.target)
+        loss = img_loss
+        if "rgb0" in extras:
+            loss = loss + utils.img2mse(extras["rgb0"], self.target)
+        psnr = torch.log(img_loss.detach()) * (-10.0 / math.log(10.0))     # utils.mse2psnr without its H2D constant
+        loss.backward()
+        if self.world > 1:
+            torch.distributed.all_reduce(opt.flat_g, group=self.group)
+        opt.step()
+        return loss.detach(), psnr
+
+    def _capture(self):
+        opt = self.opt
+        dev = opt.flat_p.device
+        keep = [t.clone() for t in (opt.flat_p, opt.exp_avg, opt.exp_avg_sq)]
+        step0 = opt._step
+        opt.in_graph = True
+        try:
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(self._warmup):       # allocator / packing caches / lazy init, then undone
+                    opt.push_hyper()
+                    self._step()
+                    opt.bump_versions()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            with torch.no_grad():
+                for t, k in zip((opt.flat_p, opt.exp_avg, opt.exp_avg_sq), keep):
+                    t.copy_(k)
+            opt._step = step0
+            opt.bump_versions()                     # the capture must contain the weight re-packing kernels
+            from . import _lib
+            g = torch.cuda.CUDAGraph()
+            l0 = _lib.launch_count()
+            with torch.cuda.graph(g):
+                self.loss, self.psnr = self._step()
+            self.launches_per_replay = _lib.launch_count() - l0     # libnerf_b200 kernels in the graph
+            self.graph = g
+        finally:
+            opt.in_graph = False
+
+    def __call__(self, batch_rays, target):
+        if self.graph is None:
+            self.rays.copy_(torch.as_tensor(batch_rays), non_blocking=True)
+            self.target.copy_(target, non_blocking=True)
+            self._capture()
+        self.rays.copy_(torch.as_tensor(batch_rays) if not torch.is_tensor(batch_rays) else batch_rays, non_blocking=True)
+        self.target.copy_(target, non_blocking=True)
+        self.opt.push_hyper()
+        self.graph.replay()
+        self.opt.bump_versions()
+        return self.loss, self.psnr

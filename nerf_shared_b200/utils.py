@@ -180,6 +180,31 @@ def copy_log_dir(args):
             f.write(src.read())
 
 
+
+_sel_rng = None
+_stages = {}
+
+
+def _choice_without_replacement(n, k):
+    """k distinct indices in [0, n), uniform -- what np.random.choice(n, k, replace=False) draws
+    (utils.py:435), without permuting all n indices every iteration: a Generator seeded from the global
+    NumPy stream (so np.random.seed() still controls it) samples in O(k)."""
+    global _sel_rng
+    if _sel_rng is None:
+        _sel_rng = np.random.default_rng(np.random.randint(0, 2 ** 31 - 1))
+    return _sel_rng.choice(n, size=k, replace=False)
+
+
+def _pinned_stage(n):
+    """Two alternating pinned staging buffers per batch size (async H2D must not race the next fill)."""
+    st = _stages.get(n)
+    if st is None:
+        st = {"i": 0, "bufs": [{"pix": torch.empty(n, dtype=torch.int64).pin_memory(),
+                                 "tgt": torch.empty((n, 3), dtype=torch.float32).pin_memory()} for _ in range(4)]}
+        _stages[n] = st
+    st["i"] = (st["i"] + 1) % len(st["bufs"])
+    return st["bufs"][st["i"]]
+
 # ----------------------------------------------------------------------------- batching (utils.py:360-442)
 def batch_training_data(args, poses, hwf, K, images, i_train):
     """-> images, poses, rays_rgb, use_batching, N_rand, i_batch (same tuple as the reference)."""
@@ -220,15 +245,23 @@ def sample_random_ray_batch(args, images, poses, rays_rgb, N_rand, use_batching,
             print(f"[Config] Center cropping of size {2*dH} x {2*dW} is enabled until iter {args.precrop_iters}")
     else:
         ys, xs = np.arange(H), np.arange(W)
-    sel = np.random.choice(len(ys) * len(xs), size=[N_rand], replace=False)
+    sel = _choice_without_replacement(len(ys) * len(xs), N_rand)
     py, px = ys[sel // len(xs)], xs[sel % len(xs)]
-    pix = torch.as_tensor(py.astype(np.int64) * W + px.astype(np.int64), device=device)
-    rays_o, rays_d = get_rays_at(H, W, K, pose, pix)
+    pix_h = torch.from_numpy(py.astype(np.int64) * W + px.astype(np.int64))
     tgt = images[img_i]
-    if torch.is_tensor(tgt):
-        target_s = tgt.to(device)[torch.as_tensor(py, device=device), torch.as_tensor(px, device=device)]
+    if torch.is_tensor(tgt) and tgt.device.type == "cuda":
+        pix = pix_h.to(device, non_blocking=True)
+        target_s = tgt.reshape(-1, tgt.shape[-1])[pix]
     else:
-        target_s = torch.as_tensor(np.ascontiguousarray(tgt[py, px]), dtype=torch.float32).to(device)
+        # host-resident images (no_batching keeps them in NumPy / pinned memory, utils.py:383-390):
+        # gather the N_rand target pixels on the host and ship 12 B per ray, not the whole image
+        tnp = tgt.numpy() if torch.is_tensor(tgt) else tgt
+        stage = _pinned_stage(N_rand)
+        stage["pix"].copy_(pix_h)
+        stage["tgt"].copy_(torch.from_numpy(np.ascontiguousarray(tnp[py, px], dtype=np.float32)))
+        pix = stage["pix"].to(device, non_blocking=True)
+        target_s = stage["tgt"].to(device, non_blocking=True)
+    rays_o, rays_d = get_rays_at(H, W, K, pose, pix)
     return torch.stack([rays_o, rays_d], 0), target_s, rays_rgb, i_batch
 
 

@@ -171,3 +171,97 @@ def test_training_step_golden(golden):
         # Adam's first step moves every weight by ~lr * sign(g): compare where |g| is not tiny
         e = T(golden["train/%s/after_adam/l0_b" % tag])
         assert maxabs(m.pts_linears[0].bias, e) <= 1.1e-3
+
+
+def _train_setup():
+    from nerf_shared_b200 import render_utils, utils
+
+    class A:
+        lrate = 5e-4
+    mc, mf = make_model(11), make_model(12)
+    r = render_utils.Renderer(perturb=0.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                              raw_noise_std=0.0, near=2.0, far=6.0)
+    r.train()
+    opt = utils.get_optimizer(mc, mf, A())
+    return mc, mf, r, opt
+
+
+def test_graphed_train_step_matches_eager(golden):
+    """train.GraphedTrainStep (one CUDA graph per step) == the eager main.py loop on the same batches,
+    including the learning-rate schedule written to param_groups between steps."""
+    from nerf_shared_b200 import train, utils
+    H = W = 8
+    K = O.blender_intrinsics(H, W)
+    rb = cuda(golden["rr/ray_batch"])
+    rays = torch.stack([rb[:, 0:3], rb[:, 3:6]], 0).contiguous()
+    g = torch.Generator().manual_seed(3)
+    targets = [torch.rand(rays.shape[1], 3, generator=g).cuda() for _ in range(4)]
+    lrs = [5e-4, 4e-4, 3e-4, 2e-4]
+
+    mc, mf, r, opt = _train_setup()
+    eager_losses = []
+    for tgt, lr in zip(targets, lrs):
+        for pg in opt.param_groups:
+            pg["lr"] = lr
+        rgb, _, _, extras = r.render_from_rays(H, W, K, chunk=32768, rays=rays, coarse_model=mc, fine_model=mf, retraw=True)
+        opt.zero_grad()
+        loss = utils.img2mse(rgb, tgt) + utils.img2mse(extras["rgb0"], tgt)
+        loss.backward()
+        opt.step()
+        eager_losses.append(float(loss))
+    p_eager = opt.flat_p.clone()
+
+    mc2, mf2, r2, opt2 = _train_setup()
+    step = train.GraphedTrainStep(r2, mc2, mf2, opt2, H, W, K, rays.shape[1])
+    graph_losses = []
+    for tgt, lr in zip(targets, lrs):
+        for pg in opt2.param_groups:
+            pg["lr"] = lr
+        loss, psnr = step(rays, tgt)
+        graph_losses.append(float(loss))
+    assert opt2._step == 4
+    for a, b in zip(eager_losses, graph_losses):
+        assert abs(a - b) <= 1e-4 * abs(a), (eager_losses, graph_losses)
+    # parameters: Adam's sign-like first steps amplify atomics-order noise where |g| ~ 0; bound by a few lr
+    assert float((opt2.flat_p - p_eager).abs().max()) <= 2.5e-3
+    assert float((opt2.flat_p - p_eager).abs().mean()) <= 2e-5
+    # an eager render after graph replays must see the updated weights (version bump -> re-pack)
+    with torch.no_grad():
+        rgb_a = r.render_from_rays(H, W, K, chunk=32768, rays=rays, coarse_model=mc, fine_model=mf, retraw=False)[0]
+        rgb_b = r2.render_from_rays(H, W, K, chunk=32768, rays=rays, coarse_model=mc2, fine_model=mf2, retraw=False)[0]
+    assert maxabs(rgb_a, rgb_b) <= 2e-2
+
+
+def test_sample_random_ray_batch_rays_and_targets():
+    """utils.sample_random_ray_batch (utils.py:394-442, no_batching branch): distinct pixels, rays equal
+    to get_rays() at those pixels bit for bit, targets equal to the image at those pixels."""
+    from nerf_shared_b200 import utils
+
+    class A:
+        precrop_iters, precrop_frac = 0, 0.5
+    H, W, N = 40, 60, 256
+    K = O.blender_intrinsics(H, W)
+    rng = np.random.default_rng(0)
+    images = rng.random((3, H, W, 3), dtype=np.float32)
+    poses = np.stack([O.pose_spherical(float(t), -30.0, 4.0) for t in (10.0, 80.0, 200.0)], 0).astype(np.float32)
+    poses_d = cuda(poses)
+    for imgs in (images, torch.from_numpy(images).pin_memory(), cuda(images)):
+        np.random.seed(5)
+        utils._sel_rng = None
+        batch_rays, target, _, _ = utils.sample_random_ray_batch(A(), imgs, poses_d, None, N, False, None, np.arange(3),
+                                                                 [H, W, float(K[0][0])], K, 0, 1)
+        assert tuple(batch_rays.shape) == (2, N, 3) and tuple(target.shape) == (N, 3)
+        hit = None
+        for i in range(3):
+            ro, rd = utils.get_rays(H, W, K, poses_d[i, :3, :4])
+            flat = rd.reshape(-1, 3)
+            # locate each sampled direction in this image's ray grid
+            eq = (flat[None, :, :] == batch_rays[1][:, None, :]).all(-1)          # [N, H*W]
+            if bool(eq.any(1).all()):
+                hit = (i, eq.float().argmax(1))
+                break
+        assert hit is not None, "sampled rays are not rays of any training image"
+        i, pix = hit
+        assert pix.unique().numel() == N                                          # without replacement
+        assert torch.equal(batch_rays[0], ro.reshape(-1, 3)[pix])
+        assert torch.equal(target.cpu(), torch.from_numpy(images[i].reshape(-1, 3))[pix.cpu()])
