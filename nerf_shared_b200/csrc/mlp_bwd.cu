@@ -317,6 +317,7 @@ struct WJob {
   int n_valid;    // in features actually present
   int ld;         // row stride of the fp32 weight gradient
   int64_t off;    // float offset of dW[0][first in-feature] in the flat gradient buffer
+  int64_t bias_off;  // float offset of the bias gradient (column sums of this job's dA block), or -1
 };
 constexpr int kNumWJobs = 12;
 struct WJobs {
@@ -325,7 +326,8 @@ struct WJobs {
 
 constexpr int kWStages = 3;
 constexpr uint32_t kWStageBytes = 65536;  // 64 samples x (256 + 256) features
-constexpr uint32_t kWSmBar = kWStages * kWStageBytes;
+constexpr uint32_t kWSmRed = kWStages * kWStageBytes;       // [4 sample groups][256 features] fp32 bias partials
+constexpr uint32_t kWSmBar = kWSmRed + 4096;
 constexpr uint32_t kWSmTmemPtr = kWSmBar + 120;
 constexpr uint32_t kWSmemBytes = kWSmBar + 128 + 1024;
 
@@ -343,7 +345,7 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16_mn(int M, int N) {
   return make_idesc_bf16(M, N) | (1u << 15) | (1u << 16);  // A and B MN-major
 }
 
-__global__ void __launch_bounds__(256, 1) mlp_wgrad_kernel(WJobs jobs, const uint8_t* __restrict__ acts,
+__global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, const uint8_t* __restrict__ acts,
                                                            const uint8_t* __restrict__ dA, int num_tiles,
                                                            int tiles_per_unit, int num_units,
                                                            float* __restrict__ grads) {
@@ -356,7 +358,7 @@ __global__ void __launch_bounds__(256, 1) mlp_wgrad_kernel(WJobs jobs, const uin
   if (threadIdx.x == 0) {
     for (int i = 0; i < kWStages; ++i) {
       mbar_init(bar_full + 8 * i, 1);
-      mbar_init(bar_empty + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 2);  // tcgen05.commit + the bias warps
     }
     mbar_init(bar_acc, 1);
     mbar_init(bar_flush, 128);
@@ -432,7 +434,7 @@ __global__ void __launch_bounds__(256, 1) mlp_wgrad_kernel(WJobs jobs, const uin
         umma_commit(bar_acc);
       }
     }
-  } else if (warp >= 4) {
+  } else if (warp >= 4 && warp < 8) {
     // flush warps: TMEM lane = out feature within the 128-block
     const int row = ((warp & 3) << 5) | lane;
     uint32_t par_acc = 0;
@@ -454,6 +456,53 @@ __global__ void __launch_bounds__(256, 1) mlp_wgrad_kernel(WJobs jobs, const uin
       }
       tc_fence_before();
       mbar_arrive(bar_flush);
+    }
+  } else if (warp >= 8) {
+    // bias warps: db = column sums of dA over the samples, taken from the operand stages while they
+    // sit in shared memory (no second pass over dA in HBM).  Thread (c, q): 8 features 8c..8c+7,
+    // samples q, q+4, ... of each 64-sample stage.
+    const int t = threadIdx.x - 256, c = t & 31, q = t >> 5;
+    float* red = reinterpret_cast<float*>(gbase + kWSmRed);
+    uint32_t stage = 0, phase = 0;
+    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+      const WJob j = jobs.job[u % kNumWJobs];
+      const int t0 = (u / kNumWJobs) * tiles_per_unit;
+      const int t1 = min(t0 + tiles_per_unit, num_tiles);
+      const bool mine = j.bias_off >= 0 && c < j.m_blocks * 16;
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int st = 2 * (t1 - t0); st > 0; --st) {
+        mbar_wait(bar_full + 8 * stage, phase);
+        if (mine) {
+          const uint32_t blk = base + stage * kWStageBytes + (c >> 3) * 8192;
+#pragma unroll 4
+          for (int i = 0; i < 16; ++i) {
+            const int sm = q + 4 * i;
+            uint4 v;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                         : "r"(blk + (sm >> 3) * 1024 + (sm & 7) * 128 + (((c & 7) ^ (sm & 7)) << 4)));
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              acc[2 * k] += __uint_as_float(w[k] << 16);
+              acc[2 * k + 1] += __uint_as_float(w[k] & 0xFFFF0000u);
+            }
+          }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // all four bias warps are done reading the stage
+        if (t == 0) mbar_arrive(bar_empty + 8 * stage);
+        if (++stage == kWStages) { stage = 0; phase ^= 1; }
+      }
+      if (j.bias_off >= 0) {
+        if (mine) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) red[q * 256 + c * 8 + k] = acc[k];
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        for (int f = t; f < j.m_blocks * 128; f += 128)
+          atomicAdd(grads + j.bias_off + f, red[f] + red[256 + f] + red[512 + f] + red[768 + f]);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
     }
   }
   __syncthreads();
@@ -500,23 +549,6 @@ __global__ void __launch_bounds__(256) mlp_small_grads_kernel(const uint8_t* __r
   const int t = threadIdx.x, g = t & 7, rg = t >> 3;
   const int t0 = blockIdx.x * tiles_per_block, t1 = min(t0 + tiles_per_block, num_tiles);
   if (t0 >= t1) return;
-  // biases: column sums of every dA slab
-  for (int s = 0; s < kDaSlabs; ++s) {
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int tile = t0; tile < t1; ++tile) {
-      const uint8_t* slab = dA + ((size_t)tile * kDaSlabs + s) * kSlabBytes;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        float f[8];
-        unpack8(*reinterpret_cast<const uint4*>(slab + sw128_chunk_off(rg + 32 * i, g)), f);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += f[j];
-      }
-    }
-    float* dst = s < 32 ? grads + o.pts_b[s >> 2] + (s & 3) * 64
-                        : (s < 36 ? grads + o.feature_b + (s - 32) * 64 : grads + o.views_b + (s - 36) * 64);
-    reduce_cols(acc, red, dst, 64);
-  }
   // alpha_linear: dW = sum d_sigma * h7, db = sum d_sigma ; rgb_linear: dW[k] = sum d_rgb[k] * hv, db = sum d_rgb
   for (int s = 0; s < 4; ++s) {
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -721,25 +753,25 @@ int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* act
   {
     WJobs jobs;
     int n = 0;
-    jobs.job[n++] = WJob{0, 2, kActSlabEncP, 64, in_ch, in_ch, off[0]};                       // pts_linears[0]
+    jobs.job[n++] = WJob{0, 2, kActSlabEncP, 64, in_ch, in_ch, off[0], off[8]};                // pts_linears[0] (+ its bias)
     for (int l = 1; l < 8; ++l) {
       if (l == 5) {
-        jobs.job[n++] = WJob{20, 2, 16, 256, 256, 256 + in_ch, off[5] + in_ch};               // W5[:, in_ch:]  (h4)
-        jobs.job[n++] = WJob{20, 2, kActSlabEncP, 64, in_ch, 256 + in_ch, off[5]};            // W5[:, :in_ch]  (enc)
+        jobs.job[n++] = WJob{20, 2, 16, 256, 256, 256 + in_ch, off[5] + in_ch, off[13]};         // W5[:, in_ch:]  (h4)
+        jobs.job[n++] = WJob{20, 2, kActSlabEncP, 64, in_ch, 256 + in_ch, off[5], -1};           // W5[:, :in_ch]  (enc)
       } else {
-        jobs.job[n++] = WJob{4 * l, 2, 4 * (l - 1), 256, 256, 256, off[l]};
+        jobs.job[n++] = WJob{4 * l, 2, 4 * (l - 1), 256, 256, 256, off[l], off[8 + l]};
       }
     }
-    jobs.job[n++] = WJob{kDaSlabFeat, 2, 28, 256, 256, 256, off[16]};                         // feature_linear (h7)
-    jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabFeat, 256, 256, 256 + in_views, off[20]};      // views[:, :256] (feature)
-    jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabEncD, 64, in_views, 256 + in_views, off[20] + 256};  // views[:, 256:]
+    jobs.job[n++] = WJob{kDaSlabFeat, 2, 28, 256, 256, 256, off[16], off[17]};                   // feature_linear (h7)
+    jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabFeat, 256, 256, 256 + in_views, off[20], off[21]};  // views[:, :256] (feature)
+    jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabEncD, 64, in_views, 256 + in_views, off[20] + 256, -1};  // views[:, 256:]
     NB_REQUIRE(n == kNumWJobs, "internal: wgrad job table");
     int tpu = (int)((tiles * kNumWJobs + 2 * kNumSMs - 1) / (2 * kNumSMs));
     if (tpu < 4) tpu = 4;
     const int chunks = (int)((tiles + tpu - 1) / tpu);
     const int units = chunks * kNumWJobs;
     const int grid = units < kNumSMs ? units : kNumSMs;
-    mlp_wgrad_kernel<<<grid, 256, kWSmemBytes, st>>>(jobs, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, tpu,
+    mlp_wgrad_kernel<<<grid, 384, kWSmemBytes, st>>>(jobs, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, tpu,
                                                      units, grads);
     int rc = check_launch("mlp_wgrad_kernel");
     if (rc) return rc;
