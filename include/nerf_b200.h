@@ -161,6 +161,18 @@ NB_API int64_t nb_mlp_da_bytes(int64_t M);
 NB_API int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
                          void* dA, const int64_t* grad_off_host24, float* grads, void* stream);
 
+/* Gradient wrt the MLP's INPUTS from the dA tiles nb_mlp_bwd_tc left behind (pose estimation:
+ * demo_est_rel_pose.py:87-97 backpropagates through frozen weights to the sample positions and view
+ * directions).  replaces: autograd of the two Embedder calls, the first layer, the skip connection and
+ * the view branch input, nerf.py:97-104,110-118,124.
+ * packed_in: nb_mlp_pack_ingrad output (nb_mlp_ingrad_packed_bytes bytes).  pts [M,3], viewdirs [M/S,3]
+ * as given to nb_mlp_fwd_tc.  d_pts [M,3] is written; d_viewdirs [M/S,3] is ACCUMULATED into (caller
+ * zeroes): the reference broadcasts one view direction over the S samples of a ray (nerf.py:101). */
+NB_API int64_t nb_mlp_ingrad_packed_bytes(int L_pts, int L_dirs);
+NB_API int nb_mlp_pack_ingrad(const NbMlpWeights* w, void* packed_in, void* stream);
+NB_API int nb_mlp_bwd_inputs(const void* packed_in, int L_pts, int L_dirs, const void* dA, const float* pts,
+                             const float* viewdirs, int64_t M, int S, float* d_pts, float* d_viewdirs, void* stream);
+
 /* ---- optimizer ------------------------------------------------------------------------- */
 /* torch.optim.Adam (utils.py:170) on flat fp32 buffers; step is 1-based.
  * replaces: Adam.step main.py:104. */

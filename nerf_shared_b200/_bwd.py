@@ -18,38 +18,67 @@ def grad_layout(model):
     return offs, total
 
 
+def packed_ingrad(model) -> torch.Tensor:
+    """Transposed bf16 slabs of the three weight blocks that touch the encoded inputs (first layer,
+    skip connection, view branch); cached like _ops.packed_weights."""
+    params = _ops.mlp_params(model)
+    dev = params[0].device
+    lib = _ops._lib_for(params[0])
+    key = tuple((p.data_ptr(), p._version) for p in (params[0], params[5], params[20]))
+    cache = model.__dict__.get("_nb_packed_in")
+    if cache is not None and cache[0] == key and cache[1].device == dev:
+        return cache[1]
+    nbytes = int(lib.nb_mlp_ingrad_packed_bytes(int(model.multires), int(model.multires_views)))
+    buf = torch.empty((nbytes,), device=dev, dtype=torch.uint8)
+    w = _ops.mlp_weight_struct(model)
+    with torch.cuda.device(dev):
+        check(lib.nb_mlp_pack_ingrad(C.byref(w), ptr(buf), stream_ptr()), "nb_mlp_pack_ingrad")
+    model.__dict__["_nb_packed_in"] = (key, buf)
+    return buf
+
+
 def nerf_mlp_backward(ctx, g_raw):
     model, S = ctx.model, ctx.S
     pts, viewdirs, acts = ctx.saved_tensors
     lib = _ops._lib_for(pts)
     M = pts.shape[0]
-    if ctx.needs_input_grad[0] or ctx.needs_input_grad[1]:
-        raise NotImplementedError("gradients wrt sample positions / view directions (pose estimation path) are not "
-                                  "implemented yet in libnerf_b200")
     params = _ops.mlp_params(model)
+    need_in = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
     need_w = any(ctx.needs_input_grad[5:])
-    if not need_w:
-        return (None, None, None, None, None) + (None,) * len(params)
+    none5 = (None, None, None, None, None)
+    if not (need_w or need_in):
+        return none5 + (None,) * len(params)
     dev = pts.device
-    # a FlatAdam optimizer registers its flat gradient buffer on the model: the wgrad kernels then
-    # accumulate in place (every p.grad is a view of that buffer) and autograd gets no tensors
-    target = model.__dict__.get("_nb_grad_target")
-    in_place = target is not None and target[0].device == dev
-    if in_place:
-        grads, offs = target
-    else:
-        offs, total = grad_layout(model)
-        grads = torch.zeros((total,), device=dev, dtype=torch.float32)
+    grads, offs, in_place = None, [0] * 24, False
+    if need_w:
+        # a FlatAdam optimizer registers its flat gradient buffer on the model: the wgrad kernels then
+        # accumulate in place (every p.grad is a view of that buffer) and autograd gets no tensors
+        target = model.__dict__.get("_nb_grad_target")
+        in_place = target is not None and target[0].device == dev
+        if in_place:
+            grads, offs = target
+        else:
+            offs, total = grad_layout(model)
+            grads = torch.zeros((total,), device=dev, dtype=torch.float32)
     dA = torch.empty((int(lib.nb_mlp_da_bytes(M)),), device=dev, dtype=torch.uint8)
     packed_bwd = _ops.packed_weights(model, backward=True)
     off_arr = (C.c_int64 * 24)(*offs)
     g = f32c(g_raw).view(-1, 4)
+    L, Lv = int(model.multires), int(model.multires_views)
+    d_pts = d_vd = None
     with torch.cuda.device(dev):
-        check(lib.nb_mlp_bwd_tc(ptr(packed_bwd), int(model.multires), int(model.multires_views), ptr(acts), ptr(g), M,
-                                ptr(dA), off_arr, ptr(grads), stream_ptr()), "nb_mlp_bwd_tc")
+        # frozen weights (grads == NULL): only the dgrad chain runs (pose estimation, demo_est_rel_pose.py:375)
+        check(lib.nb_mlp_bwd_tc(ptr(packed_bwd), L, Lv, ptr(acts), ptr(g), M, ptr(dA), off_arr, ptr(grads), stream_ptr()),
+              "nb_mlp_bwd_tc")
+        if need_in:
+            d_pts = torch.empty((M, 3), device=dev, dtype=torch.float32)
+            d_vd = torch.zeros((M // S, 3), device=dev, dtype=torch.float32)
+            check(lib.nb_mlp_bwd_inputs(ptr(packed_ingrad(model)), L, Lv, ptr(dA), ptr(pts), ptr(viewdirs), M, S,
+                                        ptr(d_pts), ptr(d_vd), stream_ptr()), "nb_mlp_bwd_inputs")
     out = []
     for i, p in enumerate(params):
-        use = ctx.needs_input_grad[5 + i] and not in_place
+        use = need_w and ctx.needs_input_grad[5 + i] and not in_place
         out.append(grads[offs[i]:offs[i] + p.numel()].view_as(p) if use else None)
     ctx.model._nb_last_dA = dA if getattr(ctx.model, "_nb_keep_dA", False) else None
-    return (None, None, None, None, None) + tuple(out)
+    return (d_pts if ctx.needs_input_grad[0] else None, d_vd if ctx.needs_input_grad[1] else None, None, None,
+            None) + tuple(out)

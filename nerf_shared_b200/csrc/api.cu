@@ -32,6 +32,7 @@ int check_launch(const char* what) {
 int init_mlp_tc(int device);      // mlp_tc.cu
 int init_mlp_simt(int device);    // mlp_simt.cu
 int init_mlp_bwd(int device);     // mlp_bwd.cu
+int init_mlp_ingrad(int device);  // mlp_ingrad.cu
 
 }  // namespace nb
 
@@ -68,6 +69,7 @@ int nb_init(int device) {
   int rc = nb::init_mlp_simt(device);
   if (rc == 0) rc = nb::init_mlp_tc(device);
   if (rc == 0) rc = nb::init_mlp_bwd(device);
+  if (rc == 0) rc = nb::init_mlp_ingrad(device);
   cudaSetDevice(cur);
   return rc;
 }

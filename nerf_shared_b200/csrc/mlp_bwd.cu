@@ -26,8 +26,6 @@ using namespace ptx;
 
 constexpr int kBwdSlabs = 68;         // views^T (4) + feature^T (8) + pts_linears[7..1]^T (7 x 8)
 constexpr int kBwdConstFloats = 640;  // rgb_w [3][128] | alpha_w [256]
-constexpr int kDaSlabs = 38;          // d_a0..d_a7 (4 each) | d_feature (4) | d_a(view hidden) (2)
-constexpr int kDaSlabFeat = 32, kDaSlabHv = 36;
 constexpr int kBwdStages = 5;
 
 // dgrad shared memory map

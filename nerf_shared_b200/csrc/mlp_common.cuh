@@ -15,6 +15,9 @@ constexpr int kConstFloats = 3200;
 //   slabs 4l..4l+3 = h_l (l = 0..7) | 32..35 = feature | 36,37 = view hidden | 38 = enc(pts) | 39 = enc(dirs)
 constexpr int kActSlabs = 40;
 constexpr int kActSlabFeat = 32, kActSlabHv = 36, kActSlabEncP = 38, kActSlabEncD = 39;
-
+// Pre-activation gradients written by the dgrad chain (same slab image):
+//   slabs 4l..4l+3 = d_a_l (l = 0..7) | 32..35 = d_feature | 36,37 = d_a(view hidden)
+constexpr int kDaSlabs = 38;
+constexpr int kDaSlabFeat = 32, kDaSlabHv = 36;
 
 }  // namespace nb
