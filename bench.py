@@ -237,10 +237,11 @@ def run_b200(a):
                       "launch": "one CUDA graph per step (train.GraphedTrainStep)"},
            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
 
+    render = None if a.no_render else render_leg(renderer, coarse, fine, K, poses_d, dev, world)   # all ranks (row-sharded)
     if rank == 0:
         out.update(kernel_breakdown(a, coarse, fine, pool[0], dev))
-        if not a.no_render and world == 1:
-            out["render"] = render_leg(renderer, coarse, fine, K, poses_d, dev)
+        if render is not None:
+            out["render"] = render
         if not a.no_cpu_baseline:
             out["cpu_baseline"] = cpu_train_baseline(budget_s=15.0)
         print(json.dumps(out), file=_real_stdout, flush=True)
@@ -299,29 +300,42 @@ def kernel_breakdown(a, coarse, fine, batch, dev):
                          "per_kernel_tflops": {k: round(flops[k] / times[k] / 1e9, 1) for k in times}}}
 
 
-def render_leg(renderer, coarse, fine, K, poses_d, dev):
-    """800x800 full-res render (BASELINE.json configs[3] on one GPU): frames/s, inputs resident."""
+def render_leg(renderer, coarse, fine, K, poses_d, dev, world=1):
+    """800x800 full-res render (BASELINE.json configs[3]): frames/s with the pose resident; image rows are
+    split across the ranks (dist.render_sharded) and the tiles all-gathered, time = max over ranks."""
+    import torch.distributed as dist
+    from nerf_shared_b200 import dist as nd
     from oracle import nerf_oracle as O
     K8 = O.blender_intrinsics(800, 800)
     renderer.eval()
     perturb = renderer.perturb
     renderer.perturb = 0.0
+
+    def frame(i):
+        return nd.render_sharded(renderer, 800, 800, K8, 32768, poses_d[i % N_IMAGES, :3, :4], coarse, fine)
+
     with torch.no_grad():
-        renderer.render_from_pose(800, 800, K8, 32768, poses_d[0, :3, :4], coarse, fine, retraw=False)
+        frame(0)
+        frame(1)
+        if world > 1:
+            dist.barrier()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        n = 3
+        n = 4
         for i in range(n):
-            renderer.render_from_pose(800, 800, K8, 32768, poses_d[(i + 1) % N_IMAGES, :3, :4], coarse, fine, retraw=False)
+            frame(i + 2)
         e1.record()
         torch.cuda.synchronize()
     renderer.perturb = perturb
-    ms = e0.elapsed_time(e1) / n
+    t = torch.tensor([e0.elapsed_time(e1) / n], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
     burst, sustained, _, _ = peaks()
     tf = 640000 * (64 + 192) * FLOP_FWD / ms / 1e9
-    return {"workload": "800x800 Blender render, 64+128 samples, 1 GPU", "fps": 1e3 / ms, "ms_per_frame": ms,
-            "mlp_tflops": tf, "frac_of_sustained_peak": tf / sustained}
+    return {"workload": "800x800 Blender render, 64+128 samples, rows split over %d GPU(s)" % world, "fps": 1e3 / ms,
+            "ms_per_frame": ms, "mlp_tflops": tf, "frac_of_sustained_peak": tf / (sustained * world)}
 
 
 def cpu_step_fn():
