@@ -19,6 +19,10 @@ import sys
 import threading
 import time
 
+# torchrun exports OMP_NUM_THREADS=1 to every rank; rank 0 times the CPU arm and needs the host cores
+if os.environ.get("RANK", "0") == "0" and os.environ.get("OMP_NUM_THREADS") == "1":
+    os.environ["OMP_NUM_THREADS"] = os.environ["MKL_NUM_THREADS"] = str(os.cpu_count() or 1)
+
 import numpy as np
 import torch
 
@@ -242,12 +246,21 @@ def run_b200(a):
         out.update(kernel_breakdown(a, coarse, fine, pool[0], dev))
         if render is not None:
             out["render"] = render
-        if not a.no_cpu_baseline:
+        if not a.no_cpu_baseline and world == 1:     # the CPU baseline is reported at N=1 only
             out["cpu_baseline"] = cpu_train_baseline(budget_s=15.0)
         print(json.dumps(out), file=_real_stdout, flush=True)
+    # teardown: a CUDA graph that captured NCCL kernels must be released before its communicator;
+    # if anything in the teardown still blocks, dump the stacks and leave (the result is already printed)
+    import faulthandler
+    import gc
+    faulthandler.dump_traceback_later(90, exit=True)
+    step.graph = None
+    gc.collect()
+    torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    faulthandler.cancel_dump_traceback_later()
 
 
 def kernel_breakdown(a, coarse, fine, batch, dev):
