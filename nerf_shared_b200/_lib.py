@@ -72,6 +72,7 @@ SIGNATURES = {
     "nb_adam_hyper": (i32, [vp, f32, f32, f32, f32, i32, f32, vp]),
     "nb_adam_step_dev": (i32, [vp, vp, vp, vp, i64, vp, vp]),
     "nb_debug_umma": (i32, [vp, vp, i32, vp, vp]),
+    "nb_debug_umma_rate": (i32, [i32, i32, i32, vp, vp]),
 }
 
 

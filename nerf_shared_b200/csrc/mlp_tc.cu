@@ -279,7 +279,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
   const float* cst = reinterpret_cast<const float*>(gbase + kSmConst);
   const uint32_t bar_full = base + kSmBar, bar_empty = bar_full + 8 * kStages, bar_act = bar_empty + 8 * kStages,
                  bar_acc = bar_act + 16, bar_const = bar_acc + 16;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;  // warp: provably uniform
   const uint32_t rank = cluster_ctarank();
   const int cluster = (int)cluster_id_x(), num_clusters = (int)cluster_count_x();
 
@@ -305,36 +305,47 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kSmTmemPtr);
 
+  // The producer and MMA warps run CONVERGED (all 32 lanes execute the loops and the barrier waits) and
+  // issue the asynchronous instructions under elect.sync: with a single provably-active lane and
+  // warp-uniform operands the compiler feeds UTMALDG / UTCHMMA / UTCBAR from uniform registers directly;
+  // a `lane == 0` branch instead costs an ELECT + R2UR waterfall loop per instruction (~100 cycles per MMA
+  // on the issuing thread, which then cannot keep ahead of the 128-cycle MMAs).
   if (warp == 0) {
     // ---------------- weight producer: this CTA's half of every slab ----------------
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(bar_const, kConstFloats * 4);
       bulk_g2s(base + kSmConst, blob + (size_t)kNumSlabs * kSlabBytes, kConstFloats * 4, bar_const);
-      uint32_t stage = 0, phase = 0;
-      for (int quad = cluster; quad < num_quads; quad += num_clusters) {
-        for (int layer = 0; layer < 10; ++layer) {
-          const int nks = ks_count(layer), sb = slab_base(layer);
-          const uint32_t half_bytes = layer == 9 ? 8192u : 16384u;
-          for (int x = 0; x < 2; ++x) {
-            for (int ks = 0; ks < nks; ++ks) {
-              mbar_wait_cluster(bar_empty + 8 * stage, phase ^ 1);
+    }
+    __syncwarp();
+    uint32_t stage = 0, phase = 0;
+    const uint32_t full_leader0 = mapa(bar_full, 0);
+    for (int quad = cluster; quad < num_quads; quad += num_clusters) {
+      for (int layer = 0; layer < 10; ++layer) {
+        const int nks = ks_count(layer), sb = slab_base(layer);
+        const uint32_t half_bytes = layer == 9 ? 8192u : 16384u;
+        for (int x = 0; x < 2; ++x) {
+          for (int ks = 0; ks < nks; ++ks) {
+            mbar_wait_cluster(bar_empty + 8 * stage, phase ^ 1);
+            // layers 0..8: slab (ks, nh = rank), 128 rows; layer 9 (N = 128): rows 64*rank.. of slab ks
+            const int row0 = layer == 9 ? (sb + ks) * 128 + 64 * (int)rank : (sb + ks * 2 + (int)rank) * 128;
+            if (elect_one()) {
               if (rank == 0) mbar_expect_tx(bar_full + 8 * stage, 2 * half_bytes);
-              const uint32_t full_leader = mapa(bar_full + 8 * stage, 0);
+              const uint32_t full_leader = full_leader0 + 8 * stage;
               const uint32_t dst = base + kSmRing + stage * kSlabBytes;
-              // layers 0..8: slab (ks, nh = rank), 128 rows; layer 9 (N = 128): rows 64*rank.. of slab ks
-              const int row0 = layer == 9 ? (sb + ks) * 128 + 64 * (int)rank : (sb + ks * 2 + (int)rank) * 128;
               tma_load_2d_2sm(dst, &wmap, 0, row0, full_leader);
               if (layer != 9) tma_load_2d_2sm(dst + 8192, &wmap, 0, row0 + 64, full_leader);
-              if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
+            __syncwarp();
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
     // ---------------- MMA issuer (leader CTA only) ----------------
-    if (lane == 0 && rank == 0) {
+    if (rank == 0) {
       const uint32_t idesc256 = make_idesc_bf16(256, 256), idesc128 = make_idesc_bf16(256, 128);
+      const uint64_t desc0 = make_desc_kmajor_sw128(0);
       uint32_t stage = 0, phase = 0, par_act0 = 0, par_act1 = 0;
       for (int quad = cluster; quad < num_quads; quad += num_clusters) {
         for (int layer = 0; layer < 10; ++layer) {
@@ -352,17 +363,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
               else if (layer == 5) a_addr = ks == 0 ? sEnc : sAct + (ks - 1) * kSlabBytes;  // cat[input_pts, h]
               else if (layer == 9 && ks == 4) a_addr = sEnc;                              // cat[feature, dirs]
               else a_addr = sAct + ks * kSlabBytes;
-              const int nk16 = (layer == 9 && ks == 4) ? 2 : 4;
-              const uint64_t adesc = make_desc_kmajor_sw128(a_addr);
+              const bool half_k = layer == 9 && ks == 4;   // 32-wide view encoding: two K=16 steps
+              const uint64_t adesc = desc0 | (uint64_t)((a_addr & 0x3FFFFu) >> 4);
+              const uint64_t bdesc = desc0 | (uint64_t)(((base + kSmRing + stage * kSlabBytes) & 0x3FFFFu) >> 4);
               mbar_wait_cluster(bar_full + 8 * stage, phase);
               tc_fence_after();
-              const uint64_t bdesc = make_desc_kmajor_sw128(base + kSmRing + stage * kSlabBytes);
-              for (int k16 = 0; k16 < nk16; ++k16)
-                umma_bf16_2sm(d, adesc + 2 * k16, bdesc + 2 * k16, idesc, (ks | k16) != 0);
-              umma_commit_2sm(bar_empty + 8 * stage);  // frees the stage in both CTAs
+              if (elect_one()) {
+                umma_bf16_2sm(d, adesc, bdesc, idesc, ks != 0);
+                umma_bf16_2sm(d, adesc + 2, bdesc + 2, idesc, 1);
+                if (!half_k) {
+                  umma_bf16_2sm(d, adesc + 4, bdesc + 4, idesc, 1);
+                  umma_bf16_2sm(d, adesc + 6, bdesc + 6, idesc, 1);
+                }
+                umma_commit_2sm(bar_empty + 8 * stage);  // frees the stage in both CTAs
+                if (ks == nks - 1) umma_commit_2sm(bar_acc + 8 * x);  // accumulator of (tile x, layer) complete
+              }
+              __syncwarp();
               if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
-            umma_commit_2sm(bar_acc + 8 * x);  // accumulator of (tile x, layer) complete in both CTAs
           }
         }
       }
