@@ -139,7 +139,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
   const float* cst = reinterpret_cast<const float*>(gbase + kBSmConst);
   const uint32_t bar_full = base + kBSmBar, bar_empty = bar_full + 8 * kBwdStages, bar_act = bar_empty + 8 * kBwdStages,
                  bar_acc = bar_act + 16, bar_const = bar_acc + 16;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
   const int cluster = (int)cluster_id_x(), num_clusters = (int)cluster_count_x();
 
@@ -165,32 +165,39 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kBSmTmemPtr);
 
+  // producer and MMA warps run converged and issue under elect.sync (see mlp_tc.cu)
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(bar_const, kBwdConstFloats * 4);
       bulk_g2s(base + kBSmConst, blob + (size_t)kBwdSlabs * kSlabBytes, kBwdConstFloats * 4, bar_const);
-      uint32_t stage = 0, phase = 0;
-      for (int quad = cluster; quad < num_quads; quad += num_clusters) {
-        for (int step = 0; step < 9; ++step) {
-          const int nks = bwd_ks_count(step), sb = bwd_slab_base(step);
-          for (int x = 0; x < 2; ++x) {
-            for (int ks = 0; ks < nks; ++ks) {
-              mbar_wait_cluster(bar_empty + 8 * stage, phase ^ 1);
+    }
+    __syncwarp();
+    uint32_t stage = 0, phase = 0;
+    const uint32_t full_leader0 = mapa(bar_full, 0);
+    for (int quad = cluster; quad < num_quads; quad += num_clusters) {
+      for (int step = 0; step < 9; ++step) {
+        const int nks = bwd_ks_count(step), sb = bwd_slab_base(step);
+        for (int x = 0; x < 2; ++x) {
+          for (int ks = 0; ks < nks; ++ks) {
+            mbar_wait_cluster(bar_empty + 8 * stage, phase ^ 1);
+            const int row0 = (sb + ks * 2 + (int)rank) * 128;  // this CTA's 128 output columns
+            if (elect_one()) {
               if (rank == 0) mbar_expect_tx(bar_full + 8 * stage, 2 * kSlabBytes);
-              const uint32_t full_leader = mapa(bar_full + 8 * stage, 0);
+              const uint32_t full_leader = full_leader0 + 8 * stage;
               const uint32_t dst = base + kBSmRing + stage * kSlabBytes;
-              const int row0 = (sb + ks * 2 + (int)rank) * 128;  // this CTA's 128 output columns
               tma_load_2d_2sm(dst, &wmap, 0, row0, full_leader);
               tma_load_2d_2sm(dst + 8192, &wmap, 0, row0 + 64, full_leader);
-              if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
             }
+            __syncwarp();
+            if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
           }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && rank == 0) {
+    if (rank == 0) {
       const uint32_t idesc = make_idesc_bf16(256, 256);
+      const uint64_t desc0 = make_desc_kmajor_sw128(0);
       uint32_t stage = 0, phase = 0, par_act0 = 0, par_act1 = 0;
       for (int quad = cluster; quad < num_quads; quad += num_clusters) {
         for (int step = 0; step < 9; ++step) {
@@ -202,16 +209,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
             tc_fence_after();
             const uint32_t d = tmem + x * 256;
             for (int ks = 0; ks < nks; ++ks) {
-              const uint64_t adesc = make_desc_kmajor_sw128(sAct + ks * kSlabBytes);
+              const uint64_t adesc = desc0 | (uint64_t)(((sAct + ks * kSlabBytes) & 0x3FFFFu) >> 4);
+              const uint64_t bdesc = desc0 | (uint64_t)(((base + kBSmRing + stage * kSlabBytes) & 0x3FFFFu) >> 4);
               mbar_wait_cluster(bar_full + 8 * stage, phase);
               tc_fence_after();
-              const uint64_t bdesc = make_desc_kmajor_sw128(base + kBSmRing + stage * kSlabBytes);
-              for (int k16 = 0; k16 < 4; ++k16)
-                umma_bf16_2sm(d, adesc + 2 * k16, bdesc + 2 * k16, idesc, (ks | k16) != 0);
-              umma_commit_2sm(bar_empty + 8 * stage);
+              if (elect_one()) {
+                umma_bf16_2sm(d, adesc, bdesc, idesc, ks != 0);
+                umma_bf16_2sm(d, adesc + 2, bdesc + 2, idesc, 1);
+                umma_bf16_2sm(d, adesc + 4, bdesc + 4, idesc, 1);
+                umma_bf16_2sm(d, adesc + 6, bdesc + 6, idesc, 1);
+                umma_commit_2sm(bar_empty + 8 * stage);
+                if (ks == nks - 1) umma_commit_2sm(bar_acc + 8 * x);
+              }
+              __syncwarp();
               if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
             }
-            umma_commit_2sm(bar_acc + 8 * x);
           }
         }
       }
@@ -352,7 +364,7 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, const uin
   uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t bar_full = base + kWSmBar, bar_empty = bar_full + 8 * kWStages, bar_acc = bar_empty + 8 * kWStages,
                  bar_flush = bar_acc + 8;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kWStages; ++i) {
       mbar_init(bar_full + 8 * i, 1);
@@ -371,65 +383,71 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, const uin
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kWSmTmemPtr);
 
+  // producer and MMA warps run converged and issue under elect.sync (see mlp_tc.cu)
   if (warp == 0) {
-    if (lane == 0) {
-      uint32_t stage = 0, phase = 0;
-      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-        const WJob j = jobs.job[u % kNumWJobs];
-        const int t0 = (u / kNumWJobs) * tiles_per_unit;
-        const int t1 = min(t0 + tiles_per_unit, num_tiles);
-        const int na = j.m_blocks * 2, nb_ = j.n_cols / 64;
-        for (int t = t0; t < t1; ++t) {
-          const uint8_t* da_t = dA + (size_t)t * kDaSlabs * kSlabBytes + (size_t)j.a_slab * kSlabBytes;
-          const uint8_t* ac_t = acts + (size_t)t * kActSlabs * kSlabBytes + (size_t)j.b_slab * kSlabBytes;
-          for (int half = 0; half < 2; ++half) {
-            mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+    uint32_t stage = 0, phase = 0;
+    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+      const WJob& j = jobs.job[u % kNumWJobs];
+      const int t0 = (u / kNumWJobs) * tiles_per_unit;
+      const int t1 = min(t0 + tiles_per_unit, num_tiles);
+      const int na = j.m_blocks * 2, nb_ = j.n_cols / 64;
+      for (int t = t0; t < t1; ++t) {
+        const uint8_t* da_t = dA + (size_t)t * kDaSlabs * kSlabBytes + (size_t)j.a_slab * kSlabBytes;
+        const uint8_t* ac_t = acts + (size_t)t * kActSlabs * kSlabBytes + (size_t)j.b_slab * kSlabBytes;
+        for (int half = 0; half < 2; ++half) {
+          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+          if (elect_one()) {
             mbar_expect_tx(bar_full + 8 * stage, (na + nb_) * 8192);
             const uint32_t dst = base + stage * kWStageBytes;
             for (int s = 0; s < na; ++s)
               bulk_g2s(dst + s * 8192, da_t + (size_t)s * kSlabBytes + half * 8192, 8192, bar_full + 8 * stage);
             for (int s = 0; s < nb_; ++s)
               bulk_g2s(dst + (na + s) * 8192, ac_t + (size_t)s * kSlabBytes + half * 8192, 8192, bar_full + 8 * stage);
-            if (++stage == kWStages) { stage = 0; phase ^= 1; }
           }
+          __syncwarp();
+          if (++stage == kWStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      uint32_t stage = 0, phase = 0, par_flush = 0;
-      bool first_unit = true;
-      for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-        const WJob j = jobs.job[u % kNumWJobs];
-        const int t0 = (u / kNumWJobs) * tiles_per_unit;
-        const int t1 = min(t0 + tiles_per_unit, num_tiles);
-        const int na = j.m_blocks * 2;
-        const uint32_t idesc = make_idesc_bf16_mn(128, j.n_cols);
-        if (!first_unit) {  // the previous unit's accumulators must be drained before they are overwritten
-          mbar_wait(bar_flush, par_flush);
-          par_flush ^= 1;
+    uint32_t stage = 0, phase = 0, par_flush = 0;
+    bool first_unit = true;
+    const uint64_t desc0 = make_desc_mnmajor_sw128(0, 8192);
+    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
+      const WJob& j = jobs.job[u % kNumWJobs];
+      const int t0 = (u / kNumWJobs) * tiles_per_unit;
+      const int t1 = min(t0 + tiles_per_unit, num_tiles);
+      const int na = j.m_blocks * 2;
+      const uint32_t idesc = make_idesc_bf16_mn(128, j.n_cols);
+      if (!first_unit) {  // the previous unit's accumulators must be drained before they are overwritten
+        mbar_wait(bar_flush, par_flush);
+        par_flush ^= 1;
+        tc_fence_after();
+      }
+      first_unit = false;
+      uint32_t acc = 0;
+      for (int t = t0; t < t1; ++t) {
+        for (int half = 0; half < 2; ++half) {
+          mbar_wait(bar_full + 8 * stage, phase);
           tc_fence_after();
-        }
-        first_unit = false;
-        bool acc = false;
-        for (int t = t0; t < t1; ++t) {
-          for (int half = 0; half < 2; ++half) {
-            mbar_wait(bar_full + 8 * stage, phase);
-            tc_fence_after();
-            const uint32_t sa = base + stage * kWStageBytes, sb = sa + na * 8192;
+          const uint32_t sa = base + stage * kWStageBytes, sb = sa + na * 8192;
+          const uint64_t ad0 = desc0 | (uint64_t)((sa & 0x3FFFFu) >> 4), bd0 = desc0 | (uint64_t)((sb & 0x3FFFFu) >> 4);
+          if (elect_one()) {
             for (int mb = 0; mb < j.m_blocks; ++mb) {
-              for (int k16 = 0; k16 < 4; ++k16) {
-                const uint64_t ad = make_desc_mnmajor_sw128(sa + mb * 2 * 8192 + k16 * 2048, 8192);
-                const uint64_t bd = make_desc_mnmajor_sw128(sb + k16 * 2048, 8192);
-                umma_bf16(tmem + mb * j.n_cols, ad, bd, idesc, (acc || k16 != 0) ? 1u : 0u);
-              }
+              const uint32_t d = tmem + mb * j.n_cols;
+              const uint64_t ad = ad0 + (uint64_t)(mb * (2 * 8192 >> 4));
+              umma_bf16(d, ad, bd0, idesc, acc);
+              umma_bf16(d, ad + (2048 >> 4), bd0 + (2048 >> 4), idesc, 1);
+              umma_bf16(d, ad + 2 * (2048 >> 4), bd0 + 2 * (2048 >> 4), idesc, 1);
+              umma_bf16(d, ad + 3 * (2048 >> 4), bd0 + 3 * (2048 >> 4), idesc, 1);
             }
-            acc = true;
             umma_commit(bar_empty + 8 * stage);
-            if (++stage == kWStages) { stage = 0; phase ^= 1; }
+            if (t == t1 - 1 && half == 1) umma_commit(bar_acc);
           }
+          __syncwarp();
+          acc = 1;
+          if (++stage == kWStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(bar_acc);
       }
     }
   } else if (warp >= 4 && warp < 8) {

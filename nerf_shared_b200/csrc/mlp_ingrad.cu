@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(192, 1)
   uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t bar_full = base + kISmBar, bar_empty = bar_full + 8 * kInStages, bar_acc = bar_empty + 8 * kInStages,
                  bar_free = bar_acc + 16, bar_w = bar_free + 16;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int i = 0; i < kInStages; ++i) {
       mbar_init(bar_full + 8 * i, 1);
@@ -105,47 +105,57 @@ __global__ void __launch_bounds__(192, 1)
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kISmTmemPtr);
 
+  // producer and MMA warps run converged and issue under elect.sync (see mlp_tc.cu)
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(bar_w, kInSlabs * kInWBytes);
       bulk_g2s(base + kISmW, wblob, kInSlabs * kInWBytes, bar_w);
-      uint32_t stage = 0, phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const uint8_t* dt = dA + (size_t)tile * kDaSlabs * kSlabBytes;
-        for (int j = 0; j < kInSlabs; ++j) {
-          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+    }
+    __syncwarp();
+    uint32_t stage = 0, phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const uint8_t* dt = dA + (size_t)tile * kDaSlabs * kSlabBytes;
+      for (int j = 0; j < kInSlabs; ++j) {
+        mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+        if (elect_one()) {
           mbar_expect_tx(bar_full + 8 * stage, kSlabBytes);
           bulk_g2s(base + kISmRing + stage * kSlabBytes, dt + (size_t)in_da_slab(j) * kSlabBytes, kSlabBytes,
                    bar_full + 8 * stage);
-          if (++stage == kInStages) { stage = 0; phase ^= 1; }
         }
+        __syncwarp();
+        if (++stage == kInStages) { stage = 0; phase ^= 1; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc64 = make_idesc_bf16(128, 64), idesc32 = make_idesc_bf16(128, 32);
-      uint32_t stage = 0, phase = 0, par_free[2] = {0, 0};
-      int it = 0;
-      mbar_wait(bar_w, 0);
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const int b = it & 1;
-        if (it >= 2) {  // accumulator b was used two tiles ago: wait until its epilogue has read it
-          mbar_wait(bar_free + 8 * b, par_free[b]);
-          par_free[b] ^= 1;
-          tc_fence_after();
-        }
-        for (int j = 0; j < kInSlabs; ++j) {
-          mbar_wait(bar_full + 8 * stage, phase);
-          tc_fence_after();
-          const uint64_t ad = make_desc_kmajor_sw128(base + kISmRing + stage * kSlabBytes);
-          const uint64_t bd = make_desc_kmajor_sw128(base + kISmW + j * kInWBytes);
-          const uint32_t d = tmem + b * 128 + (j < 8 ? 0 : 64);
-          for (int k16 = 0; k16 < 4; ++k16)
-            umma_bf16(d, ad + 2 * k16, bd + 2 * k16, j < 8 ? idesc64 : idesc32, ((j & 7) | k16) != 0);
+    const uint32_t idesc64 = make_idesc_bf16(128, 64), idesc32 = make_idesc_bf16(128, 32);
+    const uint64_t desc0 = make_desc_kmajor_sw128(0);
+    uint32_t stage = 0, phase = 0, par_free0 = 0, par_free1 = 0;
+    int it = 0;
+    mbar_wait(bar_w, 0);
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int b = it & 1;
+      if (it >= 2) {  // accumulator b was used two tiles ago: wait until its epilogue has read it
+        if (b == 0) { mbar_wait(bar_free, par_free0); par_free0 ^= 1; }
+        else { mbar_wait(bar_free + 8, par_free1); par_free1 ^= 1; }
+        tc_fence_after();
+      }
+      for (int j = 0; j < kInSlabs; ++j) {
+        mbar_wait(bar_full + 8 * stage, phase);
+        tc_fence_after();
+        const uint64_t ad = desc0 | (uint64_t)(((base + kISmRing + stage * kSlabBytes) & 0x3FFFFu) >> 4);
+        const uint64_t bd = desc0 | (uint64_t)(((base + kISmW + j * kInWBytes) & 0x3FFFFu) >> 4);
+        const uint32_t d = tmem + b * 128 + (j < 8 ? 0 : 64);
+        const uint32_t idesc = j < 8 ? idesc64 : idesc32;
+        if (elect_one()) {
+          umma_bf16(d, ad, bd, idesc, (j & 7) != 0);
+          umma_bf16(d, ad + 2, bd + 2, idesc, 1);
+          umma_bf16(d, ad + 4, bd + 4, idesc, 1);
+          umma_bf16(d, ad + 6, bd + 6, idesc, 1);
           umma_commit(bar_empty + 8 * stage);
-          if (++stage == kInStages) { stage = 0; phase ^= 1; }
+          if (j == kInSlabs - 1) umma_commit(bar_acc + 8 * b);
         }
-        umma_commit(bar_acc + 8 * b);
+        __syncwarp();
+        if (++stage == kInStages) { stage = 0; phase ^= 1; }
       }
     }
   } else {
