@@ -179,7 +179,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
         const int nks = bwd_ks_count(step), sb = bwd_slab_base(step);
         for (int x = 0; x < 2; ++x) {
           for (int ks = 0; ks < nks; ++ks) {
-            mbar_wait_cluster(bar_empty + 8 * stage, phase ^ 1);
+            mbar_wait(bar_empty + 8 * stage, phase ^ 1);
             const int row0 = (sb + ks * 2 + (int)rank) * 128;  // this CTA's 128 output columns
             if (elect_one()) {
               if (rank == 0) mbar_expect_tx(bar_full + 8 * stage, 2 * kSlabBytes);
@@ -211,7 +211,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
             for (int ks = 0; ks < nks; ++ks) {
               const uint64_t adesc = desc0 | (uint64_t)(((sAct + ks * kSlabBytes) & 0x3FFFFu) >> 4);
               const uint64_t bdesc = desc0 | (uint64_t)(((base + kBSmRing + stage * kSlabBytes) & 0x3FFFFu) >> 4);
-              mbar_wait_cluster(bar_full + 8 * stage, phase);
+              mbar_wait(bar_full + 8 * stage, phase);
               tc_fence_after();
               if (elect_one()) {
                 umma_bf16_2sm(d, adesc, bdesc, idesc, ks != 0);
@@ -283,11 +283,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       }
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(act_leader);
+      if (lane == 0) mbar_arrive_remote(act_leader);
       flush(kDaSlabHv, 2);
 #pragma unroll 1
       for (int step = 0; step < 9; ++step) {
-        mbar_wait_cluster(my_acc, par_acc);
+        mbar_wait(my_acc, par_acc);
         par_acc ^= 1;
         tc_fence_after();
         reuse();
@@ -305,7 +305,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
         fence_proxy_async();
         tc_fence_before();
         __syncwarp();
-        if (step < 8 && lane == 0) mbar_arrive_cluster(act_leader);
+        if (step < 8 && lane == 0) mbar_arrive_remote(act_leader);
         flush(dst_slab, 4);
       }
     }

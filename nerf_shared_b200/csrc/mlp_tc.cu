@@ -268,6 +268,16 @@ __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __re
 //   empty[s]  per CTA: the MMAs reading stage s retired (tcgen05.commit multicast to both CTAs)
 //   act[x]    leader only: tile x's A operand is written in both CTAs (8 warp arrivals, 4 remote)
 //   acc[x]    per CTA: tile x's accumulator is complete (tcgen05.commit multicast)
+#ifdef NB_TRACE
+// timing experiments (make EXTRA_FLAGS=-DNB_TRACE): SM-clock timestamps of CTA 0's first quads,
+// slot = ((quad_iter * 10 + layer) * 2 + x) * 8 + event
+__device__ long long g_trace[4 * 10 * 2 * 8];
+#define NB_TR(qi, layer, x, ev) \
+  do { if (blockIdx.x == 0 && (qi) < 4) g_trace[((((qi) * 10 + (layer)) * 2 + (x)) << 3) + (ev)] = clock64(); } while (0)
+#else
+#define NB_TR(qi, layer, x, ev)
+#endif
+
 template <int L_PTS, int L_DIRS>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
     mlp_fwd_tc_kernel(const __grid_constant__ CUtensorMap wmap, const uint8_t* __restrict__ blob,
@@ -325,7 +335,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
         const uint32_t half_bytes = layer == 9 ? 8192u : 16384u;
         for (int x = 0; x < 2; ++x) {
           for (int ks = 0; ks < nks; ++ks) {
-            mbar_wait_cluster(bar_empty + 8 * stage, phase ^ 1);
+            mbar_wait(bar_empty + 8 * stage, phase ^ 1);
             // layers 0..8: slab (ks, nh = rank), 128 rows; layer 9 (N = 128): rows 64*rank.. of slab ks
             const int row0 = layer == 9 ? (sb + ks) * 128 + 64 * (int)rank : (sb + ks * 2 + (int)rank) * 128;
             if (elect_one()) {
@@ -347,7 +357,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       const uint32_t idesc256 = make_idesc_bf16(256, 256), idesc128 = make_idesc_bf16(256, 128);
       const uint64_t desc0 = make_desc_kmajor_sw128(0);
       uint32_t stage = 0, phase = 0, par_act0 = 0, par_act1 = 0;
+      int qi = -1;
       for (int quad = cluster; quad < num_quads; quad += num_clusters) {
+        ++qi;
         for (int layer = 0; layer < 10; ++layer) {
           const int nks = ks_count(layer);
           const uint32_t idesc = layer == 9 ? idesc128 : idesc256;
@@ -356,6 +368,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
             if (x == 0) { mbar_wait_cluster(bar_act, par_act0); par_act0 ^= 1; }
             else { mbar_wait_cluster(bar_act + 8, par_act1); par_act1 ^= 1; }
             tc_fence_after();
+            if (lane == 0) NB_TR(qi, layer, x, 0);
             const uint32_t d = tmem + x * 256;
             for (int ks = 0; ks < nks; ++ks) {
               uint32_t a_addr;
@@ -366,7 +379,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
               const bool half_k = layer == 9 && ks == 4;   // 32-wide view encoding: two K=16 steps
               const uint64_t adesc = desc0 | (uint64_t)((a_addr & 0x3FFFFu) >> 4);
               const uint64_t bdesc = desc0 | (uint64_t)(((base + kSmRing + stage * kSlabBytes) & 0x3FFFFu) >> 4);
-              mbar_wait_cluster(bar_full + 8 * stage, phase);
+              mbar_wait(bar_full + 8 * stage, phase);
               tc_fence_after();
               if (elect_one()) {
                 umma_bf16_2sm(d, adesc, bdesc, idesc, ks != 0);
@@ -381,6 +394,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
               __syncwarp();
               if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
+            if (lane == 0) NB_TR(qi, layer, x, 1);
           }
         }
       }
@@ -394,7 +408,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
     const uint32_t act_leader = mapa(bar_act + 8 * x, 0), my_acc = bar_acc + 8 * x;
     uint32_t par_acc = 0;
     mbar_wait(bar_const, 0);
+    int qi = -1;
     for (int quad = cluster; quad < num_quads; quad += num_clusters) {
+      ++qi;
       const int64_t tile = (int64_t)quad * 4 + rank * 2 + x;
       const int64_t m = tile * kTileM + row;
       const bool valid = m < M;
@@ -426,14 +442,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       }
       fence_proxy_async();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(act_leader);
+      if (lane == 0) mbar_arrive_remote(act_leader);
       flush(sEnc, kActSlabEncP, 1);
       float sigma = cst[kOffAlphaB];
 #pragma unroll 1
       for (int layer = 0; layer < 9; ++layer) {
-        mbar_wait_cluster(my_acc, par_acc);
+        mbar_wait(my_acc, par_acc);
         par_acc ^= 1;
         tc_fence_after();
+        if ((warp & 3) == 0 && lane == 0) NB_TR(qi, layer, x, 2);
         reuse();
         if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, sigma);
         else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, sigma);
@@ -450,14 +467,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
           encode3<L_DIRS>(v0, v1, v2, e);
           store_operand_row(sEnc, row, e);
         }
+        if ((warp & 3) == 0 && lane == 0) NB_TR(qi, layer, x, 3);
         fence_proxy_async();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(act_leader);
+        if (lane == 0) mbar_arrive_remote(act_leader);
+        if ((warp & 3) == 0 && lane == 0) NB_TR(qi, layer, x, 4);
         flush(sAct, layer * 4, 4);
         if (layer == 8) flush(sEnc, kActSlabEncD, 1);
       }
-      mbar_wait_cluster(my_acc, par_acc);
+      mbar_wait(my_acc, par_acc);
       par_acc ^= 1;
       tc_fence_after();
       reuse();
@@ -562,6 +581,12 @@ int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, c
       wmap, (const uint8_t*)packed, pts, viewdirs, M, S, raw, (uint8_t*)acts, (int)quads);
   return check_launch("nb_mlp_fwd_tc");
 }
+
+#ifdef NB_TRACE
+__attribute__((visibility("default"))) int nb_trace_read(long long* out_host) {
+  return (int)cudaMemcpyFromSymbol(out_host, g_trace, sizeof(long long) * 4 * 10 * 2 * 8);
+}
+#endif
 
 // test hook: D[128,128] = A[128,K] B[128,K]^T with bf16-rounded operands (K in {64,128,192,256})
 int nb_debug_umma(const float* A, const float* B, int K, float* D, void* stream) {

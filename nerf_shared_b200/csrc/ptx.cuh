@@ -89,6 +89,13 @@ __device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// Remote arrive with the default (CTA-scope release) semantics, as CUTLASS's ClusterBarrier::arrive(cta_id):
+// no MEMBAR.GPU in front of it (~1000 cycles on the epilogue -> MMA chain).  The writer has already made its
+// shared-memory stores visible to the async proxy with fence.proxy.async, which completes them in its own SM
+// before the arrive leaves for the peer.
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait_cluster(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(

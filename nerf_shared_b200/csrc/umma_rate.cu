@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int mode, int iters, 
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(gbase + kRSmPtr);
   const uint32_t rank = CG == 2 ? cluster_ctarank() : 0;
   const int N = (mode == 2 || mode == 3) ? 128 : 256;
-  if (threadIdx.x == 0 && rank == 0) {
+  if (mode < 8 && threadIdx.x == 0 && rank == 0) {
     const uint32_t idesc = make_idesc_bf16(CG == 2 ? 256 : 128, N);
     const long long t0 = clock64();
     for (int i = 0; i < (mode >= 5 ? 0 : iters); ++i) {
@@ -87,7 +87,7 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int mode, int iters, 
     const long long t2 = clock64();
     cycles[2 * (blockIdx.x / CG)] = t2 - t0;
     cycles[2 * (blockIdx.x / CG) + 1] = t1 - t0;
-  } else if (threadIdx.x == 0 && CG == 2) {
+  } else if (mode < 8 && threadIdx.x == 0 && CG == 2) {
     mbar_wait(bar, 0);  // the multicast commit also arrives here: keep the peer alive until the MMAs are done
   } else if (CG == 2 && mode == 7 && threadIdx.x == 32) {
     // producer of the fused kernels without the copy: stage free in this CTA -> (leader) signal it full
@@ -96,6 +96,31 @@ __global__ void __launch_bounds__(128, 1) umma_rate_kernel(int mode, int iters, 
       const int st = g % 3;
       mbar_wait_cluster(bar_e + 8 * st, ((g / 3) & 1) ^ 1);
       if (rank == 0) mbar_arrive(bar_f + 8 * st);
+    }
+  }
+  if (mode == 8 || mode == 9) {
+    // tcgen05.ld throughput: mode 8 = all four warps, mode 9 = warp 0 alone; each reads its 32 lanes x 256
+    // columns (32 KB per warp and iteration) `iters` times
+    __syncthreads();
+    if (mode == 8 || warp == 0) {
+      const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16);
+      uint32_t sink = 0;
+      const long long t0 = clock64();
+      for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          uint32_t v[32];
+          tmem_ld32(taddr + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 32; ++q) sink ^= v[q];
+        }
+      }
+      const long long t1 = clock64();
+      if ((threadIdx.x & 31) == 0 && (CG == 1 || rank == 0)) {
+        cycles[2 * (blockIdx.x / CG)] = t1 - t0;
+        cycles[2 * (blockIdx.x / CG) + 1] = sink;
+      }
     }
   }
   tc_fence_before();
@@ -113,7 +138,7 @@ extern "C" {
 
 // cycles: 2 int64 per CTA (pair): [total incl. drain, issue only]
 int nb_debug_umma_rate(int mode, int iters, int ctas, long long* cycles, void* stream) {
-  NB_REQUIRE(cycles && iters > 0 && mode >= 0 && mode <= 7 && ctas >= 1 && ctas <= kNumSMs, "nb_debug_umma_rate: bad arguments");
+  NB_REQUIRE(cycles && iters > 0 && mode >= 0 && mode <= 9 && ctas >= 1 && ctas <= kNumSMs, "nb_debug_umma_rate: bad arguments");
   cudaError_t e;
   if (mode == 0 || mode == 2 || mode >= 4) {
     e = cudaFuncSetAttribute(umma_rate_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRSmemBytes);
