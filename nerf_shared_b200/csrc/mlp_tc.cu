@@ -16,8 +16,9 @@
 // shared-memory image the UMMA descriptor expects, in consumption order, and streamed
 // L2 -> SMEM with 1-D bulk async copies through a 3-stage mbarrier ring.
 //
-// Warp roles (384 threads): warp 0 = weight producer, warp 1 = MMA issuer, warp 2 = TMEM
-// allocator, warps 4-7 = epilogue of tile A, warps 8-11 = epilogue of tile B.
+// Warp roles (640 threads): warp 0 = weight producer, warp 1 = MMA issuer, warp 2 = TMEM
+// allocator, warps 4-11 = epilogue of tile A, warps 12-19 = epilogue of tile B (two warps per TMEM lane
+// quarter, each taking half of the 256 accumulator columns).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "mlp_common.cuh"
@@ -43,7 +44,9 @@ constexpr uint32_t kSmRing = 163840;
 constexpr uint32_t kSmConst = kSmRing + kStages * kSlabBytes;  // 212992
 constexpr uint32_t kSmBar = kSmConst + kConstFloats * 4;       // 225792
 constexpr uint32_t kSmTmemPtr = kSmBar + 120;
-constexpr uint32_t kSmemBytes = kSmBar + 128 + 1024;           // + alignment slack
+constexpr uint32_t kSmPart = kSmBar + 128;                     // [2 tiles][128 rows] float4 head partial sums
+constexpr uint32_t kSmemBytes = kSmPart + 4096 + 1024;         // + alignment slack
+constexpr int kFwdThreads = 640;                               // 4 control warps + 16 epilogue warps
 
 __host__ __device__ constexpr int ks_count(int layer) { return layer == 0 ? 1 : ((layer == 5 || layer == 9) ? 5 : 4); }
 __host__ __device__ constexpr int nh_count(int layer) { return layer == 9 ? 1 : 2; }
@@ -173,21 +176,28 @@ __device__ __forceinline__ void store_operand_row(uint32_t slab, int row, const 
 // epilogues: TMEM accumulator row -> bias (+relu) -> bf16 -> next layer's A operand in SMEM
 // ------------------------------------------------------------------------------------------
 // MODE 0: relu hidden layer; 1: relu hidden layer + fp32 sigma head; 2: linear (feature layer)
+// A warp handles `nchunks` 32-column chunks starting at chunk `cbeg` of its 32 rows (two warps share a
+// lane quarter and split the 256 columns).  The bias row of a chunk is fetched between the TMEM load and
+// its wait, so the shared-memory latency hides behind the tcgen05.ld.
 template <int MODE>
 __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __restrict__ bias,
-                                                const float* __restrict__ alpha_w, uint32_t act, int row,
+                                                const float* __restrict__ alpha_w, uint32_t act, int row, int cbeg,
                                                 float& sigma) {
 #pragma unroll
-  for (int c = 0; c < 8; ++c) {
+  for (int cc = 0; cc < 4; ++cc) {
+    const int c = cbeg + cc;
     uint32_t v[32];
     tmem_ld32(taddr + c * 32, v);
+    float4 bq[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) bq[j] = *reinterpret_cast<const float4*>(bias + c * 32 + j * 4);
     tmem_ld_wait();
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       float f[8];
 #pragma unroll
       for (int j = 0; j < 8; j += 4) {
-        float4 b = *reinterpret_cast<const float4*>(bias + c * 32 + g * 8 + j);
+        const float4 b = bq[g * 2 + (j >> 2)];
         f[j] = __uint_as_float(v[g * 8 + j]) + b.x;
         f[j + 1] = __uint_as_float(v[g * 8 + j + 1]) + b.y;
         f[j + 2] = __uint_as_float(v[g * 8 + j + 2]) + b.z;
@@ -217,24 +227,29 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
   }
 }
 
-// view branch: hv = relu(acc + b) (128 wide), rgb = hv . Wrgb^T + b_rgb in fp32 (nerf.py:125-129)
+// view branch: hv = relu(acc + b) (128 wide), rgb = hv . Wrgb^T in fp32 (nerf.py:125-129); this warp's two
+// chunks [cbeg, cbeg + 2), partial sums returned in r / g_ / b_ (the caller adds the bias and the other half)
 __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __restrict__ cst, float& r, float& g_,
-                                               float& b_, int row, uint32_t act, bool save) {
+                                               float& b_, int row, int cbeg, uint32_t act, bool save) {
   const float* bias = cst + kOffViewB;
   const float* wr = cst + kOffRgbW;
-  r = cst[kOffRgbB]; g_ = cst[kOffRgbB + 1]; b_ = cst[kOffRgbB + 2];
+  r = 0.f; g_ = 0.f; b_ = 0.f;
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
+  for (int cc = 0; cc < 2; ++cc) {
+    const int c = cbeg + cc;
     uint32_t v[32];
     tmem_ld32(taddr + c * 32, v);
+    float4 bq[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) bq[j] = *reinterpret_cast<const float4*>(bias + c * 32 + j * 4);
     tmem_ld_wait();
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       float f[8];
 #pragma unroll
       for (int j = 0; j < 8; j += 4) {
-        int col = c * 32 + g * 8 + j;
-        float4 b = *reinterpret_cast<const float4*>(bias + col);
+        const int col = c * 32 + g * 8 + j;
+        const float4 b = bq[g * 2 + (j >> 2)];
         float4 w0 = *reinterpret_cast<const float4*>(wr + col);
         float4 w1 = *reinterpret_cast<const float4*>(wr + 128 + col);
         float4 w2 = *reinterpret_cast<const float4*>(wr + 256 + col);
@@ -252,6 +267,20 @@ __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __re
     }
   }
 }
+
+// chunks [4H, 4H + 4) (32 of the 64 columns) of an operand row from the full encoding
+template <int H>
+__device__ __forceinline__ void store_operand_half(uint32_t slab, int row, const float (&e)[64]) {
+#pragma unroll
+  for (int gg = 0; gg < 4; ++gg) {
+    const int g = 4 * H + gg;
+    const uint32_t p0 = pack_bf16x2(e[8 * g], e[8 * g + 1]), p1 = pack_bf16x2(e[8 * g + 2], e[8 * g + 3]),
+                   p2 = pack_bf16x2(e[8 * g + 4], e[8 * g + 5]), p3 = pack_bf16x2(e[8 * g + 6], e[8 * g + 7]);
+    st_shared_v4(slab + sw128_chunk_off(row, g), p0, p1, p2, p3);
+  }
+}
+
+__device__ __forceinline__ void pair_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
 
 // ------------------------------------------------------------------------------------------
 // the fused forward kernel (CTA pairs, tcgen05 cta_group::2)
@@ -279,7 +308,7 @@ __device__ long long g_trace[4 * 10 * 2 * 8];
 #endif
 
 template <int L_PTS, int L_DIRS>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
     mlp_fwd_tc_kernel(const __grid_constant__ CUtensorMap wmap, const uint8_t* __restrict__ blob,
                       const float* __restrict__ pts, const float* __restrict__ viewdirs, int64_t M, int S,
                       float* __restrict__ raw, uint8_t* __restrict__ acts, int num_quads) {
@@ -299,7 +328,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       mbar_init(bar_empty + 8 * i, 1);  // tcgen05.commit
     }
     for (int x = 0; x < 2; ++x) {
-      mbar_init(bar_act + 8 * x, 8);    // one arrival per epilogue warp of the tile, both CTAs
+      mbar_init(bar_act + 8 * x, 16);   // one arrival per epilogue warp of the tile (8), both CTAs
       mbar_init(bar_acc + 8 * x, 1);    // tcgen05.commit
     }
     mbar_init(bar_const, 1);
@@ -400,12 +429,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       }
     }
   } else if (warp >= 4) {
-    // ---------------- epilogue warps: tile x, row = TMEM lane ----------------
-    const int x = (warp - 4) >> 2;
-    const int row = ((warp & 3) << 5) | lane;
+    // ---------------- epilogue warps: tile x, row = TMEM lane, column half h ----------------
+    // Eight warps per tile: the two warps of a lane quarter split the 256 accumulator columns (h = 0: chunks
+    // 0..3, h = 1: chunks 4..7), which halves the accumulator -> operand latency on the MMA's critical chain.
+    const int x = (warp - 4) >> 3, h = ((warp - 4) >> 2) & 1, q = warp & 3;
+    const int row = (q << 5) | lane;
+    const int pair_id = 1 + x * 4 + q;   // named barrier shared by the two warps of (tile, lane quarter)
     const uint32_t sAct = base + (x ? kSmAct1 : kSmAct0), sEnc = base + (x ? kSmEnc1 : kSmEnc0);
-    const uint32_t taddr = tmem + x * 256 + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t taddr = tmem + x * 256 + ((uint32_t)(q * 32) << 16);
     const uint32_t act_leader = mapa(bar_act + 8 * x, 0), my_acc = bar_acc + 8 * x;
+    float4* part = reinterpret_cast<float4*>(gbase + kSmPart) + x * 128 + row;
     uint32_t par_acc = 0;
     mbar_wait(bar_const, 0);
     int qi = -1;
@@ -415,10 +448,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       const int64_t m = tile * kTileM + row;
       const bool valid = m < M;
       // whole tiles are saved (rows past M hold finite values computed from zero inputs).  The SMEM
-      // operand image IS the saved image, so every warp streams its own 32 rows (4 KB of each slab)
+      // operand image IS the saved image, so every warp streams its own 32 rows of its own two slabs
       // to HBM with bulk async stores; `flush` follows the fence that publishes the rows to the MMA.
       uint8_t* save = (acts && tile * kTileM < M) ? acts + (size_t)tile * kActSlabs * kSlabBytes : nullptr;
-      const uint32_t wrow = (uint32_t)(warp & 3) * 4096u;
+      const uint32_t wrow = (uint32_t)q * 4096u;
       auto flush = [&](uint32_t src_slab0, int dst_slab0, int nslabs) {
         if (save && lane == 0) {
           for (int j = 0; j < nslabs; ++j)
@@ -432,63 +465,89 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
           __syncwarp();
         }
       };
+      // the encoding slab is flushed by the h = 0 warp but written by both: order the other warp's bulk reads /
+      // stores against it with the pair barrier
       reuse();
+      if (save) pair_sync(pair_id);
       {
         float p0 = 0.f, p1 = 0.f, p2 = 0.f;
         if (valid) { p0 = pts[m * 3]; p1 = pts[m * 3 + 1]; p2 = pts[m * 3 + 2]; }
         float e[64];
         encode3<L_PTS>(p0, p1, p2, e);
-        store_operand_row(sEnc, row, e);
+        if (h == 0) store_operand_half<0>(sEnc, row, e);
+        else store_operand_half<1>(sEnc, row, e);
       }
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(act_leader);
-      flush(sEnc, kActSlabEncP, 1);
-      float sigma = cst[kOffAlphaB];
+      if (save) {
+        pair_sync(pair_id);
+        if (h == 0) flush(sEnc, kActSlabEncP, 1);
+      }
+      float sigma = 0.f;
 #pragma unroll 1
       for (int layer = 0; layer < 9; ++layer) {
         mbar_wait(my_acc, par_acc);
         par_acc ^= 1;
         tc_fence_after();
-        if ((warp & 3) == 0 && lane == 0) NB_TR(qi, layer, x, 2);
+        if (q == 0 && h == 0 && lane == 0) NB_TR(qi, layer, x, 2);
         reuse();
-        if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, sigma);
-        else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, sigma);
+        if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, 4 * h, sigma);
+        else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, 4 * h, sigma);
         else {
-          epilogue_hidden<2>(taddr, cst + kOffFeatB, nullptr, sAct, row, sigma);
+          epilogue_hidden<2>(taddr, cst + kOffFeatB, nullptr, sAct, row, 4 * h, sigma);
           // view-direction encoding replaces the position encoding in the auxiliary slab
           // (its last reader, layer 5's MMA, retired before layer 5's accumulator was signalled)
-          float v0 = 0.f, v1 = 0.f, v2 = 0.f;
-          if (valid) {
-            const int64_t ray = m / S;
-            v0 = viewdirs[ray * 3]; v1 = viewdirs[ray * 3 + 1]; v2 = viewdirs[ray * 3 + 2];
+          if (save) pair_sync(pair_id);   // the h = 0 warp's flush of enc(pts) has been waited for (reuse above)
+          if (h == 0) {
+            float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+            if (valid) {
+              const int64_t ray = m / S;
+              v0 = viewdirs[ray * 3]; v1 = viewdirs[ray * 3 + 1]; v2 = viewdirs[ray * 3 + 2];
+            }
+            float e[64];
+            encode3<L_DIRS>(v0, v1, v2, e);
+            store_operand_half<0>(sEnc, row, e);
+          } else {   // columns 32..63 are zero: the wgrad kernel reads the whole 64-wide slab
+#pragma unroll
+            for (int g = 4; g < 8; ++g) st_shared_v4(sEnc + sw128_chunk_off(row, g), 0u, 0u, 0u, 0u);
           }
-          float e[64];   // columns 32..63 are zero: the wgrad kernel reads the whole 64-wide slab
-          encode3<L_DIRS>(v0, v1, v2, e);
-          store_operand_row(sEnc, row, e);
         }
-        if ((warp & 3) == 0 && lane == 0) NB_TR(qi, layer, x, 3);
+        if (q == 0 && h == 0 && lane == 0) NB_TR(qi, layer, x, 3);
         fence_proxy_async();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_remote(act_leader);
-        if ((warp & 3) == 0 && lane == 0) NB_TR(qi, layer, x, 4);
-        flush(sAct, layer * 4, 4);
-        if (layer == 8) flush(sEnc, kActSlabEncD, 1);
+        if (q == 0 && h == 0 && lane == 0) NB_TR(qi, layer, x, 4);
+        flush(sAct + 2 * h * kSlabBytes, layer * 4 + 2 * h, 2);
+        if (layer == 8 && save) {
+          pair_sync(pair_id);
+          if (h == 0) flush(sEnc, kActSlabEncD, 1);
+        }
       }
       mbar_wait(my_acc, par_acc);
       par_acc ^= 1;
       tc_fence_after();
       reuse();
+      if (save) pair_sync(pair_id);   // slab 1 (hv of the h = 1 warp) was flushed as layer 8's output by the h = 0 warp
       float r, g, b;
       // the view-branch hidden layer is staged in the (now idle) activation buffer only to be saved
-      epilogue_views(taddr, cst, r, g, b, row, sAct, save != nullptr);
-      if (valid) *reinterpret_cast<float4*>(raw + m * 4) = make_float4(r, g, b, sigma);
+      epilogue_views(taddr, cst, r, g, b, row, 2 * h, sAct, save != nullptr);
       tc_fence_before();
+      // heads: the h = 1 warp hands its partial sums to the h = 0 warp of the same rows
+      if (h == 1) *part = make_float4(r, g, b, sigma);
+      pair_sync(pair_id);
+      if (h == 0) {
+        const float4 o = *part;
+        if (valid)
+          *reinterpret_cast<float4*>(raw + m * 4) = make_float4(cst[kOffRgbB] + r + o.x, cst[kOffRgbB + 1] + g + o.y,
+                                                                cst[kOffRgbB + 2] + b + o.z, cst[kOffAlphaB] + sigma + o.w);
+      }
+      pair_sync(pair_id);   // the partial slot may be rewritten next iteration
       if (save) {
         fence_proxy_async();
         __syncwarp();
-        flush(sAct, kActSlabHv, 2);
+        flush(sAct + h * kSlabBytes, kActSlabHv + h, 1);
       }
     }
     if (acts && lane == 0) bulk_wait_all();
@@ -577,7 +636,7 @@ int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, c
   int rc = make_slab_tmap(&wmap, packed, kNumSlabs);
   if (rc) return rc;
   const int clusters = (int)(quads < kNumSMs / 2 ? quads : kNumSMs / 2);
-  mlp_fwd_tc_kernel<10, 4><<<2 * clusters, 384, kSmemBytes, as_stream(stream)>>>(
+  mlp_fwd_tc_kernel<10, 4><<<2 * clusters, kFwdThreads, kSmemBytes, as_stream(stream)>>>(
       wmap, (const uint8_t*)packed, pts, viewdirs, M, S, raw, (uint8_t*)acts, (int)quads);
   return check_launch("nb_mlp_fwd_tc");
 }
