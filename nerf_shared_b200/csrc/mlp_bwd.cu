@@ -82,20 +82,26 @@ __device__ __forceinline__ uint32_t relu_mask2(uint32_t d, uint32_t h) {
 }
 
 // MODE 0: plain copy (d_feature); 1: + d_sigma * alpha_w, masked by h7; 2: masked
+// This warp's four chunks [cbeg, cbeg + 4) of its 32 rows (two warps share a lane quarter).  The saved
+// activation that supplies relu' comes from HBM: the rows of chunk cc + 1 are requested before chunk cc is
+// processed, and the caller requests chunk cbeg before it waits for the accumulator (`hm`).
+__device__ __forceinline__ void load_mask_chunk(const uint8_t* __restrict__ mask_src, int row, int c, uint4 (&hm)[4]) {
+#pragma unroll
+  for (int g = 0; g < 4; ++g)
+    hm[g] = *reinterpret_cast<const uint4*>(mask_src + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g));
+}
+
 template <int MODE>
-__device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, int row,
-                                               const uint8_t* __restrict__ mask_src, float d_sigma,
+__device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, int row, int cbeg,
+                                               const uint8_t* __restrict__ mask_src, uint4 (&hm)[4], float d_sigma,
                                                const float* __restrict__ alpha_w) {
 #pragma unroll
-  for (int c = 0; c < 8; ++c) {
-    uint4 hm[4];
-    if (MODE != 0 && mask_src) {
-#pragma unroll
-      for (int g = 0; g < 4; ++g)
-        hm[g] = *reinterpret_cast<const uint4*>(mask_src + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g));
-    }
+  for (int cc = 0; cc < 4; ++cc) {
+    const int c = cbeg + cc;
     uint32_t v[32];
     tmem_ld32(taddr + c * 32, v);
+    uint4 hn[4];
+    if (MODE != 0 && mask_src && cc < 3) load_mask_chunk(mask_src, row, c + 1, hn);
     tmem_ld_wait();
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
@@ -123,13 +129,20 @@ __device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, int
       const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g);
       st_shared_v4(act + off, p0, p1, p2, p3);
     }
+    if (MODE != 0 && mask_src && cc < 3) {
+#pragma unroll
+      for (int g = 0; g < 4; ++g) hm[g] = hn[g];
+    }
   }
 }
+
+__device__ __forceinline__ void pair_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+constexpr int kBwdThreads = 640;  // 4 control warps + 16 epilogue warps (see mlp_tc.cu)
 
 // CTA-pair form (tcgen05 cta_group::2), same protocol as the forward kernel (mlp_tc.cu): M = 256
 // samples per MMA (128 per CTA), each CTA streams its half (128 of the 256 output columns) of every
 // transposed weight slab, a cluster works on a quad of four tiles per iteration.
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
     mlp_dgrad_kernel(const __grid_constant__ CUtensorMap wmap, const uint8_t* __restrict__ blob,
                      const uint8_t* __restrict__ acts, const float* __restrict__ d_raw, int64_t M,
                      uint8_t* __restrict__ dA, int num_quads) {
@@ -149,7 +162,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       mbar_init(bar_empty + 8 * i, 1);
     }
     for (int x = 0; x < 2; ++x) {
-      mbar_init(bar_act + 8 * x, 8);  // one arrival per epilogue warp of the tile, both CTAs
+      mbar_init(bar_act + 8 * x, 16);  // one arrival per epilogue warp of the tile (8), both CTAs
       mbar_init(bar_acc + 8 * x, 1);
     }
     mbar_init(bar_const, 1);
@@ -229,12 +242,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       }
     }
   } else if (warp >= 4) {
-    const int x = (warp - 4) >> 2;
-    const int row = ((warp & 3) << 5) | lane;
+    // eight epilogue warps per tile: lane quarter q, column half h (chunks 4h .. 4h+3 = slabs 2h, 2h+1)
+    const int x = (warp - 4) >> 3, h = ((warp - 4) >> 2) & 1, q = warp & 3;
+    const int row = (q << 5) | lane;
+    const int pair_id = 1 + x * 4 + q;
     const uint32_t sAct = base + (x ? kBSmAct1 : kBSmAct0);
-    const uint32_t taddr = tmem + x * 256 + ((uint32_t)((warp & 3) * 32) << 16);
+    const uint32_t taddr = tmem + x * 256 + ((uint32_t)(q * 32) << 16);
     const uint32_t act_leader = mapa(bar_act + 8 * x, 0), my_acc = bar_acc + 8 * x;
-    const uint32_t wrow = (uint32_t)(warp & 3) * 4096u;
+    const uint32_t wrow = (uint32_t)q * 4096u;
     uint32_t par_acc = 0;
     mbar_wait(bar_const, 0);
     const float* wr = cst;
@@ -245,11 +260,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       const bool real = tile * kTileM < M;
       const uint8_t* at = real ? acts + (size_t)tile * kActSlabs * kSlabBytes : nullptr;
       uint8_t* dt = real ? dA + (size_t)tile * kDaSlabs * kSlabBytes : nullptr;
-      // every warp streams its own 32 rows (4 KB of each slab) of the freshly written dA tile to HBM
-      auto flush = [&](int dst_slab0, int nslabs) {
+      // every warp streams its own 32 rows (4 KB of each of its slabs) of the freshly written dA tile to HBM
+      auto flush = [&](int src_slab0, int dst_slab0, int nslabs) {
         if (dt && lane == 0) {
           for (int j = 0; j < nslabs; ++j)
-            bulk_s2g(dt + (size_t)(dst_slab0 + j) * kSlabBytes + wrow, sAct + j * kSlabBytes + wrow, 4096);
+            bulk_s2g(dt + (size_t)(dst_slab0 + j) * kSlabBytes + wrow, sAct + (src_slab0 + j) * kSlabBytes + wrow, 4096);
           bulk_commit();
         }
       };
@@ -260,21 +275,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
       if (m < M) g = *reinterpret_cast<const float4*>(d_raw + m * 4);
       reuse();
-      // prologue: d(view hidden) = (d_rgb . W_rgb) * relu'(hv)   (nerf.py:125-129 backwards)
+      pair_sync(pair_id);   // slab 1 below belongs to the h = 1 warp; step 8 of the previous quad flushed it from h = 0
+      // prologue: d(view hidden) = (d_rgb . W_rgb) * relu'(hv)   (nerf.py:125-129 backwards); chunks 2h, 2h+1
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = 2 * h + cc;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int col = c * 32 + q * 8;
+        for (int qq = 0; qq < 4; ++qq) {
+          const int col = c * 32 + qq * 8;
           float f[8];
 #pragma unroll
           for (int j = 0; j < 8; ++j) f[j] = g.x * wr[col + j] + g.y * wr[128 + col + j] + g.z * wr[256 + col + j];
           uint32_t p0 = pack_bf16x2(f[0], f[1]), p1 = pack_bf16x2(f[2], f[3]), p2 = pack_bf16x2(f[4], f[5]),
                    p3 = pack_bf16x2(f[6], f[7]);
-          const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + q);
+          const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + qq);
           if (at) {
-            const uint4 h = *reinterpret_cast<const uint4*>(at + (size_t)kActSlabHv * kSlabBytes + off);
-            p0 = relu_mask2(p0, h.x); p1 = relu_mask2(p1, h.y); p2 = relu_mask2(p2, h.z); p3 = relu_mask2(p3, h.w);
+            const uint4 hh = *reinterpret_cast<const uint4*>(at + (size_t)kActSlabHv * kSlabBytes + off);
+            p0 = relu_mask2(p0, hh.x); p1 = relu_mask2(p1, hh.y); p2 = relu_mask2(p2, hh.z); p3 = relu_mask2(p3, hh.w);
           } else {
             p0 = p1 = p2 = p3 = 0u;
           }
@@ -284,29 +301,32 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(act_leader);
-      flush(kDaSlabHv, 2);
+      flush(h, kDaSlabHv + h, 1);
 #pragma unroll 1
       for (int step = 0; step < 9; ++step) {
+        const int l = 8 - step;  // step >= 1 produces d_a_l, masked by h_l: step 1 -> l = 7 ... step 8 -> l = 0
+        const uint8_t* ms = (step > 0 && at) ? at + (size_t)l * 4 * kSlabBytes : nullptr;
+        uint4 hm[4];
+        if (ms) load_mask_chunk(ms, row, 4 * h, hm);   // in flight while the MMAs of this step run
         mbar_wait(my_acc, par_acc);
         par_acc ^= 1;
         tc_fence_after();
         reuse();
+        if (step == 0) pair_sync(pair_id);   // slab 1 was flushed (d hv) by the h = 1 warp, h = 0 overwrites it now
         int dst_slab;
         if (step == 0) {
-          dgrad_epilogue<0>(taddr, sAct, row, nullptr, 0.f, nullptr);
+          dgrad_epilogue<0>(taddr, sAct, row, 4 * h, nullptr, hm, 0.f, nullptr);
           dst_slab = kDaSlabFeat;
         } else {
-          const int l = 8 - step;  // produces d_a_l, masked by h_l: step 1 -> l = 7 ... step 8 -> l = 0
-          const uint8_t* ms = at ? at + (size_t)l * 4 * kSlabBytes : nullptr;
-          if (step == 1) dgrad_epilogue<1>(taddr, sAct, row, ms, g.w, wa);
-          else dgrad_epilogue<2>(taddr, sAct, row, ms, 0.f, nullptr);
+          if (step == 1) dgrad_epilogue<1>(taddr, sAct, row, 4 * h, ms, hm, g.w, wa);
+          else dgrad_epilogue<2>(taddr, sAct, row, 4 * h, ms, hm, 0.f, nullptr);
           dst_slab = l * 4;
         }
         fence_proxy_async();
         tc_fence_before();
         __syncwarp();
         if (step < 8 && lane == 0) mbar_arrive_remote(act_leader);
-        flush(dst_slab, 4);
+        flush(2 * h, dst_slab + 2 * h, 2);
       }
     }
     if (lane == 0) bulk_wait_all();
@@ -757,7 +777,7 @@ int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* act
     int rc = make_slab_tmap(&wmap, packed_bwd, kBwdSlabs);
     if (rc) return rc;
     const int clusters = (int)(quads < kNumSMs / 2 ? quads : kNumSMs / 2);
-    mlp_dgrad_kernel<<<2 * clusters, 384, kBSmemBytes, st>>>(wmap, (const uint8_t*)packed_bwd, (const uint8_t*)acts, d_raw,
+    mlp_dgrad_kernel<<<2 * clusters, kBwdThreads, kBSmemBytes, st>>>(wmap, (const uint8_t*)packed_bwd, (const uint8_t*)acts, d_raw,
                                                              M, (uint8_t*)dA, (int)quads);
     rc = check_launch("mlp_dgrad_kernel");
     if (rc) return rc;
