@@ -201,21 +201,25 @@ def run_b200(a):
     # ---- end to end through the public API (e2e) -----------------------------------------------
     # host images (pinned) -> utils.sample_random_ray_batch (pixel ids + targets H2D) -> graphed step ->
     # loss.item() (D2H) every step
-    def e2e_step(i, fn):
-        batch_rays, target, _, _ = utils.sample_random_ray_batch(args, images_pinned, poses_d, None, a.rays, False, None,
-                                                                 i_train, hwf, K, 0, i + 1)
-        out = fn(batch_rays, target)
-        return float((out[0] if isinstance(out, tuple) else out).item())
+    def sample(i):
+        return utils.sample_random_ray_batch(args, images_pinned, poses_d, None, a.rays, False, None, i_train, hwf, K, 0, i + 1)
 
     def time_e2e(fn):
-        for i in range(3):
-            e2e_step(i, fn)
+        """Per step: host batch sampling (pixel ids + targets gathered on the host, H2D from pinned memory), the
+        step, and a D2H read of that step's loss.  The next batch is sampled while the GPU runs the current
+        step (what a training loop does); the loss of EVERY step is still read back before the next launch."""
+        def loop(k):
+            batch_rays, target, _, _ = sample(0)
+            for i in range(k):
+                out = fn(batch_rays, target)
+                batch_rays, target, _, _ = sample(i + 1)          # overlaps the step on the GPU
+                float((out[0] if isinstance(out, tuple) else out).item())   # D2H of this step's loss
+        loop(3)
         sync_all()
         t0 = time.perf_counter()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for i in range(a.steps):
-            e2e_step(i, fn)
+        loop(a.steps)
         e1.record()
         sync_all()
         ms = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3) / a.steps

@@ -19,7 +19,8 @@ struct SampleTerms {
   float z;
 };
 
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+// ex2.approx + rcp.approx: relative error < 1e-6 (the maps are compared at 2e-5); exp() of the opacity stays exact
+__device__ __forceinline__ float sigmoidf_(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
 
 __device__ __forceinline__ SampleTerms load_terms(const float* __restrict__ raw, const float* __restrict__ z,
                                                   const float* __restrict__ noise, int64_t base, int s, int S,
@@ -67,6 +68,52 @@ __device__ __forceinline__ float warp_excl_suffix_sum(float v, int lane, float& 
   return inc - v;
 }
 
+// terms of one sample from values already in registers (z_next = depth of the following sample)
+__device__ __forceinline__ SampleTerms make_terms(const float4& r, float zz, float z_next, bool last, bool valid, float nz,
+                                                  float dnorm) {
+  SampleTerms t;
+  if (valid) {
+    t.z = zz;
+    t.dz = last ? 1e10f : (z_next - zz);
+    t.dist = t.dz * dnorm;
+    t.rs = fmaxf(r.w + nz, 0.0f);
+    t.alpha = 1.0f - expf(-t.rs * t.dist);
+    t.q = 1.0f - t.alpha + 1e-10f;
+    t.c0 = sigmoidf_(r.x); t.c1 = sigmoidf_(r.y); t.c2 = sigmoidf_(r.z);
+  } else {
+    t.c0 = t.c1 = t.c2 = 0.f; t.alpha = 0.f; t.q = 1.0f; t.rs = 0.f; t.dist = 0.f; t.dz = 0.f; t.z = 0.f;
+  }
+  return t;
+}
+
+// All C 32-sample chunks of a ray are requested before any arithmetic (C x 640 B in flight per warp), and the
+// depth of the following sample comes from the neighbouring lane instead of a second, misaligned load.
+template <int C>
+__device__ __forceinline__ void load_ray(const float* __restrict__ raw, const float* __restrict__ z,
+                                         const float* __restrict__ noise, int64_t base, int S, int lane, float4 (&r)[C],
+                                         float (&zz)[C], float (&zn)[C], float (&nz)[C]) {
+#pragma unroll
+  for (int j = 0; j < C; ++j) {
+    const int s = j * 32 + lane;
+    if (s < S) {
+      r[j] = __ldcs(reinterpret_cast<const float4*>(raw + (base + s) * 4));
+      zz[j] = z[base + s];
+      nz[j] = noise ? noise[base + s] : 0.f;
+    } else {
+      r[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+      zz[j] = 0.f;
+      nz[j] = 0.f;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < C; ++j) {
+    float nx = __shfl_down_sync(0xffffffffu, zz[j], 1);
+    const float first_of_next = __shfl_sync(0xffffffffu, j + 1 < C ? zz[j + 1 < C ? j + 1 : j] : 0.f, 0);
+    zn[j] = lane == 31 ? first_of_next : nx;
+  }
+}
+
+template <int C>
 __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restrict__ raw,
                                                             const float* __restrict__ z,
                                                             const float* __restrict__ rays_d,
@@ -79,18 +126,22 @@ __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restr
   int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t r = warp; r < n; r += nwarps) {
     float d0 = rays_d[r * 3], d1 = rays_d[r * 3 + 1], d2 = rays_d[r * 3 + 2];
-    float dnorm = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);
     int64_t base = r * S;
+    float4 rw[C];
+    float zz[C], zn[C], nz[C];
+    load_ray<C>(raw, z, noise, base, S, lane, rw, zz, zn, nz);
+    float dnorm = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);
     float carry = 1.0f, a0 = 0.f, a1 = 0.f, a2 = 0.f, adepth = 0.f, aacc = 0.f;
-    for (int s0 = 0; s0 < S; s0 += 32) {
-      int s = s0 + lane;
-      SampleTerms t = load_terms(raw, z, noise, base, s, S, dnorm);
+#pragma unroll
+    for (int j = 0; j < C; ++j) {
+      int s = j * 32 + lane;
+      SampleTerms t = make_terms(rw[j], zz[j], zn[j], s + 1 >= S, s < S, nz[j], dnorm);
       float total;
       float T = carry * warp_excl_prod(t.q, lane, total);
       carry *= total;
       float w = t.alpha * T;
       if (s < S) {
-        if (weights) weights[base + s] = w;
+        if (weights) __stcs(weights + base + s, w);
         a0 += w * t.c0; a1 += w * t.c1; a2 += w * t.c2;
         adepth += w * t.z;
         aacc += w;
@@ -114,9 +165,11 @@ __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restr
   }
 }
 
-// C = number of 32-sample chunks held in registers (S <= 32*C)
+// C = number of 32-sample chunks held in registers (S <= 32*C).  Only the inputs and the transmittance
+// stay live between the forward and the reverse scan; the per-sample terms are recomputed (the kernel is
+// bandwidth-bound, registers buy occupancy).
 template <int C>
-__global__ void __launch_bounds__(256) composite_bwd_kernel(const float* __restrict__ raw,
+__global__ void __launch_bounds__(256, C <= 6 ? 3 : 1) composite_bwd_kernel(const float* __restrict__ raw,
                                                             const float* __restrict__ z,
                                                             const float* __restrict__ rays_d,
                                                             const float* __restrict__ noise, int64_t n, int S,
@@ -130,20 +183,21 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(const float* __restr
   int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t r = warp; r < n; r += nwarps) {
     float d0 = rays_d[r * 3], d1 = rays_d[r * 3 + 1], d2 = rays_d[r * 3 + 2];
-    float dnorm = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);
     int64_t base = r * S;
-    SampleTerms t[C];
-    float T[C];
+    float4 rw[C];
+    float zz[C], zn[C], nz[C], T[C];
+    load_ray<C>(raw, z, noise, base, S, lane, rw, zz, zn, nz);
+    float dnorm = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);
     float carry = 1.0f, adepth = 0.f, aacc = 0.f;
 #pragma unroll
     for (int j = 0; j < C; ++j) {
       int s = j * 32 + lane;
-      t[j] = load_terms(raw, z, noise, base, s, S, dnorm);
+      SampleTerms t = make_terms(rw[j], zz[j], zn[j], s + 1 >= S, s < S, nz[j], dnorm);
       float total;
-      T[j] = carry * warp_excl_prod(t[j].q, lane, total);
+      T[j] = carry * warp_excl_prod(t.q, lane, total);
       carry *= total;
-      float w = t[j].alpha * T[j];
-      adepth += w * t[j].z;
+      float w = t.alpha * T[j];
+      adepth += w * t.z;
       aacc += w;
     }
     adepth = warp_sum(adepth);
@@ -166,23 +220,24 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(const float* __restr
 #pragma unroll
     for (int j = C - 1; j >= 0; --j) {
       int s = j * 32 + lane;
-      float w = t[j].alpha * T[j];
-      float g = gr0 * t[j].c0 + gr1 * t[j].c1 + gr2 * t[j].c2 + gdepth * t[j].z + gacc;  // dL/dw_s
+      SampleTerms t = make_terms(rw[j], zz[j], zn[j], s + 1 >= S, s < S, nz[j], dnorm);
+      float w = t.alpha * T[j];
+      float g = gr0 * t.c0 + gr1 * t.c1 + gr2 * t.c2 + gdepth * t.z + gacc;  // dL/dw_s
       float total;
       float suffix = rcarry + warp_excl_suffix_sum(g * w, lane, total);
       rcarry += total;
-      float galpha = g * T[j] - suffix / t[j].q;
+      float galpha = g * T[j] - suffix / t.q;
       // alpha = 1 - exp(-rs*dist): d/d(rs) = dist*(1-alpha), d/d(dist) = rs*(1-alpha)
-      float e = 1.0f - t[j].alpha;
-      float gsigma = (t[j].rs > 0.f) ? galpha * t[j].dist * e : 0.f;
-      gnorm += galpha * t[j].rs * e * t[j].dz;
+      float e = 1.0f - t.alpha;
+      float gsigma = (t.rs > 0.f) ? galpha * t.dist * e : 0.f;
+      gnorm += galpha * t.rs * e * t.dz;
       if (s < S) {
         float4 o;
-        o.x = w * gr0 * t[j].c0 * (1.0f - t[j].c0);
-        o.y = w * gr1 * t[j].c1 * (1.0f - t[j].c1);
-        o.z = w * gr2 * t[j].c2 * (1.0f - t[j].c2);
+        o.x = w * gr0 * t.c0 * (1.0f - t.c0);
+        o.y = w * gr1 * t.c1 * (1.0f - t.c1);
+        o.z = w * gr2 * t.c2 * (1.0f - t.c2);
         o.w = gsigma;
-        *reinterpret_cast<float4*>(d_raw + (base + s) * 4) = o;
+        __stcs(reinterpret_cast<float4*>(d_raw + (base + s) * 4), o);
       }
     }
     if (d_rays_d) {
@@ -206,8 +261,20 @@ int nb_composite_fwd(const float* raw, const float* z, const float* rays_d, cons
                      void* stream) {
   if (n == 0) return 0;
   NB_REQUIRE(raw && z && rays_d && S >= 1, "nb_composite_fwd: bad arguments");
-  composite_fwd_kernel<<<grid_for(n, 8), 256, 0, as_stream(stream)>>>(raw, z, rays_d, noise, n, S, white_bkgd,
-                                                                       rgb_map, disp, acc, weights, depth);
+  if (S > 512) {
+    set_error("nb_composite_fwd: S=%d > 512 samples per ray is not implemented", S);
+    return NB_E_UNSUPPORTED;
+  }
+  const int grid = grid_for(n, 8);
+  cudaStream_t st = as_stream(stream);
+#define NB_LAUNCH_FWD(C) \
+  composite_fwd_kernel<C><<<grid, 256, 0, st>>>(raw, z, rays_d, noise, n, S, white_bkgd, rgb_map, disp, acc, weights, depth)
+  if (S <= 64) NB_LAUNCH_FWD(2);
+  else if (S <= 128) NB_LAUNCH_FWD(4);
+  else if (S <= 192) NB_LAUNCH_FWD(6);
+  else if (S <= 256) NB_LAUNCH_FWD(8);
+  else NB_LAUNCH_FWD(16);
+#undef NB_LAUNCH_FWD
   return check_launch("nb_composite_fwd");
 }
 

@@ -170,28 +170,34 @@ __device__ __forceinline__ float z_at(float near_, float far_, float t, int lind
   return __fdiv_rn(1.0f, __fadd_rn(a, b));
 }
 
+// One thread per sample (plenty of independent loads in flight); IDX = uint32_t whenever n*S fits, so the
+// sample -> (ray, s) split is a 32-bit division.
+template <typename IDX>
 __global__ void __launch_bounds__(256) sample_coarse_kernel(const float* __restrict__ rays, int64_t n, int ld,
                                                             const float* __restrict__ t_vals,
                                                             const float* __restrict__ t_rand, int S, int lindisp,
                                                             float* __restrict__ z_out, float* __restrict__ pts) {
-  int64_t total = n * S;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    int64_t r = i / S;
-    int s = (int)(i - r * S);
-    const float* ray = rays + r * ld;
+  const IDX total = (IDX)(n * S);
+  const IDX stride = (IDX)gridDim.x * blockDim.x;
+  for (IDX i = (IDX)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const IDX r = i / (IDX)S;
+    const int s = (int)(i - r * (IDX)S);
+    const float* ray = rays + (int64_t)r * ld;
+    const float tr = t_rand ? __ldcs(t_rand + i) : 0.f;
     float near_ = ray[6], far_ = ray[7];
     float z = z_at(near_, far_, t_vals[s], lindisp);
     if (t_rand) {
       float lower = z, upper = z;
       if (s > 0) lower = __fmul_rn(0.5f, __fadd_rn(z, z_at(near_, far_, t_vals[s - 1], lindisp)));
       if (s < S - 1) upper = __fmul_rn(0.5f, __fadd_rn(z_at(near_, far_, t_vals[s + 1], lindisp), z));
-      z = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), t_rand[i]));
+      z = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), tr));
     }
-    z_out[i] = z;
+    __stcs(z_out + i, z);
     if (pts) {
-      pts[i * 3 + 0] = __fadd_rn(ray[0], __fmul_rn(ray[3], z));
-      pts[i * 3 + 1] = __fadd_rn(ray[1], __fmul_rn(ray[4], z));
-      pts[i * 3 + 2] = __fadd_rn(ray[2], __fmul_rn(ray[5], z));
+      float* p = pts + (int64_t)i * 3;
+      p[0] = __fadd_rn(ray[0], __fmul_rn(ray[3], z));
+      p[1] = __fadd_rn(ray[1], __fmul_rn(ray[4], z));
+      p[2] = __fadd_rn(ray[2], __fmul_rn(ray[5], z));
     }
   }
 }
@@ -317,8 +323,12 @@ int nb_sample_coarse(const float* rays, int64_t n, int ld, const float* t_vals, 
                      int lindisp, float* z, float* pts, void* stream) {
   if (n == 0) return 0;
   NB_REQUIRE(rays && t_vals && z && ld >= 8 && S >= 1, "nb_sample_coarse: bad arguments");
-  sample_coarse_kernel<<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays, n, ld, t_vals, t_rand, S, lindisp,
-                                                                             z, pts);
+  if (n * S < (1ll << 31))
+    sample_coarse_kernel<uint32_t><<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays, n, ld, t_vals, t_rand, S,
+                                                                                        lindisp, z, pts);
+  else
+    sample_coarse_kernel<int64_t><<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays, n, ld, t_vals, t_rand, S,
+                                                                                       lindisp, z, pts);
   return check_launch("nb_sample_coarse");
 }
 

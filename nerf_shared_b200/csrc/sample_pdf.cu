@@ -152,6 +152,141 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_kernel(const float* __re
   }
 }
 
+// ---- fast path: S <= 64 coarse samples, I = 32 * SPT importance samples (every shipped config) --------------
+// Same arithmetic, different data movement: the cdf's divisions run on all lanes and only the 62 dependent
+// additions of torch.cumsum stay serial (as register shuffles); the importance samples are sorted in registers
+// with a shuffle bitonic network (random u only: deterministic u yields ascending samples) and merged with the
+// ascending coarse depths by rank (two binary searches) instead of a 256-entry shared-memory bitonic sort.
+template <int SPT>
+__global__ void __launch_bounds__(256) sample_pdf_merge_fast_kernel(const float* __restrict__ z,
+                                                                    const float* __restrict__ weights,
+                                                                    const float* __restrict__ u,
+                                                                    const float* __restrict__ u_det, int64_t n, int S,
+                                                                    float* __restrict__ z_out, float* __restrict__ z_std,
+                                                                    float* __restrict__ z_samples) {
+  constexpr int I = 32 * SPT;
+  __shared__ float smem[8][64 + 64 + 64 + I + 64 + I];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float* zc = smem[wib];
+  float* bins = zc + 64;
+  float* cdf = bins + 64;
+  float* srt = cdf + 64;
+  float* outb = srt + I;
+  const int B = S - 1;
+  int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < n; r += nwarps) {
+    const float* zr = z + r * S;
+    const float* wr = weights + r * S + 1;   // weights[..., 1:-1]: B - 1 = S - 2 entries
+    float uu[SPT];
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) uu[k] = u ? __ldcs(u + r * I + k * 32 + lane) : u_det[k * 32 + lane];
+    const float z0 = lane < S ? zr[lane] : 0.f, z1 = lane + 32 < S ? zr[lane + 32] : 0.f;
+    // v[m] = w[m] + 1e-5, m < B - 1 (lane holds m = lane and lane + 32); sum as build_cdf does
+    const float v0 = lane < B - 1 ? __fadd_rn(wr[lane], 1e-5f) : 0.f;
+    const float v1 = lane + 32 < B - 1 ? __fadd_rn(wr[lane + 32], 1e-5f) : 0.f;
+    float part = 0.f;
+    if (lane < B - 1) part += v0;
+    if (lane + 32 < B - 1) part += v1;
+    const float wsum = warp_sum(part);
+    const float q0 = __fdiv_rn(v0, wsum), q1 = __fdiv_rn(v1, wsum);
+    if (lane < S) zc[lane] = z0;
+    if (lane + 32 < S) zc[lane + 32] = z1;
+    // cdf[0] = 0, cdf[m + 1] = cdf[m] + q[m]: the sequential fp32 sum of torch.cumsum
+    float c = 0.f, c_lo = 0.f, c_hi = 0.f;   // cdf[lane], cdf[lane + 32]
+    for (int m = 0; m < B - 1; ++m) {
+      const float qm = __shfl_sync(0xffffffffu, m < 32 ? q0 : q1, m & 31);
+      c = __fadd_rn(c, qm);
+      if (m + 1 == lane) c_lo = c;
+      if (m + 1 == lane + 32) c_hi = c;
+    }
+    if (lane < B) cdf[lane] = c_lo;
+    if (lane + 32 < B) cdf[lane + 32] = c_hi;
+    __syncwarp();
+    if (lane < B) bins[lane] = __fmul_rn(0.5f, __fadd_rn(zc[lane + 1], zc[lane]));
+    if (lane + 32 < B) bins[lane + 32] = __fmul_rn(0.5f, __fadd_rn(zc[lane + 33], zc[lane + 32]));
+    __syncwarp();
+    float smp[SPT];
+    float sum = 0.f;
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) {
+      int kk;
+      smp[k] = invert_one(bins, cdf, B, uu[k], kk);
+      sum += smp[k];
+      if (z_samples) z_samples[r * I + k * 32 + lane] = smp[k];
+    }
+    if (z_std) {
+      const float mean = warp_sum(sum) / (float)I;
+      float var = 0.f;
+#pragma unroll
+      for (int k = 0; k < SPT; ++k) {
+        const float d = smp[k] - mean;
+        var += d * d;
+      }
+      var = warp_sum(var) / (float)I;
+      if (lane == 0) z_std[r] = sqrtf(var);
+    }
+    if (u) {  // random draws: sort (element index e = k * 32 + lane)
+#pragma unroll
+      for (int kk = 2; kk <= I; kk <<= 1) {
+#pragma unroll
+        for (int j = kk >> 1; j > 0; j >>= 1) {
+          if (j >= 32) {
+            const int dj = j >> 5;
+#pragma unroll
+            for (int k = 0; k < SPT; ++k) {
+              if ((k & dj) == 0) {
+                const bool up = (((k * 32 + lane) & kk) == 0);
+                const float a = smp[k], b = smp[k | dj];
+                if ((a > b) == up) { smp[k] = b; smp[k | dj] = a; }
+              }
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < SPT; ++k) {
+              const float o = __shfl_xor_sync(0xffffffffu, smp[k], j);
+              const bool up = (((k * 32 + lane) & kk) == 0);
+              const bool low = (lane & j) == 0;
+              smp[k] = (low == up) ? fminf(smp[k], o) : fmaxf(smp[k], o);
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) srt[k * 32 + lane] = smp[k];
+    __syncwarp();
+    // merge by rank: coarse c -> c + #{samples < z_c}; sample e -> e + #{coarse <= sample}
+    {
+      const float zz[2] = {z0, z1};
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        const int ci = lane + 32 * t;
+        if (ci < S) {
+          int lo = 0, hi = I;
+          while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (srt[mid] < zz[t]) lo = mid + 1; else hi = mid;
+          }
+          outb[ci + lo] = zz[t];
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < SPT; ++k) {
+        int lo = 0, hi = S;
+        while (lo < hi) {
+          const int mid = (lo + hi) >> 1;
+          if (zc[mid] <= smp[k]) lo = mid + 1; else hi = mid;
+        }
+        outb[k * 32 + lane + lo] = smp[k];
+      }
+    }
+    __syncwarp();
+    for (int i = lane; i < S + I; i += 32) __stcs(z_out + r * (int64_t)(S + I) + i, outb[i]);
+    __syncwarp();
+  }
+}
+
 }  // namespace nb
 
 using namespace nb;
@@ -185,6 +320,15 @@ int nb_sample_pdf_merge(const float* z, const float* weights, const float* u, co
   if (n == 0) return 0;
   NB_REQUIRE(z && weights && z_out && S >= 3 && I >= 1, "nb_sample_pdf_merge: bad arguments");
   NB_REQUIRE(u || u_det, "nb_sample_pdf_merge: need u or u_det");
+  if (S <= 64 && (I == 64 || I == 128)) {
+    if (I == 128)
+      sample_pdf_merge_fast_kernel<4><<<grid_for(n, 8), 256, 0, as_stream(stream)>>>(z, weights, u, u_det, n, S, z_out, z_std,
+                                                                                       z_samples);
+    else
+      sample_pdf_merge_fast_kernel<2><<<grid_for(n, 8), 256, 0, as_stream(stream)>>>(z, weights, u, u_det, n, S, z_out, z_std,
+                                                                                       z_samples);
+    return check_launch("nb_sample_pdf_merge");
+  }
   int P = 2;
   while (P < S + I) P <<= 1;
   int Bp = (S + 31) / 32 * 32;
