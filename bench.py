@@ -250,6 +250,10 @@ def run_b200(a):
         out.update(kernel_breakdown(a, coarse, fine, pool[0], dev))
         if render is not None:
             out["render"] = render
+        if world == 1 and not a.no_render:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import bench_stream
+            out["stream_kernels"] = bench_stream.run(quiet=True)
         if not a.no_cpu_baseline and world == 1:     # the CPU baseline is reported at N=1 only
             out["cpu_baseline"] = cpu_train_baseline(budget_s=15.0)
         print(json.dumps(out), file=_real_stdout, flush=True)
@@ -306,15 +310,70 @@ def kernel_breakdown(a, coarse, fine, batch, dev):
     t_dgrad = timed(lambda: bwd(False))
     t_bwd = timed(lambda: bwd(True))
     t_wgrad = max(t_bwd - t_dgrad, 1e-6)
-    flops = {"mlp_fwd_tc(fine)": FLOP_FWD * M, "mlp_dgrad(fine)": (FLOP_FWD - 2 * (63 * 256 * 2 + 27 * 128 + 256 + 384)) * M,
-             "mlp_wgrad+small(fine)": FLOP_FWD * M}
-    times = {"mlp_fwd_tc(fine)": t_fwd, "mlp_dgrad(fine)": t_dgrad, "mlp_wgrad+small(fine)": t_wgrad}
-    top = max(times, key=times.get)
-    ach = flops[top] / times[top] / 1e9
-    return {"roofline": {"bound": "tensor", "kernel": top, "achieved": ach, "peak": burst, "unit": "TFLOP/s", "frac": ach / burst,
-                         "traffic": None, "peak_source": src + " bf16 burst (kernel timed alone)",
-                         "per_kernel_ms": {k: round(v, 4) for k, v in times.items()},
-                         "per_kernel_tflops": {k: round(flops[k] / times[k] / 1e9, 1) for k in times}}}
+    # inference-sized forward (no saved activations): the "MLP tensor-pipe utilisation" of BASELINE.json
+    Mi = 32768 * S_FINE
+    pts_i = torch.rand(Mi, 3, device=dev) * 6 - 3
+    vd_i = torch.nn.functional.normalize(torch.randn(32768, 3, device=dev), dim=-1)
+    t_inf = timed(lambda: _ops.mlp_forward_tc(fine, pts_i, vd_i, S_FINE, save_acts=False), reps=5)
+    del pts_i, vd_i
+    dgrad_flop = FLOP_FWD - 2 * (63 * 256 * 2 + 27 * 128 + 256 + 384)
+    # algorithmic bytes per sample: saved activations 40 slabs, dA 38 slabs of 128 B per row
+    act_b, da_b, mask_b = 40 * 128 + 288, 38 * 128, 288   # + relu' bit masks (9 groups x 8 words per row)
+    kern = {
+        "mlp_fwd_tc(fine, saves activations)": (t_fwd, FLOP_FWD * M, (12 + 16 + act_b) * M),
+        "mlp_dgrad(fine)": (t_dgrad, dgrad_flop * M, (16 + mask_b + da_b) * M),
+        "mlp_wgrad+small(fine)": (t_wgrad, FLOP_FWD * M, (40 * 128 + da_b + 768 + 16) * M),
+        "mlp_fwd_tc(inference 32768x192)": (t_inf, FLOP_FWD * Mi, 28 * Mi),
+    }
+    traffic = ncu_traffic()
+    per = {}
+    for k, (t, fl, by) in kern.items():
+        tf, gb = fl / t / 1e9, by / t / 1e6
+        per[k] = {"ms": round(t, 4), "tflops": round(tf, 1), "frac_tensor": round(tf / burst, 3), "algorithmic_GBps": round(gb, 1),
+                  "frac_hbm": round(gb / hbm, 3), "algorithmic_bytes": int(by)}
+    train_k = [k for k in kern if "inference" not in k]
+    top = max(train_k, key=lambda k: kern[k][0])
+    t, fl, by = kern[top]
+    tens, mem = fl / t / 1e9 / burst, by / t / 1e6 / hbm
+    if mem >= tens:   # the roofline that binds is the one the kernel sits closer to
+        roof = {"bound": "hbm", "kernel": top, "achieved": by / t / 1e6, "peak": hbm, "unit": "GB/s", "frac": mem,
+                "peak_source": src + " copy bandwidth"}
+    else:
+        roof = {"bound": "tensor", "kernel": top, "achieved": fl / t / 1e9, "peak": burst, "unit": "TFLOP/s", "frac": tens,
+                "peak_source": src + " bf16 burst (kernel timed alone)"}
+    roof["traffic"] = traffic.get(top.split("(")[0].split("+")[0] + "_kernel")
+    roof["traffic_source"] = "profiles/ (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch)" if roof["traffic"] else None
+    roof["per_kernel"] = per
+    roof["mlp_tensor_pipe"] = {"kernel": "mlp_fwd_tc(inference 32768x192)", "tflops": per["mlp_fwd_tc(inference 32768x192)"]["tflops"],
+                               "frac_of_burst_peak": round(FLOP_FWD * Mi / t_inf / 1e9 / burst, 3),
+                               "frac_of_sustained_peak": round(FLOP_FWD * Mi / t_inf / 1e9 / sustained, 3)}
+    return {"roofline": roof}
+
+
+def ncu_traffic():
+    """DRAM bytes per launch of the MLP kernels from the committed ncu summary (same sizes as kernel_breakdown:
+    tools/prof_kernels.py, 1024 rays x 192 samples); {} if the file is missing."""
+    import csv
+    import glob
+    out = {}
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_mlp_kernels.csv")))
+    if not files:
+        return out
+    rows = list(csv.reader(open(files[-1])))
+    if len(rows) < 3:
+        return out
+    h = rows[0]
+    try:
+        ik, ir, iw = h.index("Kernel Name"), h.index("dram__bytes_read.sum"), h.index("dram__bytes_write.sum")
+    except ValueError:
+        return out
+    unit = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
+    ur, uw = unit.get(rows[1][ir], 1.0), unit.get(rows[1][iw], 1.0)
+    for r in rows[2:]:
+        name = r[ik].replace("void ", "").replace("nb::", "").split("<")[0].split("(")[0].strip()
+        if name not in out:     # first launch of each kernel = the training-sized one
+            out[name] = float(r[ir]) * ur + float(r[iw]) * uw
+    return out
 
 
 def render_leg(renderer, coarse, fine, K, poses_d, dev, world=1):

@@ -361,7 +361,8 @@ def untile(buf: torch.Tensor, n_slabs: int, M: int) -> torch.Tensor:
     """Decode a tiled/swizzled slab buffer (acts or dA) to a logical [M, n_slabs*64] bf16 matrix
     (tests / debugging): chunk g of row r sits at physical chunk g ^ (r % 8)."""
     tiles = (M + 127) // 128
-    x = buf.view(torch.bfloat16).view(tiles, n_slabs, 128, 8, 8)
+    # (the activation buffer carries the relu' bit masks after its slab tiles: decode the slab part only)
+    x = buf[:tiles * n_slabs * 16384].view(torch.bfloat16).view(tiles, n_slabs, 128, 8, 8)
     r = torch.arange(128, device=buf.device)
     g = torch.arange(8, device=buf.device)
     phys = (g[None, :] ^ (r[:, None] % 8))                       # [128, 8]

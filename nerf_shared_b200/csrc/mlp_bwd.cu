@@ -81,28 +81,20 @@ __device__ __forceinline__ uint32_t relu_mask2(uint32_t d, uint32_t h) {
   return *reinterpret_cast<uint32_t*>(&r);
 }
 
-// MODE 0: plain copy (d_feature); 1: + d_sigma * alpha_w, masked by h7; 2: masked
-// This warp's four chunks [cbeg, cbeg + 4) of its 32 rows (two warps share a lane quarter).  The saved
-// activation that supplies relu' comes from HBM: the rows of chunk cc + 1 are requested before chunk cc is
-// processed, and the caller requests chunk cbeg before it waits for the accumulator (`hm`).
-__device__ __forceinline__ void load_mask_chunk(const uint8_t* __restrict__ mask_src, int row, int c, uint4 (&hm)[4]) {
-#pragma unroll
-  for (int g = 0; g < 4; ++g)
-    hm[g] = *reinterpret_cast<const uint4*>(mask_src + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g));
-}
-
+// MODE 0: plain copy (d_feature); 1: + d_sigma * alpha_w, masked by relu'(h7); 2: masked
+// This warp's four chunks [cbeg, cbeg + 4) of its 32 rows (two warps share a lane quarter).  relu' comes from
+// the bit masks the forward saved: one coalesced 32-bit word per row and 32-column chunk (`mask` points at
+// the [chunk][row] words of this layer), all four requested by the caller before it waits for the accumulator.
 template <int MODE>
-__device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, int row, int cbeg,
-                                               const uint8_t* __restrict__ mask_src, uint4 (&hm)[4], float d_sigma,
-                                               const float* __restrict__ alpha_w) {
+__device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, int row, int cbeg, const uint32_t (&mw)[4],
+                                               bool live, float d_sigma, const float* __restrict__ alpha_w) {
 #pragma unroll
   for (int cc = 0; cc < 4; ++cc) {
     const int c = cbeg + cc;
     uint32_t v[32];
     tmem_ld32(taddr + c * 32, v);
-    uint4 hn[4];
-    if (MODE != 0 && mask_src && cc < 3) load_mask_chunk(mask_src, row, c + 1, hn);
     tmem_ld_wait();
+    const uint32_t m = (MODE == 0) ? 0xFFFFFFFFu : (live ? mw[cc] : 0u);
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       float f[8];
@@ -116,22 +108,14 @@ __device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, int
           f[j + 2] = fmaf(d_sigma, a.z, f[j + 2]); f[j + 3] = fmaf(d_sigma, a.w, f[j + 3]);
         }
       }
-      uint32_t p0 = pack_bf16x2(f[0], f[1]), p1 = pack_bf16x2(f[2], f[3]), p2 = pack_bf16x2(f[4], f[5]),
-               p3 = pack_bf16x2(f[6], f[7]);
       if (MODE != 0) {
-        if (mask_src) {
-          p0 = relu_mask2(p0, hm[g].x); p1 = relu_mask2(p1, hm[g].y);
-          p2 = relu_mask2(p2, hm[g].z); p3 = relu_mask2(p3, hm[g].w);
-        } else {
-          p0 = p1 = p2 = p3 = 0u;
-        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = ((m >> (g * 8 + j)) & 1u) ? f[j] : 0.f;
       }
+      const uint32_t p0 = pack_bf16x2(f[0], f[1]), p1 = pack_bf16x2(f[2], f[3]), p2 = pack_bf16x2(f[4], f[5]),
+                     p3 = pack_bf16x2(f[6], f[7]);
       const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g);
       st_shared_v4(act + off, p0, p1, p2, p3);
-    }
-    if (MODE != 0 && mask_src && cc < 3) {
-#pragma unroll
-      for (int g = 0; g < 4; ++g) hm[g] = hn[g];
     }
   }
 }
@@ -258,7 +242,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
       const int64_t tile = (int64_t)quad * 4 + rank * 2 + x;
       const int64_t m = tile * kTileM + row;
       const bool real = tile * kTileM < M;
-      const uint8_t* at = real ? acts + (size_t)tile * kActSlabs * kSlabBytes : nullptr;
+      // relu' bit masks of this tile ([group][chunk][row] words, after all activation tiles)
+      const uint32_t* mk = real ? reinterpret_cast<const uint32_t*>(acts + (size_t)((M + kTileM - 1) / kTileM) * kActSlabs * kSlabBytes +
+                                                                    (size_t)tile * kMaskTileBytes)
+                                : nullptr;
       uint8_t* dt = real ? dA + (size_t)tile * kDaSlabs * kSlabBytes : nullptr;
       // every warp streams its own 32 rows (4 KB of each of its slabs) of the freshly written dA tile to HBM
       auto flush = [&](int src_slab0, int dst_slab0, int nslabs) {
@@ -280,21 +267,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
 #pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
         const int c = 2 * h + cc;
+        const uint32_t m = mk ? mk[(8 * 8 + c) * 128 + row] : 0u;
 #pragma unroll
         for (int qq = 0; qq < 4; ++qq) {
           const int col = c * 32 + qq * 8;
           float f[8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] = g.x * wr[col + j] + g.y * wr[128 + col + j] + g.z * wr[256 + col + j];
-          uint32_t p0 = pack_bf16x2(f[0], f[1]), p1 = pack_bf16x2(f[2], f[3]), p2 = pack_bf16x2(f[4], f[5]),
-                   p3 = pack_bf16x2(f[6], f[7]);
-          const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + qq);
-          if (at) {
-            const uint4 hh = *reinterpret_cast<const uint4*>(at + (size_t)kActSlabHv * kSlabBytes + off);
-            p0 = relu_mask2(p0, hh.x); p1 = relu_mask2(p1, hh.y); p2 = relu_mask2(p2, hh.z); p3 = relu_mask2(p3, hh.w);
-          } else {
-            p0 = p1 = p2 = p3 = 0u;
+          for (int j = 0; j < 8; ++j) {
+            const float t = g.x * wr[col + j] + g.y * wr[128 + col + j] + g.z * wr[256 + col + j];
+            f[j] = ((m >> (qq * 8 + j)) & 1u) ? t : 0.f;
           }
+          const uint32_t p0 = pack_bf16x2(f[0], f[1]), p1 = pack_bf16x2(f[2], f[3]), p2 = pack_bf16x2(f[4], f[5]),
+                         p3 = pack_bf16x2(f[6], f[7]);
+          const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + qq);
           st_shared_v4(sAct + off, p0, p1, p2, p3);
         }
       }
@@ -305,9 +290,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
 #pragma unroll 1
       for (int step = 0; step < 9; ++step) {
         const int l = 8 - step;  // step >= 1 produces d_a_l, masked by h_l: step 1 -> l = 7 ... step 8 -> l = 0
-        const uint8_t* ms = (step > 0 && at) ? at + (size_t)l * 4 * kSlabBytes : nullptr;
-        uint4 hm[4];
-        if (ms) load_mask_chunk(ms, row, 4 * h, hm);   // in flight while the MMAs of this step run
+        uint32_t mw[4] = {0u, 0u, 0u, 0u};
+        if (step > 0 && mk) {   // in flight while the MMAs of this step run
+#pragma unroll
+          for (int cc = 0; cc < 4; ++cc) mw[cc] = mk[(l * 8 + 4 * h + cc) * 128 + row];
+        }
         mbar_wait(my_acc, par_acc);
         par_acc ^= 1;
         tc_fence_after();
@@ -315,11 +302,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
         if (step == 0) pair_sync(pair_id);   // slab 1 was flushed (d hv) by the h = 1 warp, h = 0 overwrites it now
         int dst_slab;
         if (step == 0) {
-          dgrad_epilogue<0>(taddr, sAct, row, 4 * h, nullptr, hm, 0.f, nullptr);
+          dgrad_epilogue<0>(taddr, sAct, row, 4 * h, mw, true, 0.f, nullptr);
           dst_slab = kDaSlabFeat;
         } else {
-          if (step == 1) dgrad_epilogue<1>(taddr, sAct, row, 4 * h, ms, hm, g.w, wa);
-          else dgrad_epilogue<2>(taddr, sAct, row, 4 * h, ms, hm, 0.f, nullptr);
+          if (step == 1) dgrad_epilogue<1>(taddr, sAct, row, 4 * h, mw, mk != nullptr, g.w, wa);
+          else dgrad_epilogue<2>(taddr, sAct, row, 4 * h, mw, mk != nullptr, 0.f, nullptr);
           dst_slab = l * 4;
         }
         fence_proxy_async();

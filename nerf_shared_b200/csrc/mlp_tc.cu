@@ -182,7 +182,7 @@ __device__ __forceinline__ void store_operand_row(uint32_t slab, int row, const 
 template <int MODE>
 __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __restrict__ bias,
                                                 const float* __restrict__ alpha_w, uint32_t act, int row, int cbeg,
-                                                float& sigma) {
+                                                float& sigma, uint32_t* __restrict__ mask_out) {
 #pragma unroll
   for (int cc = 0; cc < 4; ++cc) {
     const int c = cbeg + cc;
@@ -192,6 +192,7 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
 #pragma unroll
     for (int j = 0; j < 8; ++j) bq[j] = *reinterpret_cast<const float4*>(bias + c * 32 + j * 4);
     tmem_ld_wait();
+    uint32_t neg = 0;   // sign bits of the 32 pre-activations, column j at bit j
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       float f[8];
@@ -202,6 +203,10 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
         f[j + 1] = __uint_as_float(v[g * 8 + j + 1]) + b.y;
         f[j + 2] = __uint_as_float(v[g * 8 + j + 2]) + b.z;
         f[j + 3] = __uint_as_float(v[g * 8 + j + 3]) + b.w;
+      }
+      if (MODE != 2 && mask_out) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) neg = (neg >> 1) | (__float_as_uint(f[j]) & 0x80000000u);
       }
       if (MODE == 1) {
 #pragma unroll
@@ -224,13 +229,15 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
       const uint32_t off = (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g);
       st_shared_v4(act + off, p0, p1, p2, p3);
     }
+    if (MODE != 2 && mask_out) mask_out[c * 128 + row] = ~neg;
   }
 }
 
 // view branch: hv = relu(acc + b) (128 wide), rgb = hv . Wrgb^T in fp32 (nerf.py:125-129); this warp's two
 // chunks [cbeg, cbeg + 2), partial sums returned in r / g_ / b_ (the caller adds the bias and the other half)
 __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __restrict__ cst, float& r, float& g_,
-                                               float& b_, int row, int cbeg, uint32_t act, bool save) {
+                                               float& b_, int row, int cbeg, uint32_t act, bool save,
+                                               uint32_t* __restrict__ mask_out) {
   const float* bias = cst + kOffViewB;
   const float* wr = cst + kOffRgbW;
   r = 0.f; g_ = 0.f; b_ = 0.f;
@@ -243,6 +250,7 @@ __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __re
 #pragma unroll
     for (int j = 0; j < 8; ++j) bq[j] = *reinterpret_cast<const float4*>(bias + c * 32 + j * 4);
     tmem_ld_wait();
+    uint32_t pos = 0;   // column j of the chunk at bit j: relu output > 0
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       float f[8];
@@ -261,10 +269,14 @@ __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __re
         g_ = fmaf(f[j], w1.x, g_); g_ = fmaf(f[j + 1], w1.y, g_); g_ = fmaf(f[j + 2], w1.z, g_); g_ = fmaf(f[j + 3], w1.w, g_);
         b_ = fmaf(f[j], w2.x, b_); b_ = fmaf(f[j + 1], w2.y, b_); b_ = fmaf(f[j + 2], w2.z, b_); b_ = fmaf(f[j + 3], w2.w, b_);
       }
-      if (save)
+      if (save) {
         st_shared_v4(act + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g), pack_bf16x2(f[0], f[1]),
                      pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) pos = (pos >> 1) | (f[j] > 0.f ? 0x80000000u : 0u);
+      }
     }
+    if (save) mask_out[c * 128 + row] = pos;
   }
 }
 
@@ -451,6 +463,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
       // operand image IS the saved image, so every warp streams its own 32 rows of its own two slabs
       // to HBM with bulk async stores; `flush` follows the fence that publishes the rows to the MMA.
       uint8_t* save = (acts && tile * kTileM < M) ? acts + (size_t)tile * kActSlabs * kSlabBytes : nullptr;
+      // relu' bit masks of this tile (after all activation tiles of the launch)
+      uint32_t* mask = save ? reinterpret_cast<uint32_t*>(acts + (size_t)((M + kTileM - 1) / kTileM) * kActSlabs * kSlabBytes +
+                                                          (size_t)tile * kMaskTileBytes)
+                            : nullptr;
       const uint32_t wrow = (uint32_t)q * 4096u;
       auto flush = [&](uint32_t src_slab0, int dst_slab0, int nslabs) {
         if (save && lane == 0) {
@@ -492,10 +508,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
         tc_fence_after();
         if (q == 0 && h == 0 && lane == 0) NB_TR(qi, layer, x, 2);
         reuse();
-        if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, 4 * h, sigma);
-        else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, 4 * h, sigma);
+        uint32_t* mk = mask ? mask + layer * 1024 : nullptr;
+        if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, 4 * h, sigma, mk);
+        else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, 4 * h, sigma, mk);
         else {
-          epilogue_hidden<2>(taddr, cst + kOffFeatB, nullptr, sAct, row, 4 * h, sigma);
+          epilogue_hidden<2>(taddr, cst + kOffFeatB, nullptr, sAct, row, 4 * h, sigma, nullptr);
           // view-direction encoding replaces the position encoding in the auxiliary slab
           // (its last reader, layer 5's MMA, retired before layer 5's accumulator was signalled)
           if (save) pair_sync(pair_id);   // the h = 0 warp's flush of enc(pts) has been waited for (reuse above)
@@ -532,7 +549,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
       if (save) pair_sync(pair_id);   // slab 1 (hv of the h = 1 warp) was flushed as layer 8's output by the h = 0 warp
       float r, g, b;
       // the view-branch hidden layer is staged in the (now idle) activation buffer only to be saved
-      epilogue_views(taddr, cst, r, g, b, row, 2 * h, sAct, save != nullptr);
+      epilogue_views(taddr, cst, r, g, b, row, 2 * h, sAct, save != nullptr, mask ? mask + 8 * 1024 : nullptr);
       tc_fence_before();
       // heads: the h = 1 warp hands its partial sums to the h = 0 warp of the same rows
       if (h == 1) *part = make_float4(r, g, b, sigma);
@@ -607,7 +624,9 @@ int64_t nb_mlp_packed_bytes(int L_pts, int L_dirs) {
   return (int64_t)kNumSlabs * kSlabBytes + kConstFloats * 4;
 }
 
-int64_t nb_mlp_act_bytes(int64_t M) { return ((M + kTileM - 1) / kTileM) * (int64_t)kActSlabs * kSlabBytes; }
+int64_t nb_mlp_act_bytes(int64_t M) {
+  return ((M + kTileM - 1) / kTileM) * ((int64_t)kActSlabs * kSlabBytes + kMaskTileBytes);
+}
 
 int nb_mlp_pack(const NbMlpWeights* w, void* packed, void* stream) {
   NB_REQUIRE(w && packed, "nb_mlp_pack: null pointer");
