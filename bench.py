@@ -97,12 +97,9 @@ class ClockSampler:
 
 def synth_scene(seed=0):
     """Blender-shaped synthetic data: poses on the standard orbit, random targets."""
-    from oracle import nerf_oracle as O   # pose / intrinsics generators only (no arithmetic on the timed path)
-    rng = np.random.default_rng(seed)
-    K = O.blender_intrinsics(H, W)
-    poses = np.stack([O.pose_spherical(float(t), -30.0, 4.0) for t in rng.uniform(-180, 180, N_IMAGES)], 0)
-    images = np.random.default_rng(seed + 1).random((N_IMAGES, H, W, 3), dtype=np.float32)
-    return K, poses.astype(np.float32), images
+    from nerf_shared_b200 import datasets
+    images, poses, _, K = datasets.synthetic_blender(H, W, N_IMAGES, seed)
+    return K, poses, images
 
 
 class Args:  # the subset of config_parser flags the API helpers read (configs/lego.txt)
@@ -118,7 +115,6 @@ class Args:  # the subset of config_parser flags the API helpers read (configs/l
 def run_b200(a):
     import torch.distributed as dist
     from nerf_shared_b200 import _lib, _ops, utils
-    from oracle import nerf_oracle as O
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -130,13 +126,11 @@ def run_b200(a):
     utils.device = dev
     args = Args()
     args.N_rand = a.rays
-    torch.manual_seed(1234 + rank)
-    np.random.seed(1234 + rank)
-
     K, poses, images = synth_scene()
+    torch.manual_seed(0)                       # identical random-init weights (nn.Linear default init) on every rank
     coarse, fine = utils.create_nerf_models(args)
-    # identical random-init weights on every rank (seeded numpy stream)
-    coarse.load_state_dict(O.make_params(11)); fine.load_state_dict(O.make_params(12))
+    torch.manual_seed(1234 + rank)             # per-rank ray batches / jitter
+    np.random.seed(1234 + rank)
     opt = utils.get_optimizer(coarse, fine, args)
     opt.grad_scale = 1.0 / world
     renderer = utils.get_renderer(args, {"near": 2.0, "far": 6.0})
@@ -380,9 +374,8 @@ def render_leg(renderer, coarse, fine, K, poses_d, dev, world=1):
     """800x800 full-res render (BASELINE.json configs[3]): frames/s with the pose resident; image rows are
     split across the ranks (dist.render_sharded) and the tiles all-gathered, time = max over ranks."""
     import torch.distributed as dist
-    from nerf_shared_b200 import dist as nd
-    from oracle import nerf_oracle as O
-    K8 = O.blender_intrinsics(800, 800)
+    from nerf_shared_b200 import datasets, dist as nd
+    K8 = datasets.synthetic_blender(800, 800, 1)[3]
     renderer.eval()
     perturb = renderer.perturb
     renderer.perturb = 0.0
