@@ -223,6 +223,7 @@ class Composite(torch.autograd.Function):
                                        ptr(acc), ptr(weights), ptr(depth), stream_ptr()), "nb_composite_fwd")
         ctx.save_for_backward(r, zc, d, nz)
         ctx.white = int(bool(white_bkgd))
+        ctx.set_materialize_grads(False)     # unused outputs arrive as None, not as zero tensors the kernel would read
         ctx.mark_non_differentiable(weights)
         return rgb, disp, acc, weights, depth
 

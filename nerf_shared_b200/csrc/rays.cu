@@ -202,6 +202,74 @@ __global__ void __launch_bounds__(256) sample_coarse_kernel(const float* __restr
   }
 }
 
+// Four consecutive samples of one ray per thread (S % 4 == 0): one 16-byte load of the jitter, one 16-byte store
+// of z (three more for the points), six instead of twelve z_at evaluations.  Same arithmetic, bit for bit.
+__global__ void __launch_bounds__(256) sample_coarse_vec4_kernel(const float* __restrict__ rays, int64_t n, int ld,
+                                                                 const float* __restrict__ t_vals,
+                                                                 const float* __restrict__ t_rand, int S, int lindisp,
+                                                                 float* __restrict__ z_out, float* __restrict__ pts) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // quad index
+  const int qpr = S >> 2;
+  if (q >= n * qpr) return;
+  const int64_t r = q / qpr;
+  const int s0 = (int)(q - r * qpr) << 2;
+  float4 tr = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (t_rand) tr = __ldcs(reinterpret_cast<const float4*>(t_rand) + q);
+  const float* ray = rays + r * ld;
+  const float near_ = ray[6], far_ = ray[7];
+  float zs[6];   // z_at(s0 - 1 .. s0 + 4)
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    const int s = min(max(s0 - 1 + k, 0), S - 1);
+    zs[k] = z_at(near_, far_, t_vals[s], lindisp);
+  }
+  float zo[4];
+  const float trs[4] = {tr.x, tr.y, tr.z, tr.w};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float zv = zs[k + 1];
+    if (t_rand) {
+      const int s = s0 + k;
+      const float lower = s > 0 ? __fmul_rn(0.5f, __fadd_rn(zv, zs[k])) : zv;
+      const float upper = s < S - 1 ? __fmul_rn(0.5f, __fadd_rn(zs[k + 2], zv)) : zv;
+      zv = __fadd_rn(lower, __fmul_rn(__fsub_rn(upper, lower), trs[k]));
+    }
+    zo[k] = zv;
+  }
+  __stcs(reinterpret_cast<float4*>(z_out) + q, make_float4(zo[0], zo[1], zo[2], zo[3]));
+  if (pts) {
+    float p[12];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) p[k * 3 + c] = __fadd_rn(ray[c], __fmul_rn(ray[3 + c], zo[k]));
+    float4* pp = reinterpret_cast<float4*>(pts) + q * 3;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) __stcs(pp + k, make_float4(p[4 * k], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3]));
+  }
+}
+
+__global__ void __launch_bounds__(256) ray_points_fwd_vec4_kernel(const float* __restrict__ ro,
+                                                                  const float* __restrict__ rd,
+                                                                  const float* __restrict__ z, int64_t n, int S,
+                                                                  float* __restrict__ pts) {
+  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int qpr = S >> 2;
+  if (q >= n * qpr) return;
+  const int64_t r = q / qpr;
+  const float4 zz = __ldcs(reinterpret_cast<const float4*>(z) + q);
+  const float o[3] = {ro[r * 3], ro[r * 3 + 1], ro[r * 3 + 2]}, d[3] = {rd[r * 3], rd[r * 3 + 1], rd[r * 3 + 2]};
+  const float zv[4] = {zz.x, zz.y, zz.z, zz.w};
+  float p[12];
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) p[k * 3 + c] = __fadd_rn(o[c], __fmul_rn(d[c], zv[k]));
+  float4* pp = reinterpret_cast<float4*>(pts) + q * 3;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) pp[k] = make_float4(p[4 * k], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3]);
+}
+
 __global__ void __launch_bounds__(256) ray_points_fwd_kernel(const float* __restrict__ ro,
                                                              const float* __restrict__ rd,
                                                              const float* __restrict__ z, int64_t n, int S,
@@ -323,7 +391,12 @@ int nb_sample_coarse(const float* rays, int64_t n, int ld, const float* t_vals, 
                      int lindisp, float* z, float* pts, void* stream) {
   if (n == 0) return 0;
   NB_REQUIRE(rays && t_vals && z && ld >= 8 && S >= 1, "nb_sample_coarse: bad arguments");
-  if (n * S < (1ll << 31))
+  const int64_t quads = n * (S >> 2);
+  if ((S & 3) == 0 && (quads + 255) / 256 < (1ll << 31) && ((uintptr_t)z & 15) == 0 && ((uintptr_t)t_rand & 15) == 0 &&
+      ((uintptr_t)pts & 15) == 0)
+    sample_coarse_vec4_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, as_stream(stream)>>>(rays, n, ld, t_vals, t_rand,
+                                                                                              S, lindisp, z, pts);
+  else if (n * S < (1ll << 31))
     sample_coarse_kernel<uint32_t><<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays, n, ld, t_vals, t_rand, S,
                                                                                         lindisp, z, pts);
   else
@@ -336,7 +409,11 @@ int nb_ray_points_fwd(const float* rays_o, const float* rays_d, const float* z, 
                       void* stream) {
   if (n == 0) return 0;
   NB_REQUIRE(rays_o && rays_d && z && pts && S >= 1, "nb_ray_points_fwd: bad arguments");
-  ray_points_fwd_kernel<<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, z, n, S, pts);
+  const int64_t quads = n * (S >> 2);
+  if ((S & 3) == 0 && (quads + 255) / 256 < (1ll << 31) && ((uintptr_t)z & 15) == 0 && ((uintptr_t)pts & 15) == 0)
+    ray_points_fwd_vec4_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, z, n, S, pts);
+  else
+    ray_points_fwd_kernel<<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, z, n, S, pts);
   return check_launch("nb_ray_points_fwd");
 }
 

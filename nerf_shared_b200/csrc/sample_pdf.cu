@@ -287,6 +287,165 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_fast_kernel(const float*
   }
 }
 
+// ---- sorted-u path (no per-sample output requested) ---------------------------------------------------------
+// The inverse cdf is monotone in u, so sorting u first (registers, blocked bitonic network: lane l owns the
+// SPT consecutive slots l*SPT..l*SPT+SPT-1, 13 of the 28 stages for I = 128 never leave the lane) yields the
+// importance samples already in ascending order.  The merge with the 64 ascending coarse depths is then pure
+// ranking: sample e goes to e + a_e, a_e = #{coarse <= sample} (the sample lies between the mid-points of its
+// cdf bin, so a_e is `below + 1` plus two comparisons), coarse c goes to c + #{e : a_e <= c}, a prefix sum over
+// a 65-entry histogram of the a_e.  The cdf's 62 dependent additions (torch.cumsum order) run on one lane from
+// shared memory as float4 reads / writes; every binary search is six fixed, branch-free steps.
+// Same bits as sample_pdf_merge_fast_kernel for z_out (the multiset of samples is identical).
+template <int SPT>
+__global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const float* __restrict__ z,
+                                                                      const float* __restrict__ weights,
+                                                                      const float* __restrict__ u,
+                                                                      const float* __restrict__ u_det, int64_t n, int S,
+                                                                      float* __restrict__ z_out, float* __restrict__ z_std) {
+  constexpr int I = 32 * SPT;
+  constexpr int kQ = 0, kCdf = 64, kBins = 128, kZc = 192, kHist = 264, kOut = 336, kPerWarp = kOut + 64 + I;
+  __shared__ __align__(16) float smem[8][kPerWarp];
+  const int lane = threadIdx.x & 31;
+  const int wib = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int64_t r = (int64_t)blockIdx.x * 8 + wib;
+  if (r >= n) return;
+  float* qv = smem[wib] + kQ;
+  float* cdf = smem[wib] + kCdf;
+  float* bins = smem[wib] + kBins;
+  float* zc = smem[wib] + kZc;
+  int* hist = reinterpret_cast<int*>(smem[wib] + kHist);
+  float* outb = smem[wib] + kOut;
+  const int B = S - 1;
+  const float* zr = z + r * S;
+  const float* wr = weights + r * S + 1;   // weights[..., 1:-1]: B - 1 = S - 2 entries
+  float uu[SPT];
+  {
+    const float* up = (u ? u + r * I : u_det) + lane * SPT;
+    if constexpr (SPT == 4) {
+      const float4 v = u ? __ldcs(reinterpret_cast<const float4*>(up)) : *reinterpret_cast<const float4*>(up);
+      uu[0] = v.x; uu[1] = v.y; uu[2] = v.z; uu[3] = v.w;
+    } else {
+      const float2 v = u ? __ldcs(reinterpret_cast<const float2*>(up)) : *reinterpret_cast<const float2*>(up);
+      uu[0] = v.x; uu[1] = v.y;
+    }
+  }
+  const float z0 = lane < S ? zr[lane] : CUDART_INF_F, z1 = lane + 32 < S ? zr[lane + 32] : CUDART_INF_F;
+  const float v0 = lane < B - 1 ? __fadd_rn(wr[lane], 1e-5f) : 0.f;
+  const float v1 = lane + 32 < B - 1 ? __fadd_rn(wr[lane + 32], 1e-5f) : 0.f;
+  const float wsum = warp_sum(v0 + v1);
+  qv[lane] = __fdiv_rn(v0, wsum);
+  qv[lane + 32] = __fdiv_rn(v1, wsum);
+  zc[lane] = z0;
+  zc[lane + 32] = z1;
+  if (lane < 8) zc[64 + lane] = CUDART_INF_F;
+  hist[lane] = 0;
+  hist[lane + 32] = 0;
+  if (lane < 8) hist[64 + lane] = 0;
+  __syncwarp();
+  if (lane == 0) {  // cdf[m] = sum_{i<m} q[i], the sequential fp32 sum of torch.cumsum
+    float c = 0.f;
+#pragma unroll
+    for (int g = 0; g < 16; ++g) {
+      const float4 q = reinterpret_cast<const float4*>(qv)[g];
+      float4 o;
+      o.x = c; c = __fadd_rn(c, q.x);
+      o.y = c; c = __fadd_rn(c, q.y);
+      o.z = c; c = __fadd_rn(c, q.z);
+      o.w = c; c = __fadd_rn(c, q.w);
+      reinterpret_cast<float4*>(cdf)[g] = o;
+    }
+  }
+  if (lane < B) bins[lane] = __fmul_rn(0.5f, __fadd_rn(zc[lane + 1], z0));
+  if (lane + 32 < B) bins[lane + 32] = __fmul_rn(0.5f, __fadd_rn(zc[lane + 33], z1));
+  if (u) {  // random draws: ascending sort, slot e = lane * SPT + k
+#pragma unroll
+    for (int kk = 2; kk <= I; kk <<= 1) {
+#pragma unroll
+      for (int j = kk >> 1; j > 0; j >>= 1) {
+        if (j < SPT) {
+#pragma unroll
+          for (int k = 0; k < SPT; ++k) {
+            if ((k & j) == 0) {
+              const bool up_ = (((lane * SPT + k) & kk) == 0);
+              const float lo = fminf(uu[k], uu[k | j]), hi = fmaxf(uu[k], uu[k | j]);
+              uu[k] = up_ ? lo : hi;
+              uu[k | j] = up_ ? hi : lo;
+            }
+          }
+        } else {
+          const int dl = j / SPT;
+          const bool keep_min = (((lane & dl) == 0) == (((lane * SPT) & kk) == 0));
+#pragma unroll
+          for (int k = 0; k < SPT; ++k) {
+            const float o = __shfl_xor_sync(0xffffffffu, uu[k], dl);
+            uu[k] = keep_min ? fminf(uu[k], o) : fmaxf(uu[k], o);
+          }
+        }
+      }
+    }
+  }
+  __syncwarp();
+  if (lane >= B) cdf[lane] = CUDART_INF_F;        // entries past the cdf: every search stops before them
+  if (lane + 32 >= B) cdf[lane + 32] = CUDART_INF_F;
+  __syncwarp();
+  int pos[SPT];
+#pragma unroll
+  for (int k = 0; k < SPT; ++k) pos[k] = 0;
+#pragma unroll
+  for (int step = 32; step > 0; step >>= 1) {
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) pos[k] += (cdf[pos[k] + step - 1] <= uu[k]) ? step : 0;   // searchsorted(right=True)
+  }
+  float smp[SPT], sum = 0.f;
+#pragma unroll
+  for (int k = 0; k < SPT; ++k) {
+    const int below = max(pos[k] - 1, 0), above = min(B - 1, pos[k]);
+    const float cb = cdf[below], ca = cdf[above], bb = bins[below], ba = bins[above];
+    float denom = __fsub_rn(ca, cb);
+    if (denom < 1e-5f) denom = 1.0f;
+    const float t = __fdiv_rn(__fsub_rn(uu[k], cb), denom);
+    smp[k] = __fadd_rn(bb, __fmul_rn(t, __fsub_rn(ba, bb)));
+    sum += smp[k];
+    // a_e = #{coarse <= sample}: coarse[below] <= bins[below] <= sample <= bins[above] <= coarse[below + 2]
+    const bool c1 = zc[below + 1] <= smp[k], c2 = zc[below + 2] <= smp[k];
+    int cnt = below + 1 + (c1 ? 1 : 0) + (c2 ? 1 : 0);
+    if (c2) {  // equal coarse depths (degenerate rays): count on
+      while (cnt < S && zc[cnt] <= smp[k]) ++cnt;
+    }
+    atomicAdd(hist + cnt, 1);
+    outb[lane * SPT + k + cnt] = smp[k];
+  }
+  if (z_std) {
+    const float mean = warp_sum(sum) / (float)I;
+    float var = 0.f;
+#pragma unroll
+    for (int k = 0; k < SPT; ++k) {
+      const float d = smp[k] - mean;
+      var += d * d;
+    }
+    var = warp_sum(var) / (float)I;
+    if (lane == 0) z_std[r] = sqrtf(var);
+  }
+  __syncwarp();
+  {  // coarse c = 2*lane, 2*lane+1 -> c + #{e : a_e <= c}
+    const int2 h = reinterpret_cast<const int2*>(hist)[lane];
+    const float2 zz = reinterpret_cast<const float2*>(zc)[lane];
+    const int pair = h.x + h.y;
+    int inc = pair;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int up_ = __shfl_up_sync(0xffffffffu, inc, o);
+      inc += (lane >= o) ? up_ : 0;
+    }
+    const int b0 = inc - pair + h.x, b1 = inc;
+    if (2 * lane < S) outb[2 * lane + b0] = zz.x;
+    if (2 * lane + 1 < S) outb[2 * lane + 1 + b1] = zz.y;
+  }
+  __syncwarp();
+  float* zo = z_out + r * (int64_t)(S + I);
+  for (int i = lane; i < S + I; i += 32) __stcs(zo + i, outb[i]);
+}
+
 }  // namespace nb
 
 using namespace nb;
@@ -320,7 +479,15 @@ int nb_sample_pdf_merge(const float* z, const float* weights, const float* u, co
   if (n == 0) return 0;
   NB_REQUIRE(z && weights && z_out && S >= 3 && I >= 1, "nb_sample_pdf_merge: bad arguments");
   NB_REQUIRE(u || u_det, "nb_sample_pdf_merge: need u or u_det");
-  if (S <= 64 && (I == 64 || I == 128)) {
+  if (S <= 64 && (I == 64 || I == 128) && !z_samples && (n + 7) / 8 < (1ll << 31)) {
+    const unsigned grid = (unsigned)((n + 7) / 8);   // one warp per ray
+    if (I == 128)
+      sample_pdf_merge_sorted_kernel<4><<<grid, 256, 0, as_stream(stream)>>>(z, weights, u, u_det, n, S, z_out, z_std);
+    else
+      sample_pdf_merge_sorted_kernel<2><<<grid, 256, 0, as_stream(stream)>>>(z, weights, u, u_det, n, S, z_out, z_std);
+    return check_launch("nb_sample_pdf_merge");
+  }
+  if (S <= 64 && (I == 64 || I == 128)) {   // per-sample output wanted (u order): sort after the inversion
     if (I == 128)
       sample_pdf_merge_fast_kernel<4><<<grid_for(n, 8), 256, 0, as_stream(stream)>>>(z, weights, u, u_det, n, S, z_out, z_std,
                                                                                        z_samples);

@@ -255,6 +255,31 @@ def test_sample_pdf_merge_vs_oracle(mods, det, I):
     assert bits_equal(again, z_out)
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("det", [True, False])
+@pytest.mark.parametrize("I", [128, 64])
+@pytest.mark.parametrize("S", [64, 40])
+def test_sample_pdf_merge_sorted_path_same_bits(mods, det, I, S):
+    """The production path (no per-sample output: u sorted first, rank merge through a histogram) must give the
+    same merged depths, bit for bit, as the path that inverts in u order and sorts afterwards."""
+    _ops, _ = mods
+    N = 1031
+    g = torch.Generator().manual_seed(7 * I + S)
+    near, far = torch.full((N, 1), 2.0), torch.full((N, 1), 6.0)
+    z = O.stratified_z(near, far, S, torch.rand(N, S, generator=g))
+    w = torch.rand(N, S, generator=g) ** 6
+    w[3] = 0
+    w[4, 10:] = 0                      # all mass in a few bins: many samples share one bin
+    z[6] = 3.0                         # degenerate ray: every coarse depth equal
+    u = None if det else torch.rand(N, I, generator=g)
+    uc = None if u is None else u.cuda()
+    z_a, std_a, smp = _ops.sample_pdf_merge(z.cuda(), w.cuda(), I, uc, want_samples=True)
+    z_b, std_b = _ops.sample_pdf_merge(z.cuda(), w.cuda(), I, uc)
+    assert bits_equal(z_a, z_b), n_diff(z_a, z_b)
+    np.testing.assert_allclose(std_b.cpu().numpy(), std_a.cpu().numpy(), rtol=1e-5, atol=1e-6)
+    assert bits_equal(torch.sort(torch.cat([z.cuda(), smp], -1), -1)[0], z_b)
+
+
 def test_ray_points_backward(mods):
     _ops, _ = mods
     N, S = 300, 192
