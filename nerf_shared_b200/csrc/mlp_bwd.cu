@@ -362,9 +362,29 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16_mn(int M, int N) {
   return make_idesc_bf16(M, N) | (1u << 15) | (1u << 16);  // A and B MN-major
 }
 
-__global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, const uint8_t* __restrict__ acts,
+// Work split.  A job's cost per tile is the number of 8 KB operand blocks it streams (dA blocks + activation
+// blocks); the jobs are laid end to end on one axis (job-major, `tiles` tiles each) and the axis is cut into
+// gridDim.x equal pieces, so every CTA streams the same number of bytes and owns at most one partial range of two
+// neighbouring jobs (<= 2 accumulator flushes).  ceil() on both ends of a piece assigns every (job, tile) once.
+struct WSplit {
+  int64_t cum[kNumWJobs + 1];  // cost before job j, for one tile of every job (units: blocks)
+};
+__device__ __forceinline__ void wgrad_unit(const WSplit& sp, const WJob& j, int ji, int num_tiles, int& t0, int& t1) {
+  const int64_t total = sp.cum[kNumWJobs] * num_tiles;
+  const int64_t lo = total * blockIdx.x / gridDim.x, hi = total * (blockIdx.x + 1) / gridDim.x;
+  const int64_t w = sp.cum[ji + 1] - sp.cum[ji], start = sp.cum[ji] * num_tiles;
+  const int64_t a = (lo - start + w - 1) / w, b = (hi - start + w - 1) / w;   // ceil; negative -> clamped below
+  t0 = (int)min(max(lo <= start ? (int64_t)0 : a, (int64_t)0), (int64_t)num_tiles);
+  t1 = (int)min(max(hi <= start ? (int64_t)0 : b, (int64_t)0), (int64_t)num_tiles);
+  (void)j;
+}
+
+__device__ __forceinline__ void red_add_v4(float* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+__global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit split, const uint8_t* __restrict__ acts,
                                                            const uint8_t* __restrict__ dA, int num_tiles,
-                                                           int tiles_per_unit, int num_units,
                                                            float* __restrict__ grads) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -393,10 +413,10 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, const uin
   // producer and MMA warps run converged and issue under elect.sync (see mlp_tc.cu)
   if (warp == 0) {
     uint32_t stage = 0, phase = 0;
-    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-      const WJob& j = jobs.job[u % kNumWJobs];
-      const int t0 = (u / kNumWJobs) * tiles_per_unit;
-      const int t1 = min(t0 + tiles_per_unit, num_tiles);
+    for (int ji = 0; ji < kNumWJobs; ++ji) {
+      const WJob& j = jobs.job[ji];
+      int t0, t1;
+      wgrad_unit(split, j, ji, num_tiles, t0, t1);
       const int na = j.m_blocks * 2, nb_ = j.n_cols / 64;
       for (int t = t0; t < t1; ++t) {
         const uint8_t* da_t = dA + (size_t)t * kDaSlabs * kSlabBytes + (size_t)j.a_slab * kSlabBytes;
@@ -420,10 +440,11 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, const uin
     uint32_t stage = 0, phase = 0, par_flush = 0;
     bool first_unit = true;
     const uint64_t desc0 = make_desc_mnmajor_sw128(0, 8192);
-    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-      const WJob& j = jobs.job[u % kNumWJobs];
-      const int t0 = (u / kNumWJobs) * tiles_per_unit;
-      const int t1 = min(t0 + tiles_per_unit, num_tiles);
+    for (int ji = 0; ji < kNumWJobs; ++ji) {
+      const WJob& j = jobs.job[ji];
+      int t0, t1;
+      wgrad_unit(split, j, ji, num_tiles, t0, t1);
+      if (t0 >= t1) continue;
       const int na = j.m_blocks * 2;
       const uint32_t idesc = make_idesc_bf16_mn(128, j.n_cols);
       if (!first_unit) {  // the previous unit's accumulators must be drained before they are overwritten
@@ -461,20 +482,30 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, const uin
     // flush warps: TMEM lane = out feature within the 128-block
     const int row = ((warp & 3) << 5) | lane;
     uint32_t par_acc = 0;
-    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-      const WJob j = jobs.job[u % kNumWJobs];
+    for (int ji = 0; ji < kNumWJobs; ++ji) {
+      const WJob j = jobs.job[ji];
+      int t0, t1;
+      wgrad_unit(split, j, ji, num_tiles, t0, t1);
+      if (t0 >= t1) continue;
       mbar_wait(bar_acc, par_acc);
       par_acc ^= 1;
       tc_fence_after();
+      // 16-byte reductions where every row of this job's block starts on a 16-byte boundary
+      const bool vec = j.n_valid == j.n_cols && (j.ld & 3) == 0 && (((uintptr_t)(grads + j.off)) & 15) == 0;
       for (int mb = 0; mb < j.m_blocks; ++mb) {
         float* grow = grads + j.off + (size_t)(mb * 128 + row) * j.ld;
         for (int c = 0; c < j.n_cols; c += 32) {
           uint32_t v[32];
           tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + mb * j.n_cols + c, v);
           tmem_ld_wait();
+          if (vec) {
 #pragma unroll
-          for (int q = 0; q < 32; ++q)
-            if (c + q < j.n_valid) atomicAdd(grow + c + q, __uint_as_float(v[q]));
+            for (int q = 0; q < 32; q += 4) red_add_v4(grow + c + q, v[q], v[q + 1], v[q + 2], v[q + 3]);
+          } else {
+#pragma unroll
+            for (int q = 0; q < 32; ++q)
+              if (c + q < j.n_valid) atomicAdd(grow + c + q, __uint_as_float(v[q]));
+          }
         }
       }
       tc_fence_before();
@@ -487,10 +518,11 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, const uin
     const int t = threadIdx.x - 256, c = t & 31, q = t >> 5;
     float* red = reinterpret_cast<float*>(gbase + kWSmRed);
     uint32_t stage = 0, phase = 0;
-    for (int u = blockIdx.x; u < num_units; u += gridDim.x) {
-      const WJob j = jobs.job[u % kNumWJobs];
-      const int t0 = (u / kNumWJobs) * tiles_per_unit;
-      const int t1 = min(t0 + tiles_per_unit, num_tiles);
+    for (int ji = 0; ji < kNumWJobs; ++ji) {
+      const WJob j = jobs.job[ji];
+      int t0, t1;
+      wgrad_unit(split, j, ji, num_tiles, t0, t1);
+      if (t0 >= t1) continue;
       const bool mine = j.bias_off >= 0 && c < j.m_blocks * 16;
       float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       for (int st = 2 * (t1 - t0); st > 0; --st) {
@@ -789,13 +821,15 @@ int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* act
     jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabFeat, 256, 256, 256 + in_views, off[20], off[21]};  // views[:, :256] (feature)
     jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabEncD, 64, in_views, 256 + in_views, off[20] + 256, -1};  // views[:, 256:]
     NB_REQUIRE(n == kNumWJobs, "internal: wgrad job table");
-    int tpu = (int)((tiles * kNumWJobs + 2 * kNumSMs - 1) / (2 * kNumSMs));
-    if (tpu < 4) tpu = 4;
-    const int chunks = (int)((tiles + tpu - 1) / tpu);
-    const int units = chunks * kNumWJobs;
-    const int grid = units < kNumSMs ? units : kNumSMs;
-    mlp_wgrad_kernel<<<grid, 384, kWSmemBytes, st>>>(jobs, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, tpu,
-                                                     units, grads);
+    WSplit split;
+    split.cum[0] = 0;
+    for (int i = 0; i < kNumWJobs; ++i) split.cum[i + 1] = split.cum[i] + jobs.job[i].m_blocks * 2 + jobs.job[i].n_cols / 64;
+    // at least ~4 tiles of the average job per CTA, else fewer CTAs (the flush is a fixed cost per range)
+    int64_t grid = split.cum[kNumWJobs] * tiles / (4 * (split.cum[kNumWJobs] / kNumWJobs));
+    if (grid > kNumSMs) grid = kNumSMs;
+    if (grid < 1) grid = 1;
+    mlp_wgrad_kernel<<<(int)grid, 384, kWSmemBytes, st>>>(jobs, split, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles,
+                                                          grads);
     int rc = check_launch("mlp_wgrad_kernel");
     if (rc) return rc;
   }
