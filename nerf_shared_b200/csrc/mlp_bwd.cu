@@ -110,7 +110,7 @@ __device__ __forceinline__ void dgrad_epilogue(uint32_t taddr, uint32_t act, int
       }
       if (MODE != 0) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = ((m >> (g * 8 + j)) & 1u) ? f[j] : 0.f;
+        for (int j = 0; j < 8; ++j) f[j] = ((m >> (31 - (g * 8 + j))) & 1u) ? f[j] : 0.f;
       }
       const uint32_t p0 = pack_bf16x2(f[0], f[1]), p1 = pack_bf16x2(f[2], f[3]), p2 = pack_bf16x2(f[4], f[5]),
                      p3 = pack_bf16x2(f[6], f[7]);
@@ -275,7 +275,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float t = g.x * wr[col + j] + g.y * wr[128 + col + j] + g.z * wr[256 + col + j];
-            f[j] = ((m >> (qq * 8 + j)) & 1u) ? t : 0.f;
+            f[j] = ((m >> (31 - (qq * 8 + j))) & 1u) ? t : 0.f;
           }
           const uint32_t p0 = pack_bf16x2(f[0], f[1]), p1 = pack_bf16x2(f[2], f[3]), p2 = pack_bf16x2(f[4], f[5]),
                          p3 = pack_bf16x2(f[6], f[7]);

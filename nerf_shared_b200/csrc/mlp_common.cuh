@@ -16,7 +16,7 @@ constexpr int kConstFloats = 3200;
 constexpr int kActSlabs = 40;
 constexpr int kActSlabFeat = 32, kActSlabHv = 36, kActSlabEncP = 38, kActSlabEncD = 39;
 // relu' bit masks (training): after ALL activation tiles of a launch, per tile 9 groups (h_0..h_7, view hidden) x
-// 8 chunks x 128 rows of uint32: bit j of word [group][chunk][row] = (pre-activation of column 32*chunk + j > 0).
+// 8 chunks x 128 rows of uint32: bit 31-j of word [group][chunk][row] = (pre-activation of column 32*chunk + j > 0).
 // The dgrad chain reads these 288 B per sample instead of the 4.35 KB of bf16 activations they summarise.
 constexpr int kMaskGroups = 9;
 constexpr int kMaskTileBytes = kMaskGroups * 8 * 128 * 4;   // 36864

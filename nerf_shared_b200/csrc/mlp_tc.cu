@@ -192,7 +192,7 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
 #pragma unroll
     for (int j = 0; j < 8; ++j) bq[j] = *reinterpret_cast<const float4*>(bias + c * 32 + j * 4);
     tmem_ld_wait();
-    uint32_t neg = 0;   // sign bits of the 32 pre-activations, column j at bit j
+    uint32_t neg = 0;   // sign bits of the 32 pre-activations, column j at bit 31 - j
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       float f[8];
@@ -206,7 +206,7 @@ __device__ __forceinline__ void epilogue_hidden(uint32_t taddr, const float* __r
       }
       if (MODE != 2 && mask_out) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) neg = (neg >> 1) | (__float_as_uint(f[j]) & 0x80000000u);
+        for (int j = 0; j < 8; ++j) neg = __funnelshift_l(__float_as_uint(f[j]), neg, 1);   // one SHF per value
       }
       if (MODE == 1) {
 #pragma unroll
@@ -250,7 +250,7 @@ __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __re
 #pragma unroll
     for (int j = 0; j < 8; ++j) bq[j] = *reinterpret_cast<const float4*>(bias + c * 32 + j * 4);
     tmem_ld_wait();
-    uint32_t pos = 0;   // column j of the chunk at bit j: relu output > 0
+    uint32_t pos = 0;   // sign bits of the pre-activations, column j of the chunk at bit 31 - j (stored inverted)
 #pragma unroll
     for (int g = 0; g < 4; ++g) {
       float f[8];
@@ -261,10 +261,15 @@ __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __re
         float4 w0 = *reinterpret_cast<const float4*>(wr + col);
         float4 w1 = *reinterpret_cast<const float4*>(wr + 128 + col);
         float4 w2 = *reinterpret_cast<const float4*>(wr + 256 + col);
-        f[j] = fmaxf(__uint_as_float(v[g * 8 + j]) + b.x, 0.f);
-        f[j + 1] = fmaxf(__uint_as_float(v[g * 8 + j + 1]) + b.y, 0.f);
-        f[j + 2] = fmaxf(__uint_as_float(v[g * 8 + j + 2]) + b.z, 0.f);
-        f[j + 3] = fmaxf(__uint_as_float(v[g * 8 + j + 3]) + b.w, 0.f);
+        f[j] = __uint_as_float(v[g * 8 + j]) + b.x;
+        f[j + 1] = __uint_as_float(v[g * 8 + j + 1]) + b.y;
+        f[j + 2] = __uint_as_float(v[g * 8 + j + 2]) + b.z;
+        f[j + 3] = __uint_as_float(v[g * 8 + j + 3]) + b.w;
+        if (save) {
+#pragma unroll
+          for (int jj = 0; jj < 4; ++jj) pos = __funnelshift_l(__float_as_uint(f[j + jj]), pos, 1);
+        }
+        f[j] = fmaxf(f[j], 0.f); f[j + 1] = fmaxf(f[j + 1], 0.f); f[j + 2] = fmaxf(f[j + 2], 0.f); f[j + 3] = fmaxf(f[j + 3], 0.f);
         r = fmaf(f[j], w0.x, r); r = fmaf(f[j + 1], w0.y, r); r = fmaf(f[j + 2], w0.z, r); r = fmaf(f[j + 3], w0.w, r);
         g_ = fmaf(f[j], w1.x, g_); g_ = fmaf(f[j + 1], w1.y, g_); g_ = fmaf(f[j + 2], w1.z, g_); g_ = fmaf(f[j + 3], w1.w, g_);
         b_ = fmaf(f[j], w2.x, b_); b_ = fmaf(f[j + 1], w2.y, b_); b_ = fmaf(f[j + 2], w2.z, b_); b_ = fmaf(f[j + 3], w2.w, b_);
@@ -272,11 +277,9 @@ __device__ __forceinline__ void epilogue_views(uint32_t taddr, const float* __re
       if (save) {
         st_shared_v4(act + (c >> 1) * kSlabBytes + sw128_chunk_off(row, (c & 1) * 4 + g), pack_bf16x2(f[0], f[1]),
                      pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
-#pragma unroll
-        for (int j = 0; j < 8; ++j) pos = (pos >> 1) | (f[j] > 0.f ? 0x80000000u : 0u);
       }
     }
-    if (save) mask_out[c * 128 + row] = pos;
+    if (save) mask_out[c * 128 + row] = ~pos;
   }
 }
 
