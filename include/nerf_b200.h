@@ -59,6 +59,11 @@ NB_API int nb_get_rays_bwd(int H, int W, float fx, float fy, float cx, float cy,
 /* viewdirs = rays_d / |rays_d| and its backward.  replaces: render_utils.py:211. */
 NB_API int nb_normalize_fwd(const float* v, int64_t n, float* out, void* stream);
 NB_API int nb_normalize_bwd(const float* v, const float* d_out, int64_t n, float* d_v, void* stream);
+/* The [n,11] ray rows Renderer.render builds: o(3) d(3) near far viewdirs(3), viewdirs = view_src / |view_src|
+ * (the rays before the NDC warp); `viewdirs` ([n,3], contiguous copy) may be NULL.
+ * replaces: render_utils.py:211 + :223-226 (normalise, two fills, cat) for rays that carry no gradient. */
+NB_API int nb_ray_rows(const float* rays_o, const float* rays_d, const float* view_src, float near_, float far_, int64_t n,
+                float* rows, float* viewdirs, void* stream);
 /* NDC reparametrisation.  replaces: utils.ndc_rays utils.py:54-71 (bit-exact forward). */
 NB_API int nb_ndc_rays_fwd(int H, int W, double focal, double near_, const float* rays_o, const float* rays_d, int64_t n,
                     float* out_o, float* out_d, void* stream);
@@ -112,6 +117,16 @@ NB_API int nb_composite_fwd(const float* raw, const float* z, const float* rays_
 NB_API int nb_composite_bwd(const float* raw, const float* z, const float* rays_d, const float* noise, int64_t n, int S,
                      int white_bkgd, const float* d_rgb, const float* d_disp, const float* d_acc,
                      const float* d_depth, float* d_raw, float* d_rays_d, void* stream);
+
+/* ---- photometric loss of the training step --------------------------------------------- */
+/* out4 = { mean((rgb-t)^2), mean((rgb0-t)^2) (0 when rgb0 is NULL), their sum, -10 log10(out4[0]) } over n3 floats.
+ * replaces: utils.img2mse / mse2psnr utils.py:24,27 as used at main.py:87-99. */
+NB_API int nb_mse_pair_fwd(const float* rgb, const float* rgb0, const float* target, int64_t n3, float* out4, void* stream);
+/* g_fine / g_coarse / g_total = upstream gradients of out4[0] / [1] / [2], device scalars, NULL = zero.
+ * d_rgb = (g_fine+g_total) * 2 (rgb-t)/n3, d_rgb0 = (g_coarse+g_total) * 2 (rgb0-t)/n3 (d_rgb0 may be NULL).
+ * replaces: autograd of the above (main.py:103). */
+NB_API int nb_mse_pair_bwd(const float* rgb, const float* rgb0, const float* target, int64_t n3, const float* g_fine,
+                    const float* g_coarse, const float* g_total, float* d_rgb, float* d_rgb0, void* stream);
 
 /* ---- the NeRF MLP (positional encoding fused) ---------------------------------------- */
 /* Network shape (nerf.py:61-94, use_viewdirs=True): D=8, W=256, skip after layer 4,

@@ -202,6 +202,51 @@ def invert_cdf(bins, cdf, u):
     return samples, inds
 
 
+def ray_rows(rays_o, rays_d, view_src, near, far):
+    """-> ([n,11] ray rows, [n,3] unit view directions) for rays that carry no gradient (render_utils.py:211,223-226)."""
+    lib = _lib_for(rays_o)
+    o, d, v = f32c(rays_o.detach()), f32c(rays_d.detach()), f32c(view_src.detach())
+    n = o.shape[0]
+    rows = torch.empty((n, 11), device=o.device, dtype=torch.float32)
+    vd = torch.empty((n, 3), device=o.device, dtype=torch.float32)
+    with torch.cuda.device(o.device):
+        check(lib.nb_ray_rows(ptr(o), ptr(d), ptr(v), float(near), float(far), n, ptr(rows), ptr(vd), stream_ptr()), "nb_ray_rows")
+    return rows, vd
+
+
+class MsePair(torch.autograd.Function):
+    """(loss, img_loss, img_loss0, psnr) of the training step: img2mse on the fine and coarse maps, their sum and
+    mse2psnr of the fine term (main.py:87-99, utils.py:24,27) in one launch; one launch backward."""
+
+    @staticmethod
+    def forward(ctx, rgb, rgb0, target):
+        lib = _lib_for(rgb)
+        a, t = f32c(rgb), f32c(target)
+        b = f32c(rgb0) if rgb0 is not None else None
+        if a.shape != t.shape or (b is not None and b.shape != t.shape):
+            raise ValueError("MsePair: shapes differ: %s %s %s" % (tuple(a.shape), None if b is None else tuple(b.shape), tuple(t.shape)))
+        out = torch.empty(4, device=a.device, dtype=torch.float32)
+        with torch.cuda.device(a.device):
+            check(lib.nb_mse_pair_fwd(ptr(a), ptr(b), ptr(t), a.numel(), ptr(out), stream_ptr()), "nb_mse_pair_fwd")
+        ctx.save_for_backward(a, b, t)
+        ctx.set_materialize_grads(False)
+        loss, m, m0, psnr = out[2], out[0], out[1], out[3]
+        ctx.mark_non_differentiable(psnr)
+        return loss, m, m0, psnr
+
+    @staticmethod
+    def backward(ctx, g_loss, g_m, g_m0, _g_psnr):
+        a, b, t = ctx.saved_tensors
+        lib = _lib_for(a)
+        gs = [f32c(x) if x is not None else None for x in (g_m, g_m0, g_loss)]
+        d_a = torch.empty_like(a)
+        d_b = torch.empty_like(b) if (b is not None and ctx.needs_input_grad[1]) else None
+        with torch.cuda.device(a.device):
+            check(lib.nb_mse_pair_bwd(ptr(a), ptr(b), ptr(t), a.numel(), ptr(gs[0]), ptr(gs[1]), ptr(gs[2]), ptr(d_a), ptr(d_b),
+                                      stream_ptr()), "nb_mse_pair_bwd")
+        return d_a, d_b, None
+
+
 # ----------------------------------------------------------------------------------- compositing
 class Composite(torch.autograd.Function):
     """Renderer.raw2outputs (render_utils.py:241-290)."""

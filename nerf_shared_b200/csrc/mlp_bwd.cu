@@ -604,42 +604,58 @@ __global__ void __launch_bounds__(256) mlp_small_grads_kernel(const uint8_t* __r
   const int t = threadIdx.x, g = t & 7, rg = t >> 3;
   const int t0 = blockIdx.x * tiles_per_block, t1 = min(t0 + tiles_per_block, num_tiles);
   if (t0 >= t1) return;
-  // alpha_linear: dW = sum d_sigma * h7, db = sum d_sigma ; rgb_linear: dW[k] = sum d_rgb[k] * hv, db = sum d_rgb
-  for (int s = 0; s < 4; ++s) {
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int tile = t0; tile < t1; ++tile) {
-      const uint8_t* slab = acts + ((size_t)tile * kActSlabs + 28 + s) * kSlabBytes;
+  // alpha_linear: dW = sum d_sigma * h7, db = sum d_sigma ; rgb_linear: dW[k] = sum d_rgb[k] * hv, db = sum d_rgb.
+  // One pass: per row the six 16-byte pieces (h7: 4 slabs, hv: 2 slabs) and d_raw are requested together.
+  {
+    float accA[4][8], accR[3][2][8];
 #pragma unroll
+    for (int s = 0; s < 4; ++s)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) accA[s][j] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+      for (int s = 0; s < 2; ++s)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) accR[k][s][j] = 0.f;
+    for (int tile = t0; tile < t1; ++tile) {
+      const uint8_t* tbase = acts + (size_t)tile * kActSlabs * kSlabBytes;
+#pragma unroll 2
       for (int i = 0; i < 4; ++i) {
         const int r = rg + 32 * i;
         const int64_t m = (int64_t)tile * kTileM + r;
-        const float ds = m < M ? d_raw[m * 4 + 3] : 0.f;
-        float f[8];
-        unpack8(*reinterpret_cast<const uint4*>(slab + sw128_chunk_off(r, g)), f);
+        const uint32_t off = sw128_chunk_off(r, g);
+        uint4 v[6];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = fmaf(ds, f[j], acc[j]);
-      }
-    }
-    reduce_cols(acc, red, grads + o.alpha_w + s * 64, 64);
-  }
-  for (int k = 0; k < 3; ++k) {
-    for (int s = 0; s < 2; ++s) {
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int tile = t0; tile < t1; ++tile) {
-        const uint8_t* slab = acts + ((size_t)tile * kActSlabs + kActSlabHv + s) * kSlabBytes;
+        for (int s = 0; s < 4; ++s) v[s] = *reinterpret_cast<const uint4*>(tbase + (size_t)(28 + s) * kSlabBytes + off);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int r = rg + 32 * i;
-          const int64_t m = (int64_t)tile * kTileM + r;
-          const float dk = m < M ? d_raw[m * 4 + k] : 0.f;
+        for (int s = 0; s < 2; ++s) v[4 + s] = *reinterpret_cast<const uint4*>(tbase + (size_t)(kActSlabHv + s) * kSlabBytes + off);
+        const float4 d = m < M ? *reinterpret_cast<const float4*>(d_raw + m * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float dk[3] = {d.x, d.y, d.z};
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
           float f[8];
-          unpack8(*reinterpret_cast<const uint4*>(slab + sw128_chunk_off(r, g)), f);
+          unpack8(v[s], f);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] = fmaf(dk, f[j], acc[j]);
+          for (int j = 0; j < 8; ++j) accA[s][j] = fmaf(d.w, f[j], accA[s][j]);
+        }
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+          float f[8];
+          unpack8(v[4 + s], f);
+#pragma unroll
+          for (int k = 0; k < 3; ++k)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) accR[k][s][j] = fmaf(dk[k], f[j], accR[k][s][j]);
         }
       }
-      reduce_cols(acc, red, grads + o.rgb_w + k * 128 + s * 64, 64);
     }
+#pragma unroll
+    for (int s = 0; s < 4; ++s) reduce_cols(accA[s], red, grads + o.alpha_w + s * 64, 64);
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+      for (int s = 0; s < 2; ++s) reduce_cols(accR[k][s], red, grads + o.rgb_w + k * 128 + s * 64, 64);
   }
   // head biases: sums of d_raw columns
   {

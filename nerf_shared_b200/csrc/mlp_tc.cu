@@ -511,6 +511,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
         tc_fence_after();
         if (q == 0 && h == 0 && lane == 0) NB_TR(qi, layer, x, 2);
         reuse();
+        if (q == 0 && h == 0 && lane == 0) NB_TR(qi, layer, x, 5);
         uint32_t* mk = mask ? mask + layer * 1024 : nullptr;
         if (layer < 7) epilogue_hidden<0>(taddr, cst + kOffBias + layer * 256, nullptr, sAct, row, 4 * h, sigma, mk);
         else if (layer == 7) epilogue_hidden<1>(taddr, cst + kOffBias + 7 * 256, cst + kOffAlphaW, sAct, row, 4 * h, sigma, mk);

@@ -114,6 +114,25 @@ __global__ void __launch_bounds__(256) normalize_bwd_kernel(const float* __restr
   }
 }
 
+// Ray rows of Renderer.render (render_utils.py:211,223-226): o(3) d(3) near far viewdirs(3), the view direction
+// normalised from `view_src` (the rays before the NDC warp) with normalize_fwd_kernel's arithmetic; one launch
+// instead of normalise + two fills + cat.  `viewdirs` (contiguous copy for the MLP) may be NULL.
+__global__ void __launch_bounds__(256) ray_rows_kernel(const float* __restrict__ ro, const float* __restrict__ rd,
+                                                       const float* __restrict__ view_src, float near_, float far_,
+                                                       int64_t n, float* __restrict__ rows, float* __restrict__ viewdirs) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float a = view_src[i * 3], b = view_src[i * 3 + 1], c = view_src[i * 3 + 2];
+  const float nrm = sqrtf(a * a + b * b + c * c);
+  const float va = __fdiv_rn(a, nrm), vb = __fdiv_rn(b, nrm), vc = __fdiv_rn(c, nrm);
+  float* r = rows + i * 11;
+  r[0] = ro[i * 3]; r[1] = ro[i * 3 + 1]; r[2] = ro[i * 3 + 2];
+  r[3] = rd[i * 3]; r[4] = rd[i * 3 + 1]; r[5] = rd[i * 3 + 2];
+  r[6] = near_; r[7] = far_;
+  r[8] = va; r[9] = vb; r[10] = vc;
+  if (viewdirs) { viewdirs[i * 3] = va; viewdirs[i * 3 + 1] = vb; viewdirs[i * 3 + 2] = vc; }
+}
+
 // utils.py:54-71, op by op.
 __global__ void __launch_bounds__(256) ndc_fwd_kernel(float sx, float sy, float near_, float two_near,
                                                       float neg_two_near, const float* __restrict__ ro,
@@ -353,6 +372,16 @@ int nb_normalize_fwd(const float* v, int64_t n, float* out, void* stream) {
   NB_REQUIRE(v && out, "nb_normalize_fwd: null pointer");
   normalize_fwd_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(v, n, out);
   return check_launch("nb_normalize_fwd");
+}
+
+int nb_ray_rows(const float* rays_o, const float* rays_d, const float* view_src, float near_, float far_, int64_t n,
+                float* rows, float* viewdirs, void* stream) {
+  if (n == 0) return 0;
+  NB_REQUIRE(rays_o && rays_d && view_src && rows, "nb_ray_rows: null pointer");
+  NB_REQUIRE((n + 255) / 256 < (1ll << 31), "nb_ray_rows: too many rays for one launch");
+  ray_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, view_src, near_, far_, n, rows,
+                                                                              viewdirs);
+  return check_launch("nb_ray_rows");
 }
 
 int nb_normalize_bwd(const float* v, const float* d_out, int64_t n, float* d_v, void* stream) {

@@ -56,6 +56,19 @@ class Renderer(torch.nn.Module):
     def _normal(self, shape, device, what):
         return torch.randn(shape, device=device, dtype=torch.float32)
 
+    _row_parts = None
+
+    def _columns_of(self, ray_batch):
+        """contiguous (rays_o, rays_d, viewdirs) of `ray_batch` when it is a row range of the rows render() built."""
+        if self._row_parts is None:
+            return None
+        rows, parts = self._row_parts
+        if (ray_batch.dim() != 2 or ray_batch.shape[1] != 11 or not ray_batch.is_contiguous()
+                or ray_batch.untyped_storage().data_ptr() != rows.untyped_storage().data_ptr()):
+            return None
+        i0 = (ray_batch.storage_offset() - rows.storage_offset()) // 11
+        return tuple(t[i0:i0 + ray_batch.shape[0]] for t in parts)
+
     # ------------------------------------------------------------------ entry points
     def render_from_pose(self, H, W, K, chunk, c2w, coarse_model, fine_model, retraw=True):
         return tuple(self.render(H, W, K, coarse_model, fine_model, chunk=chunk, c2w=c2w, retraw=retraw))
@@ -81,7 +94,11 @@ class Renderer(torch.nn.Module):
             raise NotImplementedError("rays without view directions (use_viewdirs=False) are not implemented")
         n = ray_batch.shape[0]
         dev = ray_batch.device
-        rays_o, rays_d, viewdirs = ray_batch[:, 0:3], ray_batch[:, 3:6], ray_batch[:, 8:11]
+        parts = self._columns_of(ray_batch)
+        if parts is not None:
+            rays_o, rays_d, viewdirs = parts
+        else:
+            rays_o, rays_d, viewdirs = ray_batch[:, 0:3], ray_batch[:, 3:6], ray_batch[:, 8:11]
         S, I = int(self.N_samples), int(self.N_importance)
 
         t_rand = self._uniform((n, S), dev, "t_rand") if self.perturb > 0.0 else None
@@ -120,18 +137,34 @@ class Renderer(torch.nn.Module):
         viewdirs = rays_d
         if c2w_staticcam is not None:
             rays_o, rays_d = utils.get_rays(H, W, K, c2w_staticcam)
-        viewdirs = _ops.Normalize.apply(viewdirs).reshape(-1, 3)
         out_shape = list(rays_d.shape[:-1])
-        if self.ndc:
-            rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
-        rays_o = rays_o.reshape(-1, 3).float()
-        rays_d = rays_d.reshape(-1, 3).float()
-        bounds = rays_d.new_empty((rays_d.shape[0], 2))
-        bounds[:, 0] = float(self.near)
-        bounds[:, 1] = float(self.far)
-        ray_rows = torch.cat([rays_o, rays_d, bounds, viewdirs], -1)
+        needs_grad = torch.is_grad_enabled() and any(torch.is_tensor(t) and t.requires_grad for t in (rays_o, rays_d, viewdirs))
+        if needs_grad:   # pose estimation: every step of the row construction is differentiable
+            viewdirs = _ops.Normalize.apply(viewdirs).reshape(-1, 3)
+            if self.ndc:
+                rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
+            rays_o = rays_o.reshape(-1, 3).float()
+            rays_d = rays_d.reshape(-1, 3).float()
+            bounds = rays_d.new_empty((rays_d.shape[0], 2))
+            bounds[:, 0] = float(self.near)
+            bounds[:, 1] = float(self.far)
+            ray_rows = torch.cat([rays_o, rays_d, bounds, viewdirs], -1)
+            parts = None
+        else:            # one kernel: normalise + near/far + concatenate
+            view_src = viewdirs.reshape(-1, 3)
+            if self.ndc:
+                rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
+            rays_o = rays_o.reshape(-1, 3).float().contiguous()
+            rays_d = rays_d.reshape(-1, 3).float().contiguous()
+            ray_rows, viewdirs = _ops.ray_rows(rays_o, rays_d, view_src, self.near, self.far)
+            parts = (rays_o, rays_d, viewdirs)
 
-        res = self.render_batch(coarse_model, fine_model, ray_rows, chunk, retraw)
+        # render_rays would have to copy the o / d / viewdirs columns back out of the rows; render() still holds them
+        self._row_parts = None if parts is None else (ray_rows, parts)
+        try:
+            res = self.render_batch(coarse_model, fine_model, ray_rows, chunk, retraw)
+        finally:
+            self._row_parts = None
         res = {k: v.reshape(out_shape + list(v.shape[1:])) for k, v in res.items()}
         head = ("rgb_map", "disp_map", "acc_map")
         return [res[k] for k in head] + [{k: v for k, v in res.items() if k not in head}]

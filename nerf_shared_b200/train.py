@@ -18,7 +18,7 @@ import math
 
 import torch
 
-from . import utils
+from . import _ops, utils
 
 
 class GraphedTrainStep:
@@ -43,11 +43,8 @@ class GraphedTrainStep:
         rgb, _, _, extras = self.renderer.render_from_rays(self.H, self.W, self.K, chunk=self.chunk, rays=self.rays,
                                                            coarse_model=self.coarse, fine_model=self.fine, retraw=True)
         opt.zero_grad()
-        img_loss = utils.img2mse(rgb, self.target)
-        loss = img_loss
-        if "rgb0" in extras:
-            loss = loss + utils.img2mse(extras["rgb0"], self.target)
-        psnr = torch.log(img_loss.detach()) * (-10.0 / math.log(10.0))     # utils.mse2psnr without its H2D constant
+        # img2mse(rgb) + img2mse(rgb0) and mse2psnr (main.py:87-99) as one launch, one launch backward
+        loss, _, _, psnr = _ops.MsePair.apply(rgb, extras.get("rgb0"), self.target)
         loss.backward()
         if self.world > 1:
             torch.distributed.all_reduce(opt.flat_g, group=self.group)

@@ -23,5 +23,5 @@ for q in (1, 2):
     for l in range(10):
         for x in range(2):
             e = t[q, l, x] - t0
-            print("%d %d %d | %9d %9d | %9d %9d %9d | issue %5d  mma_done-issue %5d  epi %5d  arr %4d" % (
-                q, l, x, e[0], e[1], e[2], e[3], e[4], e[1] - e[0], e[2] - e[1], e[3] - e[2], e[4] - e[3]))
+            print("%d %d %d | %9d %9d | %9d %9d %9d | issue %5d  mma_done-issue %5d  drain_wait %5d  epi %5d  arr %4d" % (
+                q, l, x, e[0], e[1], e[2], e[3], e[4], e[1] - e[0], e[2] - e[1], e[5] - e[2], e[3] - e[5], e[4] - e[3]))
