@@ -104,3 +104,30 @@ def test_chunk_does_not_change_result():
         a = r.render(20, 20, K, mc, mf, chunk=64, c2w=c2w, retraw=False)[0]
         b = r.render(20, 20, K, mc, mf, chunk=1 << 20, c2w=c2w, retraw=False)[0]
     assert torch.equal(a, b)
+
+
+def test_full_res_render_sampled_against_oracle():
+    """BASELINE.json configs[3]: the full 800x800 frame (640,000 rays, three internal launches) through
+    Renderer.render; 256 pixels spread over the frame are re-rendered by the CPU oracle with the same weights and
+    must agree within the 2e-3 bar; every pixel must be finite and inside the white-background range."""
+    H = W = 800
+    mc, mf = make_model(11), make_model(12)
+    r = _renderer()
+    K = O.blender_intrinsics(H, W)
+    c2w = torch.from_numpy(O.pose_spherical(75.0, -30.0, 4.0))[:3, :4]
+    with torch.no_grad():
+        rgb, disp, acc, extras = r.render(H, W, K, mc, mf, chunk=32768, c2w=c2w.cuda(), retraw=False)
+    torch.cuda.synchronize()
+    assert rgb.shape == (H, W, 3) and acc.shape == (H, W) and extras["rgb0"].shape == (H, W, 3)
+    assert torch.isfinite(rgb).all() and torch.isfinite(acc).all()
+    assert float(acc.min()) >= -1e-5 and float(acc.max()) <= 1.0 + 1e-4
+    assert float(rgb.min()) >= -1e-4 and float(rgb.max()) <= 1.0 + 2e-4
+    pix = np.random.default_rng(0).choice(H * W, 256, replace=False)
+    ro, rd = O.get_rays(H, W, K, c2w)
+    ro, rd = ro.reshape(-1, 3)[pix].contiguous(), rd.reshape(-1, 3)[pix].contiguous()
+    ref = O.render_rays(O.make_params(11), O.make_params(12), ro, rd, O.unit_viewdirs(rd), 2.0, 6.0)
+    got = rgb.reshape(-1, 3)[torch.from_numpy(pix).cuda()].cpu()
+    got0 = extras["rgb0"].reshape(-1, 3)[torch.from_numpy(pix).cuda()].cpu()
+    assert maxabs(got0, ref["rgb0"]) <= 2e-3
+    assert maxabs(got, ref["rgb_map"]) <= 2e-3
+    assert maxabs(acc.reshape(-1)[torch.from_numpy(pix).cuda()].cpu(), ref["acc_map"]) <= 2e-3

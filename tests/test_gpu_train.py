@@ -265,3 +265,40 @@ def test_sample_random_ray_batch_rays_and_targets():
         assert pix.unique().numel() == N                                          # without replacement
         assert torch.equal(batch_rays[0], ro.reshape(-1, 3)[pix])
         assert torch.equal(target.cpu(), torch.from_numpy(images[i].reshape(-1, 3))[pix.cpu()])
+
+
+def test_large_batch_gradient_is_mean_of_shard_gradients():
+    """BASELINE.json configs[2] at one GPU's share (16,384 rays): with the loss a mean over rays, the gradient of the
+    whole batch equals the average of the gradients of its ray shards -- the identity the multi-GPU all-reduce relies
+    on -- and the per-ray outputs do not depend on the batch they were rendered in."""
+    from nerf_shared_b200 import render_utils, utils
+    n, shards = 16384, 4
+    mc, mf = make_model(11), make_model(12)
+    params = list(mc.parameters()) + list(mf.parameters())
+    r = render_utils.Renderer(perturb=0.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                              raw_noise_std=0.0, near=2.0, far=6.0)
+    H = W = 400
+    K = O.blender_intrinsics(H, W)
+    c2w = cuda(O.pose_spherical(20.0, -30.0, 4.0))[:3, :4]
+    pix = torch.from_numpy(np.random.default_rng(3).choice(H * W, n, replace=False)).cuda()
+    ro, rd = utils.get_rays_at(H, W, K, c2w, pix)
+    tgt = torch.rand(n, 3, generator=torch.Generator().manual_seed(4)).cuda()
+
+    def grads(sl):
+        for p in params:
+            p.grad = None
+        rgb, _, _, ex = r.render_from_rays(H, W, K, chunk=32768, rays=torch.stack([ro[sl], rd[sl]], 0), coarse_model=mc,
+                                           fine_model=mf, retraw=True)
+        loss = utils.img2mse(rgb, tgt[sl]) + utils.img2mse(ex["rgb0"], tgt[sl])
+        loss.backward()
+        return torch.cat([p.grad.reshape(-1) for p in params]).clone(), rgb.detach().clone(), float(loss)
+
+    g_all, rgb_all, loss_all = grads(slice(0, n))
+    per = n // shards
+    parts = [grads(slice(i * per, (i + 1) * per)) for i in range(shards)]
+    g_mean = sum(p[0] for p in parts) / shards
+    assert torch.equal(torch.cat([p[1] for p in parts], 0), rgb_all)          # per-ray results are batch independent
+    assert abs(sum(p[2] for p in parts) / shards - loss_all) <= 1e-6 * loss_all
+    # fp32 atomics accumulate in a different order: tolerance relative to the gradient's scale
+    assert float((g_all - g_mean).abs().max()) <= 2e-5 * float(g_all.abs().max())
+    assert torch.isfinite(g_all).all() and float(g_all.abs().max()) > 0

@@ -24,7 +24,8 @@ def hbm_peak():
 
 
 def timed(fn, flush, reps=10):
-    for _ in range(3):
+    reps = int(os.environ.get("NB_STREAM_REPS", reps))            # NB_STREAM_REPS=1 NB_STREAM_WARMUP=0: one launch of
+    for _ in range(int(os.environ.get("NB_STREAM_WARMUP", 3))):  # each kernel, for an ncu --set full capture
         fn()
     torch.cuda.synchronize()
     tot = 0.0
