@@ -470,8 +470,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
       uint32_t* mask = save ? reinterpret_cast<uint32_t*>(acts + (size_t)((M + kTileM - 1) / kTileM) * kActSlabs * kSlabBytes +
                                                           (size_t)tile * kMaskTileBytes)
                             : nullptr;
+#if defined(NB_EXP) && (NB_EXP & 4)   // ablation build: every CTA stores to its own first tile (L2-resident target)
+      if (save) save = acts + (size_t)((blockIdx.x * 2 + x) & 31) * kActSlabs * kSlabBytes;
+#endif
+#if defined(NB_EXP) && (NB_EXP & 2)   // ablation build: no relu' masks
+      mask = nullptr;
+#endif
       const uint32_t wrow = (uint32_t)q * 4096u;
       auto flush = [&](uint32_t src_slab0, int dst_slab0, int nslabs) {
+#if defined(NB_EXP) && (NB_EXP & 1)   // ablation build: no activation stores (timing only, results are wrong)
+        return;
+#endif
         if (save && lane == 0) {
           for (int j = 0; j < nslabs; ++j)
             bulk_s2g(save + (size_t)(dst_slab0 + j) * kSlabBytes + wrow, src_slab0 + j * kSlabBytes + wrow, 4096);
@@ -553,7 +562,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
       if (save) pair_sync(pair_id);   // slab 1 (hv of the h = 1 warp) was flushed as layer 8's output by the h = 0 warp
       float r, g, b;
       // the view-branch hidden layer is staged in the (now idle) activation buffer only to be saved
-      epilogue_views(taddr, cst, r, g, b, row, 2 * h, sAct, save != nullptr, mask ? mask + 8 * 1024 : nullptr);
+      epilogue_views(taddr, cst, r, g, b, row, 2 * h, sAct, save != nullptr && mask != nullptr, mask ? mask + 8 * 1024 : nullptr);
       tc_fence_before();
       // heads: the h = 1 warp hands its partial sums to the h = 0 warp of the same rows
       if (h == 1) *part = make_float4(r, g, b, sigma);
