@@ -128,6 +128,11 @@ NB_API int nb_mse_pair_fwd(const float* rgb, const float* rgb0, const float* tar
 NB_API int nb_mse_pair_bwd(const float* rgb, const float* rgb0, const float* target, int64_t n3, const float* g_fine,
                     const float* g_coarse, const float* g_total, float* d_rgb, float* d_rgb0, void* stream);
 
+/* ---- frame output ------------------------------------------------------------------------ */
+/* out[i] = (uint8)(255 * clip(x[i], 0, 1)), NumPy's truncating cast.  replaces: utils.to8b utils.py:30 (host NumPy) in
+ * render_path / render_from_batch_poses (utils.py:330-357, render_utils.py:293-319). */
+NB_API int nb_to8b(const float* x, int64_t n, uint8_t* out, void* stream);
+
 /* ---- the NeRF MLP (positional encoding fused) ---------------------------------------- */
 /* Network shape (nerf.py:61-94, use_viewdirs=True): D=8, W=256, skip after layer 4,
  * L_pts / L_dirs encoding octaves (10 / 4 in every shipped config but one). */

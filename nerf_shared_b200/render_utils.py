@@ -186,7 +186,7 @@ class Renderer(torch.nn.Module):
                 c2w = torch.as_tensor(c2w, dtype=torch.float32)
                 rgb, _, _, _ = self.render_from_pose(H, W, K, chunk=chunk, c2w=c2w, coarse_model=coarse_model,
                                                      fine_model=fine_model, retraw=False)
-                frames.append(utils.to8b(rgb.cpu().numpy()))
+                frames.append(utils.to8b_device(rgb).cpu().numpy())     # 3 bytes per pixel cross PCIe, not 12
                 _write_image(os.path.join(save_directory, "{:03d}.png".format(i)), frames[-1])
         if b_combine_as_video and imageio is not None and hasattr(imageio, "mimwrite"):
             imageio.mimwrite(os.path.join(save_directory, "video.mp4"), frames, fps=30, quality=8)

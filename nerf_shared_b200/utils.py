@@ -13,7 +13,7 @@ import torch
 import torch.nn as nn              # noqa: F401  (the demos rely on `from utils import *` leaking nn, F)
 import torch.nn.functional as F    # noqa: F401
 
-from . import _ops
+from . import _lib, _ops
 
 device = torch.device("cuda" if torch.cuda.is_available() else "cpu")
 DEBUG = False
@@ -22,6 +22,17 @@ DEBUG = False
 img2mse = lambda x, y: torch.mean((x - y) ** 2)
 mse2psnr = lambda x: -10. * torch.log(x) / torch.log(torch.tensor([10.], device=x.device))
 to8b = lambda x: (255 * np.clip(x, 0, 1)).astype(np.uint8)
+
+
+def to8b_device(x):
+    """to8b of a CUDA float tensor on the device -> uint8 CUDA tensor (a frame leaves the GPU as bytes)."""
+    _lib.ensure_device(x.device)        # raises for CPU tensors: there is no host path here (utils.to8b is the NumPy one)
+    lib = _lib.load()
+    xc = _lib.f32c(x.detach())
+    out = torch.empty(xc.shape, device=xc.device, dtype=torch.uint8)
+    with torch.cuda.device(xc.device):
+        _lib.check(lib.nb_to8b(_lib.ptr(xc), xc.numel(), _lib.ptr(out), _lib.stream_ptr()), "nb_to8b")
+    return out
 
 
 def _on_gpu(t, like=None):
@@ -290,11 +301,12 @@ def render_path(render_poses, hwf, K, chunk, renderer_and_models, gt_imgs=None, 
         for n, c2w in enumerate(render_poses):
             rgb, disp, _, _ = renderer.render_from_pose(H, W, K, chunk, torch.as_tensor(c2w, dtype=torch.float32)[:3, :4],
                                                         coarse, fine, retraw=False)
+            rgb8 = to8b_device(rgb) if savedir is not None else None     # the PNG's bytes are made on the device
             rgbs.append(rgb.cpu().numpy())
             disps.append(disp.cpu().numpy())
             if savedir is not None:
                 from .render_utils import _write_image
-                _write_image(os.path.join(savedir, "{:03d}.png".format(n)), to8b(rgbs[-1]))
+                _write_image(os.path.join(savedir, "{:03d}.png".format(n)), rgb8.cpu().numpy())
     return np.stack(rgbs, 0), np.stack(disps, 0)
 
 

@@ -362,3 +362,14 @@ def test_ray_rows_same_bits_as_op_by_op(mods):
     ref = torch.cat([o, d, torch.full((1000, 1), 2.0).cuda(), torch.full((1000, 1), 6.0).cuda(), vd_ref], -1)
     assert bits_equal(rows, ref) and bits_equal(vd, vd_ref)
     np.testing.assert_allclose(vd_ref.cpu().numpy(), O.unit_viewdirs(d.cpu()).numpy(), rtol=0, atol=2e-7)
+
+
+def test_to8b_device_matches_numpy(mods):
+    _, utils = mods
+    g = torch.Generator().manual_seed(9)
+    x = torch.rand(37, 41, 3, generator=g) * 1.4 - 0.2          # out-of-range values on both sides
+    x[0, 0, 0], x[0, 0, 1], x[0, 0, 2] = 1.0, 0.0, 0.999999
+    ref = (255 * np.clip(x.numpy(), 0, 1)).astype(np.uint8)
+    got = utils.to8b_device(x.cuda()).cpu().numpy()
+    assert got.dtype == np.uint8 and np.array_equal(got, ref)
+    assert np.array_equal(utils.to8b_device(x.cuda().reshape(-1)[:1001]).cpu().numpy(), ref.reshape(-1)[:1001])
