@@ -8,7 +8,7 @@ A "step" is one training step of BASELINE.json configs[1]: lego-shaped synthetic
 N_rand = 1024 rays per GPU, 64 coarse + 128 fine samples, coarse + fine forward/backward + Adam
 (reference main.py:72-112).  `value` is rays/s with the step's rays and targets already in HBM;
 `e2e` is the same step through the public API (utils.sample_random_ray_batch -> Renderer ->
-loss -> backward -> optimizer.step -> loss.item()), pinned-host -> device copies and the loss
+loss -> backward -> optimizer.step -> loss read-back), pinned-host -> device copies and the loss
 read-back inside the timed region.  One JSON line on stdout (rank 0).
 """
 import argparse
@@ -200,14 +200,28 @@ def run_b200(a):
 
     def time_e2e(fn):
         """Per step: host batch sampling (pixel ids + targets gathered on the host, H2D from pinned memory), the
-        step, and a D2H read of that step's loss.  The next batch is sampled while the GPU runs the current
-        step (what a training loop does); the loss of EVERY step is still read back before the next launch."""
+        step, and a D2H read of that step's loss into pinned memory.  Software-pipelined by one step, as a training
+        loop that logs its loss does: while the GPU runs step i the host samples batch i+1, queues step i+1 and only
+        then waits for the loss of step i.  The loss of EVERY step is read back inside the timed region."""
+        host_loss = [torch.zeros(1).pin_memory() for _ in range(2)]
+        done = [torch.cuda.Event() for _ in range(2)]
+
         def loop(k):
             batch_rays, target, _, _ = sample(0)
+            prev, losses = None, []
             for i in range(k):
                 out = fn(batch_rays, target)
+                loss = out[0] if isinstance(out, tuple) else out
+                host_loss[i & 1].copy_(loss.detach().reshape(1), non_blocking=True)   # D2H of this step's loss
+                done[i & 1].record()
                 batch_rays, target, _, _ = sample(i + 1)          # overlaps the step on the GPU
-                float((out[0] if isinstance(out, tuple) else out).item())   # D2H of this step's loss
+                if prev is not None:
+                    done[prev].synchronize()
+                    losses.append(float(host_loss[prev][0]))
+                prev = i & 1
+            done[prev].synchronize()
+            losses.append(float(host_loss[prev][0]))
+            assert len(losses) == k and all(np.isfinite(losses)), losses
         loop(3)
         sync_all()
         t0 = time.perf_counter()
@@ -226,7 +240,7 @@ def run_b200(a):
     eager_ms = time_e2e(eager_step)
     h2d = a.rays * 8 + a.rays * 3 * 4      # int64 pixel ids + fp32 targets per step
     e2e = {"value": world * a.rays / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-           "ms_per_step": e2e_ms, "api": "utils.sample_random_ray_batch -> train.GraphedTrainStep -> loss.item()",
+           "ms_per_step": e2e_ms, "api": "utils.sample_random_ray_batch -> train.GraphedTrainStep -> loss D2H (pinned, read one step later)",
            "eager_main_py_loop": {"value": world * a.rays / (eager_ms * 1e-3), "ms_per_step": eager_ms}}
 
     out = {"metric": "train_rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": a.steps,
