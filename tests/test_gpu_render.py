@@ -131,3 +131,27 @@ def test_full_res_render_sampled_against_oracle():
     assert maxabs(got0, ref["rgb0"]) <= 2e-3
     assert maxabs(got, ref["rgb_map"]) <= 2e-3
     assert maxabs(acc.reshape(-1)[torch.from_numpy(pix).cuda()].cpu(), ref["acc_map"]) <= 2e-3
+
+
+def test_full_size_llff_ndc_render_sampled_against_oracle():
+    """BASELINE.json configs[4]: the fern-shaped 504x378 NDC frame (190,512 rays, 64 + 64 samples, no white
+    background) through Renderer.render; 256 pixels are re-rendered by the CPU oracle."""
+    H, W = 378, 504
+    mc, mf = make_model(11), make_model(12)
+    r = _renderer(N_importance=64, white_bkgd=False, ndc=True, near=0.0, far=1.0)
+    K = O.llff_intrinsics(H, W)
+    c2w = torch.from_numpy(O.llff_pose(0).astype(np.float32))[:3, :4]
+    with torch.no_grad():
+        rgb, disp, acc, extras = r.render(H, W, K, mc, mf, chunk=32768, c2w=c2w.cuda(), retraw=False)
+    torch.cuda.synchronize()
+    assert rgb.shape == (H, W, 3) and torch.isfinite(rgb).all() and torch.isfinite(acc).all()
+    pix = np.random.default_rng(1).choice(H * W, 256, replace=False)
+    ro, rd = O.get_rays(H, W, K, c2w)
+    vd = O.unit_viewdirs(rd)[pix]
+    ro, rd = O.ndc_rays(H, W, float(K[0][0]), 1.0, ro, rd)
+    ro, rd = ro.reshape(-1, 3)[pix].contiguous().float(), rd.reshape(-1, 3)[pix].contiguous().float()
+    ref = O.render_rays(O.make_params(11), O.make_params(12), ro, rd, vd, 0.0, 1.0, n_importance=64, white_bkgd=False)
+    sel = torch.from_numpy(pix).cuda()
+    assert maxabs(extras["rgb0"].reshape(-1, 3)[sel].cpu(), ref["rgb0"]) <= 2e-3
+    assert maxabs(rgb.reshape(-1, 3)[sel].cpu(), ref["rgb_map"]) <= 2e-3
+    assert maxabs(acc.reshape(-1)[sel].cpu(), ref["acc_map"]) <= 2e-3
