@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--rays", type=int, default=1024, help="N_rand per GPU (weak scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-render", action="store_true")
+    ap.add_argument("--large-rays", type=int, default=8192,
+                    help="rays per GPU of the large-batch leg (configs[2]: 65,536 rays/step over 8 GPUs); 0 = skip")
     return ap.parse_args()
 
 
@@ -110,6 +112,52 @@ class Args:  # the subset of config_parser flags the API helpers read (configs/l
     perturb, raw_noise_std, white_bkgd, lindisp = 1.0, 0.0, True, False
     dataset_type, no_ndc, lrate, no_batching = "blender", False, 5e-4, True
     precrop_iters, precrop_frac, chunk = 0, 0.5, 32768
+
+
+def large_batch_leg(a, args, renderer, coarse, fine, opt, K, poses_d, images, dev, world, flush, steps=5):
+    """BASELINE.json configs[2]: 65,536 rays per step ray-sharded over the GPUs of one box.  Each rank trains
+    `--large-rays` rays per step (8,192 = the share of one of 8 GPUs; device-resident batches, same graphed step,
+    gradient all-reduce inside the graph).  At this size the MLP kernels run ~40 waves, so the wave quantisation of
+    the 1,024-ray step is gone and the figure shows the per-GPU rate the kernels sustain."""
+    import torch.distributed as dist
+    from nerf_shared_b200 import train, utils
+    n = int(a.large_rays)
+    step = train.GraphedTrainStep(renderer, coarse, fine, opt, H, W, K, n, chunk=args.chunk)
+    pool = []
+    for i in range(2):
+        pix = torch.from_numpy(np.random.choice(H * W, n, replace=False)).to(dev)
+        ro, rd = utils.get_rays_at(H, W, K, poses_d[i % N_IMAGES, :3, :4], pix)
+        tgt = torch.from_numpy(images[i % N_IMAGES].reshape(-1, 3)[pix.cpu().numpy()]).to(dev)
+        pool.append((torch.stack([ro, rd], 0), tgt))
+    for i in range(3):
+        step(*pool[i % 2])
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for i in range(steps):
+        flush.zero_()
+        ev[i][0].record()
+        loss, _ = step(*pool[i % 2])
+        ev[i][1].record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    assert np.isfinite(float(loss))
+    ms = sum(s.elapsed_time(e) for s, e in ev) / steps
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    samples = n * (args.N_samples + args.N_samples + args.N_importance)
+    step.graph = None                      # releases the graph's private pool (and its NCCL capture) now
+    del step
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    return {"workload": "training step, %d rays/GPU x %d GPU(s) = %d rays/step (configs[2] is 65,536 rays/step)" % (n, world, n * world),
+            "rays_per_s": world * n / (ms * 1e-3), "ms_per_step": ms, "steps": steps,
+            "mlp_train_tflops_per_gpu": samples * 3489024 / (ms * 1e-3) / 1e12}
 
 
 def run_b200(a):
@@ -250,9 +298,14 @@ def run_b200(a):
                                   "64 coarse + 128 fine samples, D8 W256 coarse+fine fwd/bwd + Adam" % a.rays,
                       "global_rays_per_step": world * a.rays, "parallelism": "dp%d (ray-sharded, flat-gradient all-reduce)" % world,
                       "l2": "256 MiB flush between timed iterations", "timing": "CUDA events per step, max over ranks",
-                      "launch": "one CUDA graph per step (train.GraphedTrainStep)"},
+                      "launch": "one CUDA graph per step (train.GraphedTrainStep%s)" % (
+                          ", coarse backward captured as a parallel branch beside the fine pass" if step.overlap else "")},
            "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
 
+    large = None if (a.no_render or a.large_rays <= 0) else large_batch_leg(a, args, renderer, coarse, fine, opt, K, poses_d,
+                                                                             images, dev, world, flush)
+    if large is not None:
+        out["large_batch"] = large
     render = None if a.no_render else render_leg(renderer, coarse, fine, K, poses_d, dev, world)   # all ranks (row-sharded)
     if rank == 0:
         out.update(kernel_breakdown(a, coarse, fine, pool[0], dev))

@@ -57,6 +57,7 @@ class Renderer(torch.nn.Module):
         return torch.randn(shape, device=device, dtype=torch.float32)
 
     _row_parts = None
+    _after_coarse = None   # train.GraphedTrainStep: called with the coarse map before the fine pass is issued
 
     def _columns_of(self, ray_batch):
         """contiguous (rays_o, rays_d, viewdirs) of `ray_batch` when it is a row range of the rows render() built."""
@@ -110,6 +111,8 @@ class Renderer(torch.nn.Module):
         ret = {}
         if I > 0:
             ret["rgb0"], ret["disp0"], ret["acc0"] = rgb_map, disp_map, acc_map
+            if self._after_coarse is not None:
+                self._after_coarse(rgb_map, (ray_batch, rays_o, rays_d, viewdirs, t_rand, z_vals, pts, raw, weights))
             u = self._uniform((n, I), dev, "u") if self.perturb != 0.0 else None   # det = (perturb == 0)
             z_vals, z_std = _ops.sample_pdf_merge(z_vals, weights, I, u)
             pts = _ops.RayPoints.apply(rays_o, rays_d, z_vals)

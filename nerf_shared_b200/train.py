@@ -14,16 +14,16 @@ batch into the static input buffers and one 1-thread kernel that writes Adam's s
 """
 from __future__ import annotations
 
-import math
+import os
 
 import torch
 
-from . import _ops, utils
+from . import _ops, render_utils, utils
 
 
 class GraphedTrainStep:
     def __init__(self, renderer, coarse_model, fine_model, optimizer, H, W, K, n_rays, chunk=1024 * 32, group=None,
-                 warmup=2):
+                 warmup=2, overlap=None):
         self.renderer, self.coarse, self.fine, self.opt = renderer, coarse_model, fine_model, optimizer
         self.H, self.W, self.K, self.chunk = H, W, K, chunk
         self.group = group
@@ -34,11 +34,22 @@ class GraphedTrainStep:
         self.target = torch.zeros((n_rays, 3), device=dev, dtype=torch.float32)
         self.graph = None
         self._warmup = warmup
+        # overlap: the coarse backward depends only on the coarse map (main.py:99 adds the two MSE terms), so it is
+        # captured as a second branch of the graph beside the fine forward / backward.  The MLP kernels are
+        # persistent (one CTA per SM, round-robin tiles): a branch's CTAs start on the SMs the other branch's last
+        # wave leaves idle (1,024 rays: 1.73 and 5.19 waves instead of 2 and 6).
+        if overlap is None:
+            overlap = os.environ.get("NB_OVERLAP", "1") != "0"
+        self.overlap = bool(overlap) and fine_model is not None and renderer.N_importance > 0 \
+            and n_rays <= render_utils.MIN_CHUNK
+        self._coarse_stream = torch.cuda.Stream(device=dev) if self.overlap else None
         self.loss = self.psnr = None
         self.launches_per_replay = 0
 
     # main.py:77-104 with the optimizer in graph mode
     def _step(self):
+        if self.overlap:
+            return self._step_overlap()
         opt = self.opt
         rgb, _, _, extras = self.renderer.render_from_rays(self.H, self.W, self.K, chunk=self.chunk, rays=self.rays,
                                                            coarse_model=self.coarse, fine_model=self.fine, retraw=True)
@@ -50,6 +61,48 @@ class GraphedTrainStep:
             torch.distributed.all_reduce(opt.flat_g, group=self.group)
         opt.step()
         return loss.detach(), psnr
+
+    def _step_overlap(self):
+        """Same arithmetic as _step, two streams: `side` carries the coarse pass and (later) its backward, the
+        current stream the fine pass.  Tensors that cross streams stay referenced until the join, so the caching
+        allocator cannot hand their memory to the other branch."""
+        opt, r = self.opt, self.renderer
+        dev = opt.flat_p.device
+        main, side = torch.cuda.current_stream(dev), self._coarse_stream
+        alive, box = [], {}
+        opt.zero_grad()                       # before the fork: both wgrad launches accumulate into flat_g
+        side.wait_stream(main)
+
+        def after_coarse(rgb0, tensors):      # called by render_rays once the coarse map exists (still on `side`)
+            alive.append(tensors)
+            box["m0"] = _ops.MsePair.apply(rgb0, None, self.target)[1]
+            main.wait_stream(side)
+            torch.cuda.set_stream(main)       # the fine pass continues on the main stream
+
+        r._after_coarse = after_coarse
+        torch.cuda.set_stream(side)
+        try:
+            rgb, _, _, extras = r.render_from_rays(self.H, self.W, self.K, chunk=self.chunk, rays=self.rays,
+                                                   coarse_model=self.coarse, fine_model=self.fine, retraw=True)
+        finally:
+            r._after_coarse = None
+            torch.cuda.set_stream(main)
+        _, m, _, psnr = _ops.MsePair.apply(rgb, None, self.target)
+        # autograd runs a node on the stream its forward ran on; the caller's stream is switched as well so that
+        # the engine has nothing to synchronise between the two branches
+        torch.cuda.set_stream(side)
+        try:
+            box["m0"].backward()
+        finally:
+            torch.cuda.set_stream(main)
+        m.backward()
+        main.wait_stream(side)                # join
+        loss = m.detach() + box["m0"].detach()     # main.py:99
+        alive.clear()                         # only now may the coarse pass's tensors go back to the allocator
+        if self.world > 1:
+            torch.distributed.all_reduce(opt.flat_g, group=self.group)
+        opt.step()
+        return loss, psnr
 
     def _capture(self):
         opt = self.opt

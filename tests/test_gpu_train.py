@@ -186,9 +186,11 @@ def _train_setup():
     return mc, mf, r, opt
 
 
-def test_graphed_train_step_matches_eager(golden):
-    """train.GraphedTrainStep (one CUDA graph per step) == the eager main.py loop on the same batches,
-    including the learning-rate schedule written to param_groups between steps."""
+@pytest.mark.parametrize("overlap", [True, False])
+def test_graphed_train_step_matches_eager(golden, overlap):
+    """train.GraphedTrainStep (one CUDA graph per step; with `overlap` the coarse backward is a second branch of
+    the graph beside the fine pass) == the eager main.py loop on the same batches, including the learning-rate
+    schedule written to param_groups between steps."""
     from nerf_shared_b200 import train, utils
     H = W = 8
     K = O.blender_intrinsics(H, W)
@@ -212,7 +214,8 @@ def test_graphed_train_step_matches_eager(golden):
     p_eager = opt.flat_p.clone()
 
     mc2, mf2, r2, opt2 = _train_setup()
-    step = train.GraphedTrainStep(r2, mc2, mf2, opt2, H, W, K, rays.shape[1])
+    step = train.GraphedTrainStep(r2, mc2, mf2, opt2, H, W, K, rays.shape[1], overlap=overlap)
+    assert step.overlap == overlap
     graph_losses = []
     for tgt, lr in zip(targets, lrs):
         for pg in opt2.param_groups:
