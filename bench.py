@@ -312,6 +312,7 @@ def run_b200(a):
         if render is not None:
             out["render"] = render
         if world == 1 and not a.no_render:
+            out["llff_pose"] = pose_leg(dev)
             sys.path.insert(0, os.path.join(ROOT, "tools"))
             import bench_stream
             out["stream_kernels"] = bench_stream.run(quiet=True)
@@ -472,6 +473,67 @@ def render_leg(renderer, coarse, fine, K, poses_d, dev, world=1):
     tf = 640000 * (64 + 192) * FLOP_FWD / ms / 1e9
     return {"workload": "800x800 Blender render, 64+128 samples, rows split over %d GPU(s)" % world, "fps": 1e3 / ms,
             "ms_per_frame": ms, "mlp_tflops": tf, "frac_of_sustained_peak": tf / (sustained * world)}
+
+
+def pose_leg(dev, n_rays=512, steps=20):
+    """BASELINE.json configs[4]: fern-shaped LLFF scene (504x378, NDC, 64 + 64 samples): one full-frame render and
+    the pose-estimation step of examples/relative_pose_estimation_demo/demo_est_rel_pose.py:74-98 -- rays of the whole
+    grid from a pose that requires grad, a 512-pixel batch, render with frozen weights, MSE, backward to the pose."""
+    from nerf_shared_b200 import datasets, render_utils, utils
+
+    class A(Args):
+        N_importance = 64
+    Hf, Wf = 378, 504
+    images, poses, _, Kf = datasets.synthetic_llff(Hf, Wf, 2)
+    torch.manual_seed(0)
+    mc, mf = utils.create_nerf_models(A())
+    for m in (mc, mf):
+        for p in m.parameters():
+            p.requires_grad_(False)
+    r = render_utils.Renderer(perturb=0.0, N_importance=64, N_samples=64, use_viewdirs=True, white_bkgd=False,
+                              raw_noise_std=0.0, ndc=True, lindisp=False, near=0.0, far=1.0)
+    pose0 = torch.tensor(poses[0, :3, :4], device=dev)
+    with torch.no_grad():
+        for _ in range(2):
+            r.render_from_pose(Hf, Wf, Kf, 32768, pose0, mc, mf, retraw=False)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            r.render_from_pose(Hf, Wf, Kf, 32768, pose0, mc, mf, retraw=False)
+        e1.record()
+        torch.cuda.synchronize()
+    frame_ms = e0.elapsed_time(e1) / 3
+    g = torch.Generator().manual_seed(5)
+    target = torch.from_numpy(images[1].reshape(-1, 3)).to(dev)
+    pose = pose0.clone().requires_grad_(True)
+
+    def step():
+        pix = torch.randint(0, Hf * Wf, (n_rays,), generator=g).to(dev)
+        rays_o, rays_d = utils.get_rays(Hf, Wf, Kf, pose)
+        ro, rd = rays_o.reshape(-1, 3)[pix], rays_d.reshape(-1, 3)[pix]
+        rgb = r.render_from_rays(Hf, Wf, Kf, chunk=32768, rays=torch.stack([ro, rd], 0), coarse_model=mc, fine_model=mf,
+                                 retraw=True)[0]
+        loss = utils.img2mse(rgb, target[pix])
+        pose.grad = None
+        loss.backward()
+        return loss
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        loss = step()
+    gn = float(pose.grad.norm())            # D2H read of the result
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    assert np.isfinite(gn) and np.isfinite(float(loss))
+    return {"workload": "fern-shaped LLFF NDC scene 504x378, 64+64 samples (configs[4])",
+            "render_fps": 1e3 / frame_ms, "render_ms_per_frame": frame_ms,
+            "render_mlp_tflops": Hf * Wf * (64 + 128) * FLOP_FWD / frame_ms / 1e9,
+            "pose_step": {"rays": n_rays, "ms_per_step": ms, "steps_per_s": 1e3 / ms,
+                          "what": "get_rays(full grid, pose requires grad) -> 512-pixel batch -> render (frozen weights) -> "
+                                  "MSE -> backward to the 3x4 pose; eager, wall clock incl. the host"}}
 
 
 def cpu_step_fn():

@@ -580,29 +580,16 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
   }
 }
 
-// reduce acc[8] over the 32 threads that share the chunk column g, add 64 sums to dst[g*8 + j]
-__device__ __forceinline__ void reduce_cols(float (&acc)[8], float* red, float* dst, int n_valid) {
-  const int t = threadIdx.x;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) red[t * 8 + j] = acc[j];
-  __syncthreads();
-  if (t < 64) {
-    const int g = t >> 3, j = t & 7;
-    float s = 0.f;
-    for (int rg = 0; rg < 32; ++rg) s += red[(rg * 8 + g) * 8 + j];
-    if (t < n_valid) atomicAdd(dst + t, s);
-  }
-  __syncthreads();
-}
-
-__global__ void __launch_bounds__(256) mlp_small_grads_kernel(const uint8_t* __restrict__ acts,
+__global__ void __launch_bounds__(256, 2) mlp_small_grads_kernel(const uint8_t* __restrict__ acts,
                                                               const uint8_t* __restrict__ dA,
                                                               const float* __restrict__ d_raw, int64_t M,
                                                               int num_tiles, int tiles_per_block, SmallOffsets o,
                                                               float* __restrict__ grads) {
-  __shared__ float red[256 * 8];
+  __shared__ float red[8 * 80 * 8];
   const int t = threadIdx.x, g = t & 7, rg = t >> 3;
-  const int t0 = blockIdx.x * tiles_per_block, t1 = min(t0 + tiles_per_block, num_tiles);
+  // equal tile ranges over a grid of at most two blocks per SM (tiles_per_block is unused)
+  const int t0 = (int)((int64_t)num_tiles * blockIdx.x / gridDim.x), t1 = (int)((int64_t)num_tiles * (blockIdx.x + 1) / gridDim.x);
+  (void)tiles_per_block;
   if (t0 >= t1) return;
   // alpha_linear: dW = sum d_sigma * h7, db = sum d_sigma ; rgb_linear: dW[k] = sum d_rgb[k] * hv, db = sum d_rgb.
   // One pass: per row the six 16-byte pieces (h7: 4 slabs, hv: 2 slabs) and d_raw are requested together.
@@ -650,12 +637,42 @@ __global__ void __launch_bounds__(256) mlp_small_grads_kernel(const uint8_t* __r
         }
       }
     }
+    // sum over the block's 32 row groups: the four of a warp by shuffles (lane bits 3, 4), the eight warps through
+    // shared memory in one pass (one barrier instead of two per 64 columns)
+    float* flat = &accA[0][0];
+    float* flatR = &accR[0][0][0];
 #pragma unroll
-    for (int s = 0; s < 4; ++s) reduce_cols(accA[s], red, grads + o.alpha_w + s * 64, 64);
+    for (int i = 0; i < 32; ++i) {
+      flat[i] += __shfl_xor_sync(0xffffffffu, flat[i], 8);
+      flat[i] += __shfl_xor_sync(0xffffffffu, flat[i], 16);
+    }
 #pragma unroll
-    for (int k = 0; k < 3; ++k)
+    for (int i = 0; i < 48; ++i) {
+      flatR[i] += __shfl_xor_sync(0xffffffffu, flatR[i], 8);
+      flatR[i] += __shfl_xor_sync(0xffffffffu, flatR[i], 16);
+    }
+    const int lane = t & 31, warp = t >> 5;
+    if (lane < 8) {  // lane == g; value index v = s*8+j (alpha, 32 values) or 32 + (k*2+s)*8+j (rgb, 48 values)
 #pragma unroll
-      for (int s = 0; s < 2; ++s) reduce_cols(accR[k][s], red, grads + o.rgb_w + k * 128 + s * 64, 64);
+      for (int i = 0; i < 32; ++i) red[(warp * 80 + i) * 8 + lane] = flat[i];
+#pragma unroll
+      for (int i = 0; i < 48; ++i) red[(warp * 80 + 32 + i) * 8 + lane] = flatR[i];
+    }
+    __syncthreads();
+    for (int idx = t; idx < 640; idx += 256) {
+      const int v = idx >> 3, gg = idx & 7;
+      float sum = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) sum += red[(w * 80 + v) * 8 + gg];
+      float* dst;
+      if (v < 32) {
+        dst = grads + o.alpha_w + (v >> 3) * 64 + gg * 8 + (v & 7);
+      } else {
+        const int u = v - 32, k = u >> 4, sl = (u >> 3) & 1;
+        dst = grads + o.rgb_w + k * 128 + sl * 64 + gg * 8 + (u & 7);
+      }
+      atomicAdd(dst, sum);
+    }
   }
   // head biases: sums of d_raw columns
   {
@@ -854,9 +871,8 @@ int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* act
     for (int l = 0; l < 8; ++l) o.pts_b[l] = off[8 + l];
     o.feature_b = off[17]; o.views_b = off[21]; o.alpha_w = off[18]; o.alpha_b = off[19];
     o.rgb_w = off[22]; o.rgb_b = off[23];
-    int tpb = (int)((tiles + 2 * kNumSMs - 1) / (2 * kNumSMs));
-    if (tpb < 1) tpb = 1;
-    const int grid = (int)((tiles + tpb - 1) / tpb);
+    const int tpb = 0;
+    const int grid = (int)(tiles < 2 * kNumSMs ? tiles : 2 * kNumSMs);
     mlp_small_grads_kernel<<<grid, 256, 0, st>>>((const uint8_t*)acts, (const uint8_t*)dA, d_raw, M, (int)tiles, tpb, o,
                                                  grads);
     int rc = check_launch("mlp_small_grads_kernel");

@@ -20,6 +20,27 @@ def synthetic_blender(H=400, W=400, n_images=8, seed=0):
     return images, poses.astype(np.float32), [H, W, focal], K
 
 
+def synthetic_llff(H=378, W=504, n_images=4, seed=0):
+    """LLFF-shaped synthetic scene (configs/fern.txt at factor 8): focal = 3260.5 / 8,
+    forward-facing poses = identity rotation perturbed by small rotations, N(0, 0.05^2) translations."""
+    rng = np.random.default_rng(seed)
+    focal = 3260.5 / 8.0 * (W / 504.0)
+    K = np.array([[focal, 0, 0.5 * W], [0, focal, 0.5 * H], [0, 0, 1]])
+    poses = []
+    for _ in range(n_images):
+        w = rng.normal(0.0, 0.02, 3)                       # small rotation vector
+        th = np.linalg.norm(w) + 1e-12
+        k = w / th
+        Kx = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
+        R = np.eye(3) + np.sin(th) * Kx + (1 - np.cos(th)) * (Kx @ Kx)
+        c2w = np.eye(4)
+        c2w[:3, :3] = R
+        c2w[:3, 3] = rng.normal(0.0, 0.05, 3)
+        poses.append(c2w)
+    images = np.random.default_rng(seed + 1).random((n_images, H, W, 3), dtype=np.float32)
+    return images, np.stack(poses, 0).astype(np.float32), [H, W, focal], K
+
+
 def _pose_spherical(theta, phi, radius):
     # load_blender.py:10-32 / load_LINEMOD.py:29-34
     t = np.eye(4); t[2, 3] = radius

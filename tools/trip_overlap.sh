@@ -1,9 +1,14 @@
 #!/bin/bash
-# A/B of the two-branch training graph (NB_OVERLAP=0/1) + the train tests
+# A/B of the graph concurrency switches (NB_OVERLAP: two-branch training graph, NB_FORK_HEADS: head gradients on a
+# forked stream) + the MLP / train tests
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_train.py -m gpu -q --tb=short -x > gpurun_out/t_train.log 2>&1; echo "train tests exit $?"; tail -5 gpurun_out/t_train.log
-for ov in 0 1 0 1; do
-  NB_OVERLAP=$ov timeout 600 python bench.py --no-cpu-baseline --no-render --steps 40 2>gpurun_out/bench_ov$ov.err | tail -n 1 > gpurun_out/bench_ov$ov.json; echo "bench ov=$ov exit $?"
+for t in mlp train; do
+timeout 600 python -m pytest tests/test_gpu_$t.py -m gpu -q --tb=short -x > gpurun_out/t_$t.log 2>&1; echo "$t tests exit $?"; tail -3 gpurun_out/t_$t.log
+done
+for cfg in "1 0" "1 1" "1 0" "1 1" "0 1"; do
+  set -- $cfg
+  tag=ov$1_fk$2
+  NB_OVERLAP=$1 NB_FORK_HEADS=$2 timeout 600 python bench.py --no-cpu-baseline --no-render --steps 40 2>gpurun_out/bench_$tag.err | tail -n 1 > gpurun_out/bench_$tag.json; echo "bench $tag exit $?"
   python -c "
-import json;d=json.load(open('gpurun_out/bench_ov$ov.json'));print('overlap=$ov', d['value'],d['ms_per_step'],d['e2e']['value'], d['gpu_launches'], d['config']['launch'])" || tail -20 gpurun_out/bench_ov$ov.err
+import json;d=json.load(open('gpurun_out/bench_$tag.json'));print('$tag', d['value'],d['ms_per_step'],d['e2e']['value'], d['e2e']['eager_main_py_loop']['value'], d['gpu_launches'])" || tail -20 gpurun_out/bench_$tag.err
 done
