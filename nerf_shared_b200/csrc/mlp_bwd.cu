@@ -580,21 +580,56 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
   }
 }
 
-__global__ void __launch_bounds__(256, 2) mlp_small_grads_kernel(const uint8_t* __restrict__ acts,
-                                                              const uint8_t* __restrict__ dA,
-                                                              const float* __restrict__ d_raw, int64_t M,
-                                                              int num_tiles, int tiles_per_block, SmallOffsets o,
-                                                              float* __restrict__ grads) {
-  __shared__ float red[8 * 80 * 8];
-  const int t = threadIdx.x, g = t & 7, rg = t >> 3;
-  // equal tile ranges over a grid of at most two blocks per SM (tiles_per_block is unused)
+// One CTA per SM, 8 consumer warps + 1 producer warp.  The producer stages whole tiles -- h7 (4 slabs, 64 KB
+// contiguous), hv (2 slabs, 32 KB contiguous) and the tile's 128 d_raw rows (2 KB) -- with 1-D bulk copies into a
+// two-stage ring (2 x 98 KB in flight per SM: the register-staged version of this kernel had ~23 KB in flight and
+// ran at 3.4 TB/s, latency-bound); the consumers read the swizzled slab image from shared memory.
+// alpha_linear: dW = sum d_sigma * h7, db = sum d_sigma ; rgb_linear: dW[k] = sum d_rgb[k] * hv, db = sum d_rgb.
+constexpr int kHgStages = 2;
+constexpr uint32_t kHgStageBytes = 6 * kSlabBytes + kTileM * 16;
+constexpr uint32_t kHgSmRed = kHgStages * kHgStageBytes;   // [8 warps][80 values][8 chunks] fp32
+constexpr uint32_t kHgSmBar = kHgSmRed + 8 * 80 * 8 * 4;
+constexpr uint32_t kHgSmemBytes = kHgSmBar + 64 + 1024;
+
+__global__ void __launch_bounds__(288, 1) mlp_small_grads_kernel(const uint8_t* __restrict__ acts,
+                                                                 const float* __restrict__ d_raw, int64_t M,
+                                                                 int num_tiles, SmallOffsets o,
+                                                                 float* __restrict__ grads) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t bar_full = base + kHgSmBar, bar_empty = bar_full + 8 * kHgStages;
+  const int t = threadIdx.x, lane = t & 31;
+  const int warp = __shfl_sync(0xffffffffu, t >> 5, 0);
   const int t0 = (int)((int64_t)num_tiles * blockIdx.x / gridDim.x), t1 = (int)((int64_t)num_tiles * (blockIdx.x + 1) / gridDim.x);
-  (void)tiles_per_block;
-  if (t0 >= t1) return;
-  // alpha_linear: dW = sum d_sigma * h7, db = sum d_sigma ; rgb_linear: dW[k] = sum d_rgb[k] * hv, db = sum d_rgb.
-  // One pass: per row the six 16-byte pieces (h7: 4 slabs, hv: 2 slabs) and d_raw are requested together.
-  {
-    float accA[4][8], accR[3][2][8];
+  if (t == 0) {
+    for (int i = 0; i < kHgStages; ++i) {
+      mbar_init(bar_full + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 8);   // one arrival per consumer warp
+    }
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (warp == 8) {
+    uint32_t stage = 0, phase = 0;
+    for (int tile = t0; tile < t1; ++tile) {
+      mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+      if (elect_one()) {
+        const int64_t left = M - (int64_t)tile * kTileM;
+        const uint32_t rows = (uint32_t)(left < kTileM ? left : kTileM);
+        const uint8_t* tb = acts + (size_t)tile * kActSlabs * kSlabBytes;
+        const uint32_t dst = base + stage * kHgStageBytes;
+        mbar_expect_tx(bar_full + 8 * stage, 6 * kSlabBytes + rows * 16);
+        bulk_g2s(dst, tb + (size_t)28 * kSlabBytes, 4 * kSlabBytes, bar_full + 8 * stage);
+        bulk_g2s(dst + 4 * kSlabBytes, tb + (size_t)kActSlabHv * kSlabBytes, 2 * kSlabBytes, bar_full + 8 * stage);
+        bulk_g2s(dst + 6 * kSlabBytes, d_raw + (size_t)tile * kTileM * 4, rows * 16, bar_full + 8 * stage);
+      }
+      __syncwarp();
+      if (++stage == kHgStages) { stage = 0; phase ^= 1; }
+    }
+  } else {
+    const int g = t & 7, rg = t >> 3;
+    float accA[4][8], accR[3][2][8], a4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int s = 0; s < 4; ++s)
 #pragma unroll
@@ -605,8 +640,10 @@ __global__ void __launch_bounds__(256, 2) mlp_small_grads_kernel(const uint8_t* 
       for (int s = 0; s < 2; ++s)
 #pragma unroll
         for (int j = 0; j < 8; ++j) accR[k][s][j] = 0.f;
+    uint32_t stage = 0, phase = 0;
     for (int tile = t0; tile < t1; ++tile) {
-      const uint8_t* tbase = acts + (size_t)tile * kActSlabs * kSlabBytes;
+      mbar_wait(bar_full + 8 * stage, phase);
+      const uint8_t* sb = gbase + stage * kHgStageBytes;
 #pragma unroll 2
       for (int i = 0; i < 4; ++i) {
         const int r = rg + 32 * i;
@@ -614,11 +651,10 @@ __global__ void __launch_bounds__(256, 2) mlp_small_grads_kernel(const uint8_t* 
         const uint32_t off = sw128_chunk_off(r, g);
         uint4 v[6];
 #pragma unroll
-        for (int s = 0; s < 4; ++s) v[s] = *reinterpret_cast<const uint4*>(tbase + (size_t)(28 + s) * kSlabBytes + off);
-#pragma unroll
-        for (int s = 0; s < 2; ++s) v[4 + s] = *reinterpret_cast<const uint4*>(tbase + (size_t)(kActSlabHv + s) * kSlabBytes + off);
-        const float4 d = m < M ? *reinterpret_cast<const float4*>(d_raw + m * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int s = 0; s < 6; ++s) v[s] = *reinterpret_cast<const uint4*>(sb + (size_t)s * kSlabBytes + off);
+        const float4 d = m < M ? *reinterpret_cast<const float4*>(sb + 6 * kSlabBytes + r * 16) : make_float4(0.f, 0.f, 0.f, 0.f);
         const float dk[3] = {d.x, d.y, d.z};
+        if (g == 0) { a4[0] += d.x; a4[1] += d.y; a4[2] += d.z; a4[3] += d.w; }   // head biases: column sums of d_raw
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
           float f[8];
@@ -636,9 +672,13 @@ __global__ void __launch_bounds__(256, 2) mlp_small_grads_kernel(const uint8_t* 
             for (int j = 0; j < 8; ++j) accR[k][s][j] = fmaf(dk[k], f[j], accR[k][s][j]);
         }
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_empty + 8 * stage);
+      if (++stage == kHgStages) { stage = 0; phase ^= 1; }
     }
     // sum over the block's 32 row groups: the four of a warp by shuffles (lane bits 3, 4), the eight warps through
-    // shared memory in one pass (one barrier instead of two per 64 columns)
+    // shared memory in one pass
+    float* red = reinterpret_cast<float*>(gbase + kHgSmRed);
     float* flat = &accA[0][0];
     float* flatR = &accR[0][0][0];
 #pragma unroll
@@ -651,14 +691,13 @@ __global__ void __launch_bounds__(256, 2) mlp_small_grads_kernel(const uint8_t* 
       flatR[i] += __shfl_xor_sync(0xffffffffu, flatR[i], 8);
       flatR[i] += __shfl_xor_sync(0xffffffffu, flatR[i], 16);
     }
-    const int lane = t & 31, warp = t >> 5;
     if (lane < 8) {  // lane == g; value index v = s*8+j (alpha, 32 values) or 32 + (k*2+s)*8+j (rgb, 48 values)
 #pragma unroll
       for (int i = 0; i < 32; ++i) red[(warp * 80 + i) * 8 + lane] = flat[i];
 #pragma unroll
       for (int i = 0; i < 48; ++i) red[(warp * 80 + 32 + i) * 8 + lane] = flatR[i];
     }
-    __syncthreads();
+    asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight consumer warps
     for (int idx = t; idx < 640; idx += 256) {
       const int v = idx >> 3, gg = idx & 7;
       float sum = 0.f;
@@ -673,17 +712,9 @@ __global__ void __launch_bounds__(256, 2) mlp_small_grads_kernel(const uint8_t* 
       }
       atomicAdd(dst, sum);
     }
-  }
-  // head biases: sums of d_raw columns
-  {
-    float a4[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int64_t m = (int64_t)t0 * kTileM + t; m < (int64_t)t1 * kTileM && m < M; m += 256) {
-      const float4 d = *reinterpret_cast<const float4*>(d_raw + m * 4);
-      a4[0] += d.x; a4[1] += d.y; a4[2] += d.z; a4[3] += d.w;
-    }
 #pragma unroll
     for (int k = 0; k < 4; ++k) a4[k] = warp_sum(a4[k]);
-    if ((t & 31) == 0) {
+    if (lane == 0) {
       atomicAdd(grads + o.rgb_b + 0, a4[0]);
       atomicAdd(grads + o.rgb_b + 1, a4[1]);
       atomicAdd(grads + o.rgb_b + 2, a4[2]);
@@ -753,6 +784,8 @@ int init_mlp_bwd(int) {
   cudaError_t e = cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBSmemBytes);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemBytes);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(mlp_small_grads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kHgSmemBytes);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(umma_mn_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 16384 + 2048);
   if (e != cudaSuccess) {
@@ -871,10 +904,9 @@ int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* act
     for (int l = 0; l < 8; ++l) o.pts_b[l] = off[8 + l];
     o.feature_b = off[17]; o.views_b = off[21]; o.alpha_w = off[18]; o.alpha_b = off[19];
     o.rgb_w = off[22]; o.rgb_b = off[23];
-    const int tpb = 0;
-    const int grid = (int)(tiles < 2 * kNumSMs ? tiles : 2 * kNumSMs);
-    mlp_small_grads_kernel<<<grid, 256, 0, st>>>((const uint8_t*)acts, (const uint8_t*)dA, d_raw, M, (int)tiles, tpb, o,
-                                                 grads);
+    NB_REQUIRE(((uintptr_t)d_raw & 15) == 0, "nb_mlp_bwd_tc: d_raw must be 16-byte aligned");
+    const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
+    mlp_small_grads_kernel<<<grid, 288, kHgSmemBytes, st>>>((const uint8_t*)acts, d_raw, M, (int)tiles, o, grads);
     int rc = check_launch("mlp_small_grads_kernel");
     if (rc) return rc;
   }

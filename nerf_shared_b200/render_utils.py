@@ -103,8 +103,11 @@ class Renderer(torch.nn.Module):
         S, I = int(self.N_samples), int(self.N_importance)
 
         t_rand = self._uniform((n, S), dev, "t_rand") if self.perturb > 0.0 else None
-        z_vals = _ops.sample_coarse(ray_batch, S, t_rand, self.lindisp)
-        pts = _ops.RayPoints.apply(rays_o, rays_d, z_vals)
+        if torch.is_grad_enabled() and (rays_o.requires_grad or rays_d.requires_grad):
+            z_vals = _ops.sample_coarse(ray_batch, S, t_rand, self.lindisp)
+            pts = _ops.RayPoints.apply(rays_o, rays_d, z_vals)      # pose estimation: differentiable in o, d
+        else:                                                        # depths and points from one launch
+            z_vals, pts = _ops.sample_coarse(ray_batch, S, t_rand, self.lindisp, want_pts=True)
         raw = coarse_model(pts, viewdirs)
         rgb_map, disp_map, acc_map, weights, depth_map = self.raw2outputs(raw, z_vals, rays_d, _what="noise_c")
 

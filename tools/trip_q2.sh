@@ -1,6 +1,8 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_mlp.py -m gpu -q --tb=short -x > gpurun_out/t_mlp.log 2>&1; echo "mlp tests exit $?"; tail -2 gpurun_out/t_mlp.log
+for t in mlp train pose; do
+timeout 600 python -m pytest tests/test_gpu_$t.py -m gpu -q --tb=short -x > gpurun_out/t_$t.log 2>&1; echo "$t tests exit $?"; tail -2 gpurun_out/t_$t.log
+done
 for i in 1 2; do
 timeout 900 python bench.py --no-cpu-baseline --no-render --steps 40 2>gpurun_out/bench_q.err | tail -n 1 > gpurun_out/bench_q.json; echo "bench exit $?"
 python -c "
