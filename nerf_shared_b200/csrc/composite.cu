@@ -158,6 +158,84 @@ __global__ void __launch_bounds__(256) composite_fwd_kernel(const float* __restr
   }
 }
 
+// S == 64 (the coarse pass of every shipped config): half a warp per ray, lane owns 4 consecutive samples.  Same
+// arithmetic per sample as RayRegs; the scan and the five reductions are 16 lanes wide and every instruction serves
+// two rays, which halves the instructions per ray (the 32-lane version of this size is issue-bound, not HBM-bound).
+__global__ void __launch_bounds__(256) composite_fwd_s64_kernel(const float* __restrict__ raw,
+                                                                const float* __restrict__ z,
+                                                                const float* __restrict__ rays_d,
+                                                                const float* __restrict__ noise, int64_t n,
+                                                                int white_bkgd, float* __restrict__ rgb_map,
+                                                                float* __restrict__ disp, float* __restrict__ acc_out,
+                                                                float* __restrict__ weights, float* __restrict__ depth) {
+  constexpr int S = 64, C = 4;
+  const int lane = threadIdx.x & 31, sub = lane & 15;
+  const int64_t r_raw = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 2 + (lane >> 4);
+  const bool live = r_raw < n;
+  const int64_t r = live ? r_raw : n - 1;
+  const int64_t base = r * S + sub * C;
+  float4 c[C];
+  const float4* rp = reinterpret_cast<const float4*>(raw) + base;
+#pragma unroll
+  for (int j = 0; j < C; ++j) c[j] = __ldcs(rp + j);
+  const float4 zv = __ldcs(reinterpret_cast<const float4*>(z + base));
+  const float4 nv = noise ? __ldcs(reinterpret_cast<const float4*>(noise + base)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  const float zz[C] = {zv.x, zv.y, zv.z, zv.w}, nz[C] = {nv.x, nv.y, nv.z, nv.w};
+  const float d0 = rays_d[r * 3], d1 = rays_d[r * 3 + 1], d2 = rays_d[r * 3 + 2];
+  const float dnorm = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);
+  const float znext = __shfl_down_sync(0xffffffffu, zz[0], 1);
+  float alpha[C], T[C], prod = 1.0f;
+#pragma unroll
+  for (int j = 0; j < C; ++j) {
+    const float nx = j + 1 < C ? zz[j + 1 < C ? j + 1 : j] : znext;
+    const float dz = (sub * C + j + 1 >= S) ? 1e10f : nx - zz[j];
+    const float rs = fmaxf(c[j].w + nz[j], 0.0f);
+    const float a = 1.0f - expf(-rs * (dz * dnorm));
+    c[j] = make_float4(sigmoidf_(c[j].x), sigmoidf_(c[j].y), sigmoidf_(c[j].z), rs);
+    alpha[j] = a;
+    T[j] = prod;
+    prod *= 1.0f - a + 1e-10f;
+  }
+  float inc = prod;
+#pragma unroll
+  for (int o = 1; o < 16; o <<= 1) {
+    const float up = __shfl_up_sync(0xffffffffu, inc, o, 16);
+    inc *= (sub >= o) ? up : 1.0f;
+  }
+  const float exu = __shfl_up_sync(0xffffffffu, inc, 1, 16);
+  const float ex = sub == 0 ? 1.0f : exu;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, adepth = 0.f, aacc = 0.f, w[C];
+#pragma unroll
+  for (int j = 0; j < C; ++j) {
+    w[j] = alpha[j] * (T[j] * ex);
+    a0 += w[j] * c[j].x; a1 += w[j] * c[j].y; a2 += w[j] * c[j].z;
+    adepth += w[j] * zz[j];
+    aacc += w[j];
+  }
+  if (weights && live) __stcs(reinterpret_cast<float4*>(weights + base), make_float4(w[0], w[1], w[2], w[3]));
+#pragma unroll
+  for (int o = 8; o > 0; o >>= 1) {
+    a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+    a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+    a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+    adepth += __shfl_xor_sync(0xffffffffu, adepth, o);
+    aacc += __shfl_xor_sync(0xffffffffu, aacc, o);
+  }
+  if (sub == 0 && live) {
+    if (rgb_map) {
+      const float bg = white_bkgd ? (1.0f - aacc) : 0.0f;
+      rgb_map[r * 3] = a0 + bg; rgb_map[r * 3 + 1] = a1 + bg; rgb_map[r * 3 + 2] = a2 + bg;
+    }
+    if (acc_out) acc_out[r] = aacc;
+    if (depth) depth[r] = adepth;
+    if (disp) {
+      const float ratio = adepth / aacc;                              // nan when acc == 0 (reference keeps it)
+      const float m = (ratio != ratio) ? ratio : fmaxf(1e-10f, ratio);
+      disp[r] = 1.0f / m;
+    }
+  }
+}
+
 // Reverse pass: dL/dw_s = g_s, dL/dalpha_s = g_s T_s - (sum_{k>s} g_k w_k) / q_s; the suffix sum is a serial sum
 // inside the lane plus one warp scan of the lane totals.  Nothing but the ray's registers is live between the two
 // directions (g_s is recomputed: five FMAs).
@@ -266,7 +344,11 @@ int nb_composite_fwd(const float* raw, const float* z, const float* rays_d, cons
       composite_fwd_kernel<C, false><<<grid, 256, 0, st>>>(raw, z, rays_d, noise, n, S, white_bkgd, rgb_map, disp,    \
                                                            acc, weights, depth);                                      \
   } while (0)
-  if (S <= 64) NB_LAUNCH_FWD(2);
+  const bool al16 = (((uintptr_t)raw | (uintptr_t)z | (uintptr_t)noise | (uintptr_t)weights) & 15) == 0;
+  if (S == 64 && al16 && (n + 15) / 16 < (1ll << 31))
+    composite_fwd_s64_kernel<<<(unsigned)((n + 15) / 16), 256, 0, st>>>(raw, z, rays_d, noise, n, white_bkgd, rgb_map, disp,
+                                                                      acc, weights, depth);
+  else if (S <= 64) NB_LAUNCH_FWD(2);
   else if (S <= 128) NB_LAUNCH_FWD(4);
   else if (S <= 192) NB_LAUNCH_FWD(6);
   else if (S <= 256) NB_LAUNCH_FWD(8);

@@ -221,20 +221,41 @@ __global__ void __launch_bounds__(256) sample_coarse_kernel(const float* __restr
   }
 }
 
+// A thread that owns 4 consecutive samples holds 12 consecutive floats of pts; written straight from registers the
+// three 16-byte stores of a warp each touch all 48 sectors of the warp's 1,536 bytes (lane stride 48 B).  Staged
+// through shared memory every store instruction covers 512 contiguous bytes (a third of the L2 write requests).
+__device__ __forceinline__ void store_points_warp(float* __restrict__ pts, int64_t warp_q0, int valid_quads,
+                                                  const float (&p)[12], float4* sm) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) sm[lane * 3 + k] = make_float4(p[4 * k], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3]);
+  __syncwarp();
+  float4* out = reinterpret_cast<float4*>(pts) + warp_q0 * 3;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int idx = k * 32 + lane;
+    if (idx < 3 * valid_quads) __stcs(out + idx, sm[idx]);
+  }
+}
+
 // Four consecutive samples of one ray per thread (S % 4 == 0): one 16-byte load of the jitter, one 16-byte store
 // of z (three more for the points), six instead of twelve z_at evaluations.  Same arithmetic, bit for bit.
+template <typename IDX>
 __global__ void __launch_bounds__(256) sample_coarse_vec4_kernel(const float* __restrict__ rays, int64_t n, int ld,
                                                                  const float* __restrict__ t_vals,
                                                                  const float* __restrict__ t_rand, int S, int lindisp,
                                                                  float* __restrict__ z_out, float* __restrict__ pts) {
-  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // quad index
+  __shared__ float4 stage[8][96];
   const int qpr = S >> 2;
-  if (q >= n * qpr) return;
-  const int64_t r = q / qpr;
-  const int s0 = (int)(q - r * qpr) << 2;
+  const IDX total = (IDX)(n * qpr);
+  const IDX q_raw = (IDX)blockIdx.x * blockDim.x + threadIdx.x;   // quad index
+  const bool live = q_raw < total;
+  const IDX q = live ? q_raw : total - 1;
+  const IDX r = q / (IDX)qpr;
+  const int s0 = (int)(q - r * (IDX)qpr) << 2;
   float4 tr = make_float4(0.f, 0.f, 0.f, 0.f);
   if (t_rand) tr = __ldcs(reinterpret_cast<const float4*>(t_rand) + q);
-  const float* ray = rays + r * ld;
+  const float* ray = rays + (int64_t)r * ld;
   const float near_ = ray[6], far_ = ray[7];
   float zs[6];   // z_at(s0 - 1 .. s0 + 4)
 #pragma unroll
@@ -255,38 +276,43 @@ __global__ void __launch_bounds__(256) sample_coarse_vec4_kernel(const float* __
     }
     zo[k] = zv;
   }
-  __stcs(reinterpret_cast<float4*>(z_out) + q, make_float4(zo[0], zo[1], zo[2], zo[3]));
+  if (live) __stcs(reinterpret_cast<float4*>(z_out) + q, make_float4(zo[0], zo[1], zo[2], zo[3]));
   if (pts) {
     float p[12];
 #pragma unroll
     for (int k = 0; k < 4; ++k)
 #pragma unroll
       for (int c = 0; c < 3; ++c) p[k * 3 + c] = __fadd_rn(ray[c], __fmul_rn(ray[3 + c], zo[k]));
-    float4* pp = reinterpret_cast<float4*>(pts) + q * 3;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) __stcs(pp + k, make_float4(p[4 * k], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3]));
+    const IDX warp_q0 = q_raw - (threadIdx.x & 31);
+    const int valid = warp_q0 < total ? (int)min((IDX)32, total - warp_q0) : 0;
+    store_points_warp(pts, (int64_t)warp_q0, valid, p, stage[threadIdx.x >> 5]);
   }
 }
 
+template <typename IDX>
 __global__ void __launch_bounds__(256) ray_points_fwd_vec4_kernel(const float* __restrict__ ro,
                                                                   const float* __restrict__ rd,
                                                                   const float* __restrict__ z, int64_t n, int S,
                                                                   float* __restrict__ pts) {
-  const int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ float4 stage[8][96];
   const int qpr = S >> 2;
-  if (q >= n * qpr) return;
-  const int64_t r = q / qpr;
+  const IDX total = (IDX)(n * qpr);
+  const IDX q_raw = (IDX)blockIdx.x * blockDim.x + threadIdx.x;
+  const IDX q = q_raw < total ? q_raw : total - 1;
+  const IDX r = q / (IDX)qpr;
   const float4 zz = __ldcs(reinterpret_cast<const float4*>(z) + q);
-  const float o[3] = {ro[r * 3], ro[r * 3 + 1], ro[r * 3 + 2]}, d[3] = {rd[r * 3], rd[r * 3 + 1], rd[r * 3 + 2]};
+  const float* op = ro + (int64_t)r * 3;
+  const float* dp = rd + (int64_t)r * 3;
+  const float o[3] = {op[0], op[1], op[2]}, d[3] = {dp[0], dp[1], dp[2]};
   const float zv[4] = {zz.x, zz.y, zz.z, zz.w};
   float p[12];
 #pragma unroll
   for (int k = 0; k < 4; ++k)
 #pragma unroll
     for (int c = 0; c < 3; ++c) p[k * 3 + c] = __fadd_rn(o[c], __fmul_rn(d[c], zv[k]));
-  float4* pp = reinterpret_cast<float4*>(pts) + q * 3;
-#pragma unroll
-  for (int k = 0; k < 3; ++k) pp[k] = make_float4(p[4 * k], p[4 * k + 1], p[4 * k + 2], p[4 * k + 3]);
+  const IDX warp_q0 = q_raw - (threadIdx.x & 31);
+  const int valid = warp_q0 < total ? (int)min((IDX)32, total - warp_q0) : 0;
+  store_points_warp(pts, (int64_t)warp_q0, valid, p, stage[threadIdx.x >> 5]);
 }
 
 __global__ void __launch_bounds__(256) ray_points_fwd_kernel(const float* __restrict__ ro,
@@ -423,9 +449,14 @@ int nb_sample_coarse(const float* rays, int64_t n, int ld, const float* t_vals, 
   const int64_t quads = n * (S >> 2);
   if ((S & 3) == 0 && (quads + 255) / 256 < (1ll << 31) && ((uintptr_t)z & 15) == 0 && ((uintptr_t)t_rand & 15) == 0 &&
       ((uintptr_t)pts & 15) == 0)
-    sample_coarse_vec4_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, as_stream(stream)>>>(rays, n, ld, t_vals, t_rand,
-                                                                                              S, lindisp, z, pts);
-  else if (n * S < (1ll << 31))
+  {
+    if (quads < (1ll << 32) - 256)
+      sample_coarse_vec4_kernel<uint32_t><<<(unsigned)((quads + 255) / 256), 256, 0, as_stream(stream)>>>(
+          rays, n, ld, t_vals, t_rand, S, lindisp, z, pts);
+    else
+      sample_coarse_vec4_kernel<int64_t><<<(unsigned)((quads + 255) / 256), 256, 0, as_stream(stream)>>>(
+          rays, n, ld, t_vals, t_rand, S, lindisp, z, pts);
+  } else if (n * S < (1ll << 31))
     sample_coarse_kernel<uint32_t><<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays, n, ld, t_vals, t_rand, S,
                                                                                         lindisp, z, pts);
   else
@@ -440,8 +471,12 @@ int nb_ray_points_fwd(const float* rays_o, const float* rays_d, const float* z, 
   NB_REQUIRE(rays_o && rays_d && z && pts && S >= 1, "nb_ray_points_fwd: bad arguments");
   const int64_t quads = n * (S >> 2);
   if ((S & 3) == 0 && (quads + 255) / 256 < (1ll << 31) && ((uintptr_t)z & 15) == 0 && ((uintptr_t)pts & 15) == 0)
-    ray_points_fwd_vec4_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, z, n, S, pts);
-  else
+  {
+    if (quads < (1ll << 32) - 256)
+      ray_points_fwd_vec4_kernel<uint32_t><<<(unsigned)((quads + 255) / 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, z, n, S, pts);
+    else
+      ray_points_fwd_vec4_kernel<int64_t><<<(unsigned)((quads + 255) / 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, z, n, S, pts);
+  } else
     ray_points_fwd_kernel<<<grid_for(n * S, 256), 256, 0, as_stream(stream)>>>(rays_o, rays_d, z, n, S, pts);
   return check_launch("nb_ray_points_fwd");
 }
