@@ -287,6 +287,23 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_fast_kernel(const float*
   }
 }
 
+// one step of the branch-free upper-bound search: addr += 4*STEP if cdf[(addr - base)/4 + STEP - 1] <= u
+// (LDS [reg + imm], FSETP, predicated IADD: three instructions)
+template <int STEP>
+__device__ __forceinline__ void search_step(uint32_t& addr, float u) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      ".reg .f32 c;\n"
+      "ld.shared.f32 c, [%0 + %2];\n"
+      "setp.le.f32 p, c, %1;\n"
+      "@p add.u32 %0, %0, %3;\n"
+      "}\n"
+      : "+r"(addr)
+      : "f"(u), "n"((STEP - 1) * 4), "n"(STEP * 4)
+      : "memory");
+}
+
 // ---- sorted-u path (no per-sample output requested) ---------------------------------------------------------
 // The inverse cdf is monotone in u, so sorting u first (registers, blocked bitonic network: lane l owns the
 // SPT consecutive slots l*SPT..l*SPT+SPT-1, 13 of the 28 stages for I = 128 never leave the lane) yields the
@@ -303,12 +320,15 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const floa
                                                                       const float* __restrict__ u_det, int64_t n, int S,
                                                                       float* __restrict__ z_out, float* __restrict__ z_std) {
   constexpr int I = 32 * SPT;
-  constexpr int kQ = 0, kCdf = 64, kBins = 128, kZc = 192, kHist = 264, kOut = 336, kPerWarp = kOut + 64 + I;
+  // + 4: the row stride is 20 (mod 32) banks, so the eight lanes of the block-wide cumsum below read / write their
+  // rows' float4 without bank conflicts
+  constexpr int kQ = 0, kCdf = 64, kBins = 128, kZc = 192, kHist = 264, kOut = 336, kPerWarp = kOut + 64 + I + 4;
   __shared__ __align__(16) float smem[8][kPerWarp];
   const int lane = threadIdx.x & 31;
   const int wib = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
-  const int64_t r = (int64_t)blockIdx.x * 8 + wib;
-  if (r >= n) return;
+  const int64_t r_raw = (int64_t)blockIdx.x * 8 + wib;
+  const bool live = r_raw < n;                 // no early exit: the block meets at two barriers
+  const int64_t r = live ? r_raw : n - 1;
   float* qv = smem[wib] + kQ;
   float* cdf = smem[wib] + kCdf;
   float* bins = smem[wib] + kBins;
@@ -341,40 +361,67 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const floa
   hist[lane] = 0;
   hist[lane + 32] = 0;
   if (lane < 8) hist[64 + lane] = 0;
-  __syncwarp();
-  if (lane == 0) {  // cdf[m] = sum_{i<m} q[i], the sequential fp32 sum of torch.cumsum
+  __syncthreads();
+  // cdf[m] = sum_{i<m} q[i], the sequential fp32 sum of torch.cumsum: 62 dependent additions per ray.  One lane per
+  // ray of the block (eight lanes of warp 0) instead of lane 0 of every warp: a divergent lane costs its warp the
+  // same issue slots as 32 lanes, so this is 1/8 of the instructions; the other warps sort meanwhile.
+  if (wib == 0 && lane < 8) {
+    const float* qrow = smem[lane] + kQ;
+    float* crow = smem[lane] + kCdf;
     float c = 0.f;
 #pragma unroll
     for (int g = 0; g < 16; ++g) {
-      const float4 q = reinterpret_cast<const float4*>(qv)[g];
+      const float4 q = reinterpret_cast<const float4*>(qrow)[g];
       float4 o;
       o.x = c; c = __fadd_rn(c, q.x);
       o.y = c; c = __fadd_rn(c, q.y);
       o.z = c; c = __fadd_rn(c, q.z);
       o.w = c; c = __fadd_rn(c, q.w);
-      reinterpret_cast<float4*>(cdf)[g] = o;
+      reinterpret_cast<float4*>(crow)[g] = o;
     }
   }
   if (lane < B) bins[lane] = __fmul_rn(0.5f, __fadd_rn(zc[lane + 1], z0));
   if (lane + 32 < B) bins[lane + 32] = __fmul_rn(0.5f, __fadd_rn(zc[lane + 33], z1));
   if (u) {  // random draws: ascending sort, slot e = lane * SPT + k
+    // Bitonic network in its "mirror" form: the first step of every merge stage pairs slot i with slot i ^ (kk - 1),
+    // all later steps pair i with i ^ j, and every compare-exchange is ascending -- the steps that stay inside a
+    // lane are two FMNMX with no direction select; only the cross-lane steps depend on the lane (keep min or max).
 #pragma unroll
     for (int kk = 2; kk <= I; kk <<= 1) {
+      // mirror step
+      if (kk <= SPT) {
 #pragma unroll
-      for (int j = kk >> 1; j > 0; j >>= 1) {
+        for (int k = 0; k < SPT; ++k) {
+          const int k2 = k ^ (kk - 1);
+          if (k < k2) {
+            const float lo = fminf(uu[k], uu[k2]), hi = fmaxf(uu[k], uu[k2]);
+            uu[k] = lo;
+            uu[k2] = hi;
+          }
+        }
+      } else {
+        const int dl = kk / SPT - 1;                 // partner lane = lane ^ dl, partner slot = SPT - 1 - k
+        const bool keep_min = (lane & (kk / SPT / 2)) == 0;
+        float o[SPT];
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) o[k] = __shfl_xor_sync(0xffffffffu, uu[SPT - 1 - k], dl);
+#pragma unroll
+        for (int k = 0; k < SPT; ++k) uu[k] = keep_min ? fminf(uu[k], o[k]) : fmaxf(uu[k], o[k]);
+      }
+#pragma unroll
+      for (int j = kk >> 2; j > 0; j >>= 1) {
         if (j < SPT) {
 #pragma unroll
           for (int k = 0; k < SPT; ++k) {
             if ((k & j) == 0) {
-              const bool up_ = (((lane * SPT + k) & kk) == 0);
               const float lo = fminf(uu[k], uu[k | j]), hi = fmaxf(uu[k], uu[k | j]);
-              uu[k] = up_ ? lo : hi;
-              uu[k | j] = up_ ? hi : lo;
+              uu[k] = lo;
+              uu[k | j] = hi;
             }
           }
         } else {
           const int dl = j / SPT;
-          const bool keep_min = (((lane & dl) == 0) == (((lane * SPT) & kk) == 0));
+          const bool keep_min = (lane & dl) == 0;
 #pragma unroll
           for (int k = 0; k < SPT; ++k) {
             const float o = __shfl_xor_sync(0xffffffffu, uu[k], dl);
@@ -384,17 +431,24 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const floa
       }
     }
   }
-  __syncwarp();
+  __syncthreads();                                // the cdf rows written by warp 0 are visible
   if (lane >= B) cdf[lane] = CUDART_INF_F;        // entries past the cdf: every search stops before them
   if (lane + 32 >= B) cdf[lane + 32] = CUDART_INF_F;
   __syncwarp();
   int pos[SPT];
+  {  // searchsorted(right=True): six fixed steps on a shared-memory byte address
+    const uint32_t cdf_s = (uint32_t)__cvta_generic_to_shared(cdf);
 #pragma unroll
-  for (int k = 0; k < SPT; ++k) pos[k] = 0;
-#pragma unroll
-  for (int step = 32; step > 0; step >>= 1) {
-#pragma unroll
-    for (int k = 0; k < SPT; ++k) pos[k] += (cdf[pos[k] + step - 1] <= uu[k]) ? step : 0;   // searchsorted(right=True)
+    for (int k = 0; k < SPT; ++k) {
+      uint32_t a = cdf_s;
+      search_step<32>(a, uu[k]);
+      search_step<16>(a, uu[k]);
+      search_step<8>(a, uu[k]);
+      search_step<4>(a, uu[k]);
+      search_step<2>(a, uu[k]);
+      search_step<1>(a, uu[k]);
+      pos[k] = (int)((a - cdf_s) >> 2);
+    }
   }
   float smp[SPT], sum = 0.f;
 #pragma unroll
@@ -424,7 +478,7 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const floa
       var += d * d;
     }
     var = warp_sum(var) / (float)I;
-    if (lane == 0) z_std[r] = sqrtf(var);
+    if (lane == 0 && live) z_std[r] = sqrtf(var);
   }
   __syncwarp();
   {  // coarse c = 2*lane, 2*lane+1 -> c + #{e : a_e <= c}
@@ -442,8 +496,16 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const floa
     if (2 * lane + 1 < S) outb[2 * lane + 1 + b1] = zz.y;
   }
   __syncwarp();
+  if (!live) return;
   float* zo = z_out + r * (int64_t)(S + I);
-  for (int i = lane; i < S + I; i += 32) __stcs(zo + i, outb[i]);
+  if (S == 64 && ((uintptr_t)z_out & 15) == 0) {  // 16-byte stores ((64 + I) * 4 bytes per ray keeps the rows aligned)
+    const float4* ob = reinterpret_cast<const float4*>(outb);
+#pragma unroll
+    for (int i = 0; i < (64 + I) / 4; i += 32)
+      if (i + lane < (64 + I) / 4) __stcs(reinterpret_cast<float4*>(zo) + i + lane, ob[i + lane]);
+  } else {
+    for (int i = lane; i < S + I; i += 32) __stcs(zo + i, outb[i]);
+  }
 }
 
 }  // namespace nb
