@@ -14,6 +14,7 @@
 //   3. small grads  (mlp_small_grads_kernel): biases (column sums of dA) and the two CUDA-core
 //      heads (alpha_linear, rgb_linear).
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "mlp_common.cuh"
@@ -893,6 +894,10 @@ int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* act
     // at least ~4 tiles of the average job per CTA, else fewer CTAs (the flush is a fixed cost per range)
     int64_t grid = split.cum[kNumWJobs] * tiles / (4 * (split.cum[kNumWJobs] / kNumWJobs));
     if (grid > kNumSMs) grid = kNumSMs;
+    if (const char* e = getenv("NB_WGRAD_GRID")) {   // experiment knob (tools/wgrad_sm_sweep.sh): fewer CTAs
+      const int64_t lim = atoi(e);
+      if (lim > 0 && lim < grid) grid = lim;
+    }
     if (grid < 1) grid = 1;
     mlp_wgrad_kernel<<<(int)grid, 384, kWSmemBytes, st>>>(jobs, split, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles,
                                                           grads);
