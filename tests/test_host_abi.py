@@ -105,3 +105,34 @@ def test_mlp_method_matches_oracle(golden):
     with torch.no_grad():
         out = m.MLP(x).reshape(6, 16, 4)
     assert (out - torch.from_numpy(golden["mlp/raw_seed11"])).abs().max() < 2e-6
+
+
+def test_synthetic_scenes_have_the_survey_shapes():
+    """Blender-shaped (400x400, focal from camera_angle_x) and LLFF-shaped (504x378, fern focal)
+    synthetic scenes used by bench.py; poses are rigid transforms."""
+    import numpy as np
+    from nerf_shared_b200 import datasets
+    images, poses, hwf, K = datasets.synthetic_blender(40, 40, 3)
+    assert images.shape == (3, 40, 40, 3) and poses.shape == (3, 4, 4) and abs(hwf[2] - 0.5 * 40 / np.tan(0.5 * 0.6911112070083618)) < 1e-9
+    images, poses, hwf, K = datasets.synthetic_llff(378, 504, 2)
+    assert images.shape == (2, 378, 504, 3) and poses.shape == (2, 4, 4)
+    assert abs(K[0][0] - 3260.5 / 8) < 1e-9 and K[0][2] == 252 and K[1][2] == 189
+    for p in poses:
+        R = p[:3, :3].astype(np.float64)
+        np.testing.assert_allclose(R @ R.T, np.eye(3), atol=1e-6)
+        assert abs(np.linalg.det(R) - 1.0) < 1e-6 and np.all(np.abs(p[:3, 3]) < 0.5)
+
+
+def test_graphed_step_refuses_cpu():
+    """train.GraphedTrainStep is part of the product path: no CPU fallback (it needs the FlatAdam buffers on a GPU)."""
+    import pytest
+    import torch
+    from nerf_shared_b200 import train
+    assert hasattr(train.GraphedTrainStep, "_step_overlap")
+    if not torch.cuda.is_available():
+        class _Opt:
+            flat_p = torch.zeros(1)
+        class _R:
+            N_importance = 128
+        with pytest.raises(Exception):
+            train.GraphedTrainStep(_R(), None, object(), _Opt(), 8, 8, None, 16)   # torch.cuda.Stream on a CPU-only host
