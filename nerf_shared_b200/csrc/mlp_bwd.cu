@@ -11,8 +11,10 @@
 //      saved slabs (a [128 samples x 64 features] swizzled slab is a valid MN-major operand),
 //      fp32 accumulation in TMEM (up to all 512 columns), partial results reduced into the
 //      fp32 gradient buffer with vector atomics.
-//   3. small grads  (mlp_small_grads_kernel): biases (column sums of dA) and the two CUDA-core
-//      heads (alpha_linear, rgb_linear).
+//      The layer biases (column sums of dA) are taken from the operand stages while they sit in
+//      shared memory.
+//   3. small grads  (mlp_small_grads_kernel): the two CUDA-core heads (alpha_linear, rgb_linear)
+//      and their biases; one CTA per SM, whole tiles of h7 / hv / d_raw staged by bulk copies.
 #include <cuda_bf16.h>
 #include <stdlib.h>
 
