@@ -235,6 +235,40 @@ def test_graphed_train_step_matches_eager(golden, overlap):
     assert maxabs(rgb_a, rgb_b) <= 2e-2
 
 
+def test_two_branch_graph_draws_the_same_random_numbers(golden):
+    """perturb = 1 and raw_noise_std > 0: the two-branch graph (coarse pass and its backward on a second stream) and the
+    single-stream graph draw t_rand, coarse noise, u, fine noise in the same order from the same generator state, so
+    their losses agree step by step (gradient atomics order is the only difference)."""
+    from nerf_shared_b200 import render_utils, train, utils
+    H = W = 8
+    K = O.blender_intrinsics(H, W)
+    rb = cuda(golden["rr/ray_batch"])
+    rays = torch.stack([rb[:, 0:3], rb[:, 3:6]], 0).contiguous()
+    g = torch.Generator().manual_seed(5)
+    targets = [torch.rand(rays.shape[1], 3, generator=g).cuda() for _ in range(4)]
+    losses = {}
+    for overlap in (False, True):
+        class A:
+            lrate = 5e-4
+        mc, mf = make_model(11), make_model(12)
+        r = render_utils.Renderer(perturb=1.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                                  raw_noise_std=0.5, near=2.0, far=6.0)
+        r.train()
+        opt = utils.get_optimizer(mc, mf, A())
+        torch.manual_seed(77)
+        torch.cuda.manual_seed(77)
+        step = train.GraphedTrainStep(r, mc, mf, opt, H, W, K, rays.shape[1], overlap=overlap)
+        out = []
+        for tgt in targets:
+            torch.cuda.manual_seed(1234)          # every replay starts from the same generator state in both runs
+            loss, _ = step(rays, tgt)
+            out.append(float(loss))
+        losses[overlap] = out
+    for a, b in zip(losses[False], losses[True]):
+        assert abs(a - b) <= 2e-4 * abs(a), losses
+    assert len(set(losses[True])) > 1
+
+
 def test_sample_random_ray_batch_rays_and_targets():
     """utils.sample_random_ray_batch (utils.py:394-442, no_batching branch): distinct pixels, rays equal
     to get_rays() at those pixels bit for bit, targets equal to the image at those pixels."""
