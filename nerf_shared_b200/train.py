@@ -43,6 +43,15 @@ class GraphedTrainStep:
         self.overlap = bool(overlap) and fine_model is not None and renderer.N_importance > 0 \
             and n_rays <= render_utils.MIN_CHUNK
         self._coarse_stream = torch.cuda.Stream(device=dev) if self.overlap else None
+        # multi-GPU: the coarse model's gradients are complete when the side branch ends, long before the fine wgrad;
+        # their half of the flat buffer is all-reduced on the side stream under the fine backward (NB_SPLIT_AR=0: one
+        # all-reduce after the join).  Needs the [coarse | fine] layout utils.get_optimizer builds.
+        self._n_coarse = 0
+        if self.overlap and self.world > 1 and os.environ.get("NB_SPLIT_AR", "1") != "0":
+            n_c = sum(p.numel() for p in coarse_model.parameters())
+            first_fine = next(iter(fine_model.parameters()))
+            if optimizer.grad_offset(first_fine) == n_c and 0 < n_c < optimizer.flat_g.numel():
+                self._n_coarse = n_c
         self.loss = self.psnr = None
         self.launches_per_replay = 0
 
@@ -93,6 +102,8 @@ class GraphedTrainStep:
         torch.cuda.set_stream(side)
         try:
             box["m0"].backward()
+            if self._n_coarse:                # coarse gradients are final here: reduce them under the fine backward
+                torch.distributed.all_reduce(opt.flat_g[:self._n_coarse], group=self.group)
         finally:
             torch.cuda.set_stream(main)
         m.backward()
@@ -100,7 +111,7 @@ class GraphedTrainStep:
         loss = m.detach() + box["m0"].detach()     # main.py:99
         alive.clear()                         # only now may the coarse pass's tensors go back to the allocator
         if self.world > 1:
-            torch.distributed.all_reduce(opt.flat_g, group=self.group)
+            torch.distributed.all_reduce(opt.flat_g[self._n_coarse:], group=self.group)
         opt.step()
         return loss, psnr
 

@@ -73,6 +73,28 @@ rel = float((g_n - g_1).norm() / g_1.norm())
 dp = float((p_n - p_1).abs().max())
 say("sharded gradient vs large-batch gradient: rel %.3g ; params after Adam max|d| %.3g" % (rel, dp))
 ok &= rel < 1e-3 and dp < 1.1e-3      # fp32 atomics order; Adam's first step moves every weight by ~lr
+
+# ---- (c) the graphed step (two-branch graph, coarse half of the gradients all-reduced under the fine backward):
+#          == the eager sharded step above, and bit-identical parameters on every rank
+from nerf_shared_b200 import train
+c, f = make_model(11).to(dev), make_model(12).to(dev)
+opt = utils.get_optimizer(c, f, A())
+opt.grad_scale = 1.0 / world
+rr = render_utils.Renderer(perturb=0.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                           raw_noise_std=0.0, near=2.0, far=6.0)
+step = train.GraphedTrainStep(rr, c, f, opt, H, W, K, bs.shape[1])
+step(bs, ts)
+torch.cuda.synchronize()
+dg = float((opt.flat_p - p_n).abs().max())
+lo, hi = opt.flat_p.clone(), opt.flat_p.clone()
+dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+same_p = bool(torch.equal(lo, hi))
+say("graphed step (split all-reduce: %s) vs eager sharded step: params max|d| %.3g ; identical on all ranks: %s"
+    % (bool(step._n_coarse), dg, same_p))
+ok &= dg < 1.1e-3 and same_p and (world == 1 or step._n_coarse > 0)
+step.graph = None
+del step
 t = torch.tensor([1.0 if ok else 0.0], device=dev)
 dist.all_reduce(t, op=dist.ReduceOp.MIN)
 say("DIST_CHECK", "OK" if t.item() == 1.0 else "FAILED")
