@@ -218,11 +218,26 @@ def run_b200(a):
         tgt = torch.from_numpy(images[i % N_IMAGES].reshape(-1, 3)[pix.cpu().numpy()]).to(dev)
         pool.append((torch.stack([ro, rd], 0), tgt))
 
+    # The clock sampler (rank 0 only) starts BEFORE the warm-up: nvidia-smi's start-up (NVML initialisation) stalls
+    # kernel submission for tens of milliseconds -- inside the timed region it doubled the step time of an 8-GPU run --
+    # so the warm-up keeps stepping (untimed) until the first sample has arrived; after that it is one light query
+    # every 100 ms.
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     for i in range(max(a.warmup, 3)):
         step(*pool[i % n_pool])
+    t_wait = time.perf_counter()
+    ready = torch.zeros(1, device=dev)
+    while True:                               # all ranks leave together (the steps contain a collective)
+        ready.fill_(1.0 if (rank != 0 or sampler.proc is None or sampler.lines or time.perf_counter() - t_wait > 3.0) else 0.0)
+        if world > 1:
+            dist.all_reduce(ready, op=dist.ReduceOp.MIN)
+        if float(ready.item()) == 1.0:
+            break
+        for i in range(20):
+            step(*pool[i % n_pool])
     sync_all()
-    sampler = ClockSampler(local)
-    sampler.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     sync_all()
     for i in range(a.steps):
