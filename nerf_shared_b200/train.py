@@ -147,6 +147,10 @@ class GraphedTrainStep:
             opt.in_graph = False
 
     def __call__(self, batch_rays, target):
+        shp = tuple(torch.as_tensor(batch_rays).shape) if not torch.is_tensor(batch_rays) else tuple(batch_rays.shape)
+        if shp != tuple(self.rays.shape) or tuple(target.shape) != tuple(self.target.shape):
+            raise ValueError("GraphedTrainStep was built for rays %s / targets %s (n_rays is fixed by the captured graph); "
+                             "got %s / %s" % (tuple(self.rays.shape), tuple(self.target.shape), shp, tuple(target.shape)))
         if self.graph is None:
             self.rays.copy_(torch.as_tensor(batch_rays), non_blocking=True)
             self.target.copy_(target, non_blocking=True)
