@@ -205,6 +205,12 @@ NB_API int nb_adam_step(float* p, const float* g, float* m, float* v, int64_t n,
  * replaces: Adam.step + the per-iteration lr write main.py:104-112. */
 NB_API int nb_adam_hyper(float* hyper, float lr, float beta1, float beta2, float eps, int step, float grad_scale,
                          void* stream);
+/* nb_adam_hyper plus the copy of a training step's two inputs (n1 floats src1 -> dst1: the ray batch; n2 floats
+ * src2 -> dst2: the target colours) into the static buffers a captured step graph reads, in ONE launch
+ * (train.GraphedTrainStep issues it in front of every replay). */
+NB_API int nb_train_step_prologue(float* hyper, float lr, float beta1, float beta2, float eps, int step, float grad_scale,
+                                  const float* src1, float* dst1, int64_t n1, const float* src2, float* dst2, int64_t n2,
+                                  void* stream);
 NB_API int nb_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, const float* hyper, void* stream);
 
 /* ---- self test ------------------------------------------------------------------------- */

@@ -74,6 +74,7 @@ SIGNATURES = {
     "nb_debug_umma_mn": (i32, [vp, vp, i32, vp, vp]),
     "nb_adam_step": (i32, [vp, vp, vp, vp, i64, f32, f32, f32, f32, i32, f32, vp]),
     "nb_adam_hyper": (i32, [vp, f32, f32, f32, f32, i32, f32, vp]),
+    "nb_train_step_prologue": (i32, [vp, f32, f32, f32, f32, i32, f32, vp, vp, i64, vp, vp, i64, vp]),
     "nb_adam_step_dev": (i32, [vp, vp, vp, vp, i64, vp, vp]),
     "nb_debug_umma": (i32, [vp, vp, i32, vp, vp]),
     "nb_debug_umma_rate": (i32, [i32, i32, i32, vp, vp]),

@@ -97,6 +97,18 @@ class FlatAdam(torch.optim.Optimizer):
             check(lib.nb_adam_hyper(ptr(self._hyper), float(g0["lr"]), float(b1), float(b2), float(g0["eps"]),
                                     int(self._step), float(self.grad_scale), stream_ptr()), "nb_adam_hyper")
 
+    def push_hyper_and_inputs(self, src1, dst1, src2, dst2):
+        """push_hyper() and the copies src1 -> dst1, src2 -> dst2 (contiguous fp32 CUDA tensors of equal sizes) as one
+        launch: what train.GraphedTrainStep does in front of every replay."""
+        g0 = self._lr()
+        self._step += 1
+        b1, b2 = g0["betas"]
+        lib = _lib.load()
+        with torch.cuda.device(self.flat_p.device):
+            check(lib.nb_train_step_prologue(ptr(self._hyper), float(g0["lr"]), float(b1), float(b2), float(g0["eps"]),
+                                             int(self._step), float(self.grad_scale), ptr(src1), ptr(dst1), src1.numel(),
+                                             ptr(src2), ptr(dst2), src2.numel(), stream_ptr()), "nb_train_step_prologue")
+
     def bump_versions(self):
         """The kernels write parameters through raw pointers: bump the autograd version counters (no
         launch) so caches keyed on p._version (_ops.packed_weights) see the update."""

@@ -155,9 +155,15 @@ class GraphedTrainStep:
             self.rays.copy_(torch.as_tensor(batch_rays), non_blocking=True)
             self.target.copy_(target, non_blocking=True)
             self._capture()
-        self.rays.copy_(torch.as_tensor(batch_rays) if not torch.is_tensor(batch_rays) else batch_rays, non_blocking=True)
-        self.target.copy_(target, non_blocking=True)
-        self.opt.push_hyper()
+        dev = self.rays.device
+        if (torch.is_tensor(batch_rays) and batch_rays.device == dev and batch_rays.dtype == torch.float32
+                and batch_rays.is_contiguous() and target.device == dev and target.dtype == torch.float32
+                and target.is_contiguous()):
+            self.opt.push_hyper_and_inputs(batch_rays, self.rays, target, self.target)   # one launch
+        else:
+            self.rays.copy_(torch.as_tensor(batch_rays) if not torch.is_tensor(batch_rays) else batch_rays, non_blocking=True)
+            self.target.copy_(target, non_blocking=True)
+            self.opt.push_hyper()
         self.graph.replay()
         self.opt.bump_versions()
         return self.loss, self.psnr
