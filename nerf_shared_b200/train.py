@@ -108,11 +108,11 @@ class GraphedTrainStep:
             torch.cuda.set_stream(main)
         m.backward()
         main.wait_stream(side)                # join
-        loss = m.detach() + box["m0"].detach()     # main.py:99
         alive.clear()                         # only now may the coarse pass's tensors go back to the allocator
         if self.world > 1:
             torch.distributed.all_reduce(opt.flat_g[self._n_coarse:], group=self.group)
         opt.step()
+        loss = m.detach() + box["m0"].detach()     # main.py:99 (after the update: nothing waits for the sum)
         return loss, psnr
 
     def _capture(self):
