@@ -153,6 +153,11 @@ typedef struct NbMlpWeights {
  * replaces: NeRF.forward nerf.py:96-134. */
 NB_API int nb_mlp_fwd_f32(const NbMlpWeights* w, const float* pts, const float* viewdirs, int64_t M, int S, float* raw,
                    void* stream);
+/* The use_viewdirs=False model (nerf.py:93-94, 131-132): the same trunk, then raw = output_linear(h).
+ * Only pts_w / pts_b / L_pts of `w` are read; out_w [out_ch,256], out_b [out_ch]; raw: [M,out_ch].
+ * fp32, forward only (no shipped config trains this model). */
+NB_API int nb_mlp_fwd_f32_noview(const NbMlpWeights* w, const float* out_w, const float* out_b, int out_ch,
+                                 const float* pts, int64_t M, float* raw, void* stream);
 
 /* Size in bytes of the packed bf16 operand blob + fp32 side table used by the tensor-core
  * kernels for one model. */

@@ -361,6 +361,28 @@ def mlp_forward_f32(model, pts, viewdirs, S):
     return raw
 
 
+def mlp_forward_f32_noview(model, pts):
+    """use_viewdirs=False model (nerf.py:93-94,131-132): pts [M,3] -> raw [M,output_ch]; fp32, forward only."""
+    lib = _lib_for(pts)
+    p = f32c(pts.detach()).view(-1, 3)
+    M = p.shape[0]
+    pl = list(model.pts_linears)
+    ps = [l.weight for l in pl] + [l.bias for l in pl] + [model.output_linear.weight, model.output_linear.bias]
+    for t in ps:
+        if t.dtype != torch.float32 or not t.is_contiguous() or t.device != p.device:
+            raise _lib.NerfB200Error("NeRF parameters must be contiguous fp32 tensors on the device of the points")
+    w = _lib.NbMlpWeights()
+    for i in range(8):
+        w.pts_w[i], w.pts_b[i] = ps[i].data_ptr(), ps[8 + i].data_ptr()
+    w.L_pts, w.L_dirs = int(model.multires), 0
+    out_ch = int(ps[16].shape[0])
+    raw = torch.empty((M, out_ch), device=p.device, dtype=torch.float32)
+    with torch.cuda.device(p.device):
+        check(lib.nb_mlp_fwd_f32_noview(C.byref(w), ptr(ps[16]), ptr(ps[17]), out_ch, ptr(p), M, ptr(raw), stream_ptr()),
+              "nb_mlp_fwd_f32_noview")
+    return raw
+
+
 def mlp_forward_tc(model, pts, viewdirs, S, save_acts=False):
     lib = _lib_for(pts)
     p, v = f32c(pts).view(-1, 3), f32c(viewdirs).view(-1, 3)

@@ -6,6 +6,8 @@
 // on-device numerical reference for the tcgen05 kernel (mlp_tc.cu) at sizes the CPU oracle
 // cannot reach, and serves the one shipped config whose encoding widths (multires 15/6,
 // configs/stonehenge.txt) the tensor-core kernel does not tile.  Not the fast path.
+// The same kernel evaluates the use_viewdirs=False model (nerf.py:93-94,131-132: trunk ->
+// output_linear), which no shipped config trains; forward only.
 #include "common.cuh"
 
 namespace nb {
@@ -57,7 +59,8 @@ __device__ __forceinline__ void dense(const float* __restrict__ W, const float* 
 
 __global__ void __launch_bounds__(256, 1) mlp_fwd_f32_kernel(NbMlpWeights w, const float* __restrict__ pts,
                                                              const float* __restrict__ viewdirs, int64_t M, int S,
-                                                             float* __restrict__ raw) {
+                                                             float* __restrict__ raw, const float* __restrict__ out_w,
+                                                             const float* __restrict__ out_b, int out_ch) {
   extern __shared__ __align__(16) float sm[];
   float* enc = sm;                       // [kTS][kEncLd]
   float* dirs = enc + kTS * kEncLd;      // [kTS][kDirLd]
@@ -75,7 +78,7 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_f32_kernel(NbMlpWeights w, con
       float x = 0.f, v = 0.f;
       if (m < M) {
         x = pts[m * 3 + c];
-        v = viewdirs[(m / S) * 3 + c];
+        if (viewdirs != nullptr) v = viewdirs[(m / S) * 3 + c];
       }
       float* e = enc + s * kEncLd;
       e[c] = x;
@@ -103,6 +106,17 @@ __global__ void __launch_bounds__(256, 1) mlp_fwd_f32_kernel(NbMlpWeights w, con
     dense(w.pts_w[5], w.pts_b[5], kW, enc, kEncLd, in_ch, hA, kW, kW, hB, true);  // skip: cat[input_pts, h]
     dense(w.pts_w[6], w.pts_b[6], kW, hB, kW, kW, nullptr, 0, 0, hA, true);
     dense(w.pts_w[7], w.pts_b[7], kW, hA, kW, kW, nullptr, 0, 0, hB, true);
+    if (out_w != nullptr) {   // use_viewdirs=False: raw = output_linear(h) (nerf.py:131-132); thread -> (sample, channel)
+      int s = threadIdx.x >> 2;
+      int64_t m = m0 + s;
+      for (int o = threadIdx.x & 3; o < out_ch; o += 4) {
+        float a = __ldg(out_b + o);
+        for (int k = 0; k < kW; ++k) a = fmaf(hB[s * kW + k], __ldg(out_w + o * kW + k), a);
+        if (m < M) raw[m * out_ch + o] = a;
+      }
+      __syncthreads();
+      continue;
+    }
     // sigma head (nerf.py:121): 4 threads per sample
     {
       int s = threadIdx.x >> 2, part = threadIdx.x & 3;
@@ -157,6 +171,22 @@ extern "C" int nb_mlp_fwd_f32(const NbMlpWeights* w, const float* pts, const flo
   }
   int64_t ntiles = (M + kTS - 1) / kTS;
   int grid = (int)(ntiles < (int64_t)kNumSMs ? ntiles : (int64_t)kNumSMs);
-  mlp_fwd_f32_kernel<<<grid, 256, kSimtSmem, as_stream(stream)>>>(*w, pts, viewdirs, M, S, raw);
+  mlp_fwd_f32_kernel<<<grid, 256, kSimtSmem, as_stream(stream)>>>(*w, pts, viewdirs, M, S, raw, nullptr, nullptr, 0);
   return check_launch("nb_mlp_fwd_f32");
+}
+
+extern "C" int nb_mlp_fwd_f32_noview(const NbMlpWeights* w, const float* out_w, const float* out_b, int out_ch,
+                                     const float* pts, int64_t M, float* raw, void* stream) {
+  if (M == 0) return 0;
+  NB_REQUIRE(w && out_w && out_b && pts && raw, "nb_mlp_fwd_f32_noview: bad arguments");
+  if (w->L_pts < 0 || w->L_pts > 15 || out_ch < 1 || out_ch > 64) {
+    set_error("nb_mlp_fwd_f32_noview: encoding octaves %d outside [0,15] or output_ch %d outside [1,64]", w->L_pts, out_ch);
+    return NB_E_UNSUPPORTED;
+  }
+  NbMlpWeights t = *w;
+  t.L_dirs = 0;
+  int64_t ntiles = (M + kTS - 1) / kTS;
+  int grid = (int)(ntiles < (int64_t)kNumSMs ? ntiles : (int64_t)kNumSMs);
+  mlp_fwd_f32_kernel<<<grid, 256, kSimtSmem, as_stream(stream)>>>(t, pts, nullptr, M, 1, raw, out_w, out_b, out_ch);
+  return check_launch("nb_mlp_fwd_f32_noview");
 }

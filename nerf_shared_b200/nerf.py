@@ -86,18 +86,32 @@ class NeRF(nn.Module):
             self.output_linear = nn.Linear(W, output_ch)
 
     def _check_kernel_config(self):
-        if not (self.D == 8 and self.W == 256 and list(self.skips) == [4] and self.use_viewdirs and self.i_embed == 0):
+        if not (self.D == 8 and self.W == 256 and list(self.skips) == [4] and self.i_embed == 0):
             raise NotImplementedError(
                 "libnerf_b200 implements the network every reference config uses (D=8, W=256, skips=[4], "
-                "use_viewdirs=True, i_embed=0); got D=%s W=%s skips=%s use_viewdirs=%s i_embed=%s"
-                % (self.D, self.W, self.skips, self.use_viewdirs, self.i_embed))
+                "i_embed=0); got D=%s W=%s skips=%s i_embed=%s" % (self.D, self.W, self.skips, self.i_embed))
+
+    def _forward_noview(self, inputs):
+        """use_viewdirs=False (nerf.py:93-94,131-132): trunk -> output_linear, fp32 CUDA-core kernel.
+        Forward only: no shipped config trains this model, so there are no backward kernels for it."""
+        if torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in self.parameters())):
+            raise NotImplementedError(
+                "libnerf_b200 evaluates use_viewdirs=False models forward-only; call under torch.no_grad() "
+                "(training and pose gradients need use_viewdirs=True, as in every reference config)")
+        raw = _ops.mlp_forward_f32_noview(self, inputs.reshape(-1, 3))
+        return raw.reshape(list(inputs.shape[:-1]) + [raw.shape[-1]])
 
     def forward(self, inputs, viewdirs, netchunk=1024 * 64):
-        """inputs [N, S, 3], viewdirs [N, 3] -> [N, S, 4] (rgb pre-sigmoid, sigma pre-relu).
+        """inputs [N, S, 3], viewdirs [N, 3] -> [N, S, 4] (rgb pre-sigmoid, sigma pre-relu);
+        use_viewdirs=False models: viewdirs=None -> [N, S, output_ch].
 
         `netchunk` is accepted for signature compatibility (nerf.py:96,106) and ignored: the fused
         kernel keeps activations on-chip, so there is nothing to chunk."""
         self._check_kernel_config()
+        if not self.use_viewdirs:
+            if viewdirs is not None:   # the reference fails the same way: embeddirs_fn is None (nerf.py:100-103)
+                raise TypeError("a use_viewdirs=False model has no view-direction encoder; pass viewdirs=None")
+            return self._forward_noview(inputs)
         if viewdirs is None:
             raise NotImplementedError("use_viewdirs=True models need viewdirs")
         n_rays = viewdirs.reshape(-1, 3).shape[0]

@@ -91,15 +91,14 @@ class Renderer(torch.nn.Module):
     def render_rays(self, ray_batch, coarse_model, fine_model, retraw=False, retweights=False, verbose=False,
                     pytest=False):
         """ray_batch rows: o(3) d(3) near far [viewdirs(3)] -> dict as the reference (render_utils.py:67-174)."""
-        if ray_batch.shape[-1] <= 8:
-            raise NotImplementedError("rays without view directions (use_viewdirs=False) are not implemented")
         n = ray_batch.shape[0]
         dev = ray_batch.device
         parts = self._columns_of(ray_batch)
         if parts is not None:
             rays_o, rays_d, viewdirs = parts
-        else:
-            rays_o, rays_d, viewdirs = ray_batch[:, 0:3], ray_batch[:, 3:6], ray_batch[:, 8:11]
+        else:                                  # 8 columns: no view directions (render_utils.py:100)
+            rays_o, rays_d = ray_batch[:, 0:3], ray_batch[:, 3:6]
+            viewdirs = ray_batch[:, 8:11] if ray_batch.shape[-1] > 8 else None
         S, I = int(self.N_samples), int(self.N_importance)
 
         t_rand = self._uniform((n, S), dev, "t_rand") if self.perturb > 0.0 else None
@@ -138,12 +137,12 @@ class Renderer(torch.nn.Module):
             rays_o, rays_d = utils.get_rays(H, W, K, c2w)
         else:
             rays_o, rays_d = rays
-        if not self.use_viewdirs:
-            raise NotImplementedError("use_viewdirs=False is not implemented by libnerf_b200")
-        viewdirs = rays_d
-        if c2w_staticcam is not None:
+        viewdirs = rays_d if self.use_viewdirs else None
+        if self.use_viewdirs and c2w_staticcam is not None:      # render_utils.py:207-210
             rays_o, rays_d = utils.get_rays(H, W, K, c2w_staticcam)
         out_shape = list(rays_d.shape[:-1])
+        if viewdirs is None:
+            return self._render_no_viewdirs(H, W, K, coarse_model, fine_model, chunk, rays_o, rays_d, retraw, out_shape)
         needs_grad = torch.is_grad_enabled() and any(torch.is_tensor(t) and t.requires_grad for t in (rays_o, rays_d, viewdirs))
         if needs_grad:   # pose estimation: every step of the row construction is differentiable
             viewdirs = _ops.Normalize.apply(viewdirs).reshape(-1, 3)
@@ -175,8 +174,25 @@ class Renderer(torch.nn.Module):
         head = ("rgb_map", "disp_map", "acc_map")
         return [res[k] for k in head] + [{k: v for k, v in res.items() if k not in head}]
 
+    def _render_no_viewdirs(self, H, W, K, coarse_model, fine_model, chunk, rays_o, rays_d, retraw, out_shape):
+        """render() for use_viewdirs=False: ray rows are [N,8] = o, d, near, far (render_utils.py:219-226).
+        The models of this mode run forward-only (nerf.NeRF._forward_noview)."""
+        if self.ndc:
+            rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
+        rays_o = rays_o.reshape(-1, 3).float()
+        rays_d = rays_d.reshape(-1, 3).float()
+        bounds = rays_d.new_empty((rays_d.shape[0], 2))
+        bounds[:, 0] = float(self.near)
+        bounds[:, 1] = float(self.far)
+        res = self.render_batch(coarse_model, fine_model, torch.cat([rays_o, rays_d, bounds], -1), chunk, retraw)
+        res = {k: v.reshape(out_shape + list(v.shape[1:])) for k, v in res.items()}
+        head = ("rgb_map", "disp_map", "acc_map")
+        return [res[k] for k in head] + [{k: v for k, v in res.items() if k not in head}]
+
     def raw2outputs(self, raw, z_vals, rays_d, pytest=False, _what="noise"):
         """-> rgb_map, disp_map, acc_map, weights, depth_map (render_utils.py:241-290)."""
+        if raw.shape[-1] != 4:      # output_ch=5 of a use_viewdirs=False model: channels 0-3 are read (:260,265)
+            raw = raw[..., :4].contiguous()
         noise = None
         if self.raw_noise_std > 0.0:
             noise = self._normal(tuple(raw.shape[:-1]), raw.device, _what) * self.raw_noise_std

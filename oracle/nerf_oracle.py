@@ -180,17 +180,22 @@ PARAM_ORDER_VIEWDIRS = (
 
 
 def make_params(seed: int, D: int = 8, W: int = 256, input_ch: int = 63, input_ch_views: int = 27,
-                skips: Sequence[int] = (4,), scale: float = 1.0) -> Dict[str, Tensor]:
+                skips: Sequence[int] = (4,), scale: float = 1.0, output_ch: int = 0) -> Dict[str, Tensor]:
     """Random-init weights with nn.Linear's distribution (U(+-1/sqrt(fan_in))), drawn from a
     numpy PCG64 stream so that the same bits come out on every machine / torch version.
-    Keys are the reference state_dict keys (nerf.py:79-94)."""
+    Keys are the reference state_dict keys (nerf.py:79-94).  output_ch > 0 builds the
+    use_viewdirs=False model instead (views_linears.0 [W/2, W] and output_linear [output_ch, W],
+    nerf.py:84,93-94)."""
     rng = np.random.default_rng(seed)
     shapes = []
     for i in range(D):
         fan_in = input_ch if i == 0 else (W + input_ch if (i - 1) in skips else W)
         shapes.append(("pts_linears.%d" % i, W, fan_in))
-    shapes += [("views_linears.0", W // 2, input_ch_views + W), ("feature_linear", W, W),
-               ("alpha_linear", 1, W), ("rgb_linear", 3, W // 2)]
+    if output_ch > 0:
+        shapes += [("views_linears.0", W // 2, W), ("output_linear", output_ch, W)]
+    else:
+        shapes += [("views_linears.0", W // 2, input_ch_views + W), ("feature_linear", W, W),
+                   ("alpha_linear", 1, W), ("rgb_linear", 3, W // 2)]
     p = {}
     for name, fo, fi in shapes:
         b = 1.0 / math.sqrt(fi)
@@ -203,7 +208,7 @@ def _bf16(x: Tensor) -> Tensor:
     return x.to(torch.bfloat16).to(torch.float32)
 
 
-def mlp(params: Dict[str, Tensor], enc_pts: Tensor, enc_dirs: Tensor, D: int = 8,
+def mlp(params: Dict[str, Tensor], enc_pts: Tensor, enc_dirs: Optional[Tensor], D: int = 8,
         skips: Sequence[int] = (4,), bf16: bool = False, acts: Optional[list] = None) -> Tensor:
     """nerf.py:110-134 (use_viewdirs=True branch) -> [M,4] = (r,g,b,sigma) pre-activation.
 
@@ -228,6 +233,9 @@ def mlp(params: Dict[str, Tensor], enc_pts: Tensor, enc_dirs: Tensor, D: int = 8
         if i in skips:
             h = torch.cat([x_in, h], -1)
             h_full = torch.cat([x_in, h_full], -1)
+    if "output_linear.weight" in params:        # use_viewdirs=False (nerf.py:131-132); fp32 only
+        assert not bf16
+        return lin("output_linear", h)
     if bf16:
         alpha = F.linear(h_full, params["alpha_linear.weight"], params["alpha_linear.bias"])
     else:
@@ -245,15 +253,18 @@ def mlp(params: Dict[str, Tensor], enc_pts: Tensor, enc_dirs: Tensor, D: int = 8
 
 def nerf_query(params: Dict[str, Tensor], pts: Tensor, viewdirs: Tensor, multires: int = 10,
                multires_views: int = 4, bf16: bool = False, chunk: int = 65536) -> Tensor:
-    """nerf.py:96-108: pts [N,S,3], viewdirs [N,3] -> raw [N,S,4]."""
+    """nerf.py:96-108: pts [N,S,3], viewdirs [N,3] -> raw [N,S,4]
+    (use_viewdirs=False parameters: viewdirs is ignored, raw is [N,S,output_ch])."""
     flat = pts.reshape(-1, 3)
-    dirs = viewdirs[:, None].expand(pts.shape).reshape(-1, 3)
+    noview = "output_linear.weight" in params
+    dirs = None if noview else viewdirs[:, None].expand(pts.shape).reshape(-1, 3)
     outs = []
     for s in range(0, flat.shape[0], chunk):
         e = positional_encoding(flat[s:s + chunk], multires)
-        ed = positional_encoding(dirs[s:s + chunk], multires_views)
+        ed = None if noview else positional_encoding(dirs[s:s + chunk], multires_views)
         outs.append(mlp(params, e, ed, bf16=bf16))
-    return torch.cat(outs, 0).reshape(list(pts.shape[:-1]) + [4])
+    out = torch.cat(outs, 0)
+    return out.reshape(list(pts.shape[:-1]) + [out.shape[-1]])
 
 
 # --------------------------------------------------------------------------------------

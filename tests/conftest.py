@@ -22,6 +22,13 @@ def golden():
 
 
 @pytest.fixture(scope="session")
+def golden_noview():
+    """The same for use_viewdirs=False (tests/golden/make_golden_noview.py)."""
+    with np.load(os.path.join(ROOT, "tests", "golden", "reference_noview_golden.npz")) as z:
+        return {k: z[k] for k in z.files}
+
+
+@pytest.fixture(scope="session")
 def golden_meta():
     import json
     with open(os.path.join(ROOT, "tests", "golden", "reference_golden_meta.json")) as f:

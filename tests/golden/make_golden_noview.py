@@ -1,0 +1,65 @@
+"""Generate tests/golden/reference_noview_golden.npz by running the UNMODIFIED reference (/root/reference)
+with use_viewdirs=False (nerf.py:93-94,131-132; render_utils.py:205,225: ray rows of 8 columns).
+
+Run in the build container only:  python tests/golden/make_golden_noview.py
+Every array written here comes out of reference code; inputs come from oracle.nerf_oracle's seeded generators.
+"""
+import contextlib
+import io
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+sys.path.insert(0, ROOT)
+
+import refimport  # noqa: E402
+
+nerf, render_utils, utils = refimport.load()
+from oracle import nerf_oracle as O  # noqa: E402
+
+torch.set_num_threads(8)
+
+
+def npy(t):
+    return t.detach().cpu().numpy() if torch.is_tensor(t) else np.asarray(t)
+
+
+def ref_model(params, output_ch):
+    m = nerf.NeRF(D=8, W=256, output_ch=output_ch, skips=[4], use_viewdirs=False, multires=10, multires_views=4)
+    m.load_state_dict(params, strict=True)
+    return m
+
+
+out = {}
+rng = np.random.default_rng(21)
+# output_ch = 5 is what create_nerf_models builds when N_importance > 0 (utils.py:122); 4 is the constructor default
+p5c, p5f, p4 = O.make_params(31, output_ch=5), O.make_params(32, output_ch=5), O.make_params(33, output_ch=4)
+pts = torch.from_numpy(rng.uniform(-3.0, 3.0, size=(5, 24, 3)).astype(np.float32))
+with torch.no_grad():
+    out["mlp/pts"] = npy(pts)
+    out["mlp/raw5_seed31"] = npy(ref_model(p5c, 5)(pts, None))
+    out["mlp/raw4_seed33"] = npy(ref_model(p4, 4)(pts, None))
+
+for tag, (H, W, K, c2w, kw) in {
+    "blender": (6, 7, O.blender_intrinsics(6, 7), O.pose_spherical(10.0, -30.0, 4.0),
+                dict(perturb=0.0, N_importance=128, white_bkgd=True, ndc=False, near=2.0, far=6.0)),
+    "llff_ndc": (6, 8, O.llff_intrinsics(6, 8, 6.5), O.llff_pose(3),
+                 dict(perturb=0.0, N_importance=64, white_bkgd=False, ndc=True, near=0.0, far=1.0)),
+}.items():
+    with contextlib.redirect_stdout(io.StringIO()):
+        r = render_utils.Renderer(N_samples=64, use_viewdirs=False, raw_noise_std=0.0, lindisp=False, **kw)
+    with torch.no_grad():
+        rgb, disp, acc, extras = r.render(H, W, K, ref_model(p5c, 5), ref_model(p5f, 5), chunk=32,
+                                          c2w=torch.Tensor(c2w[:3, :4]), retraw=True)
+    out["render/%s/K" % tag], out["render/%s/c2w" % tag] = K, c2w
+    out["render/%s/rgb" % tag], out["render/%s/disp" % tag], out["render/%s/acc" % tag] = npy(rgb), npy(disp), npy(acc)
+    for k in ("rgb0", "disp0", "acc0", "z_std", "raw"):
+        out["render/%s/%s" % (tag, k)] = npy(extras[k])
+
+np.savez_compressed(os.path.join(HERE, "reference_noview_golden.npz"), **out)
+print("wrote", len(out), "arrays,", os.path.getsize(os.path.join(HERE, "reference_noview_golden.npz")), "bytes")

@@ -84,6 +84,48 @@ def test_render_image_golden(golden, precision, tol):
     assert mse < 1e-6   # PSNR between ours and the reference render > 60 dB
 
 
+def _noview_model(seed, output_ch):
+    from nerf_shared_b200 import nerf
+    m = nerf.NeRF(D=8, W=256, output_ch=output_ch, skips=[4], use_viewdirs=False, multires=10, multires_views=4)
+    m.load_state_dict(O.make_params(seed, output_ch=output_ch), strict=True)
+    return m.cuda()
+
+
+def test_no_viewdirs_forward_and_render_golden(golden_noview):
+    """use_viewdirs=False (nerf.py:93-94,131-132; 8-column ray rows render_utils.py:225): fp32 kernel, forward only"""
+    g = golden_noview
+    pts = cuda(g["mlp/pts"])
+    m5, m5f, m4 = _noview_model(31, 5), _noview_model(32, 5), _noview_model(33, 4)
+    with torch.no_grad():
+        raw5, raw4 = m5(pts, None), m4(pts, None)
+    assert raw5.shape == (5, 24, 5) and raw4.shape == (5, 24, 4)
+    assert maxabs(raw5, T(g["mlp/raw5_seed31"])) <= 3e-5
+    assert maxabs(raw4, T(g["mlp/raw4_seed33"])) <= 3e-5
+    with pytest.raises(NotImplementedError):      # no backward kernels for this model: refuse instead of silently detaching
+        m5(pts, None)
+    with pytest.raises(TypeError), torch.no_grad():
+        m5(pts, pts[:, 0])
+    r = _renderer(use_viewdirs=False, N_importance=128, white_bkgd=True, ndc=False, near=2.0, far=6.0)
+    with torch.no_grad():
+        rgb, disp, acc, extras = r.render(6, 7, g["render/blender/K"], m5, m5f, chunk=32, c2w=cuda(g["render/blender/c2w"])[:3, :4])
+    assert rgb.shape == (6, 7, 3) and extras["raw"].shape == (6, 7, 192, 5)
+    for ours, key in ((rgb, "rgb"), (acc, "acc"), (extras["rgb0"], "rgb0"), (extras["acc0"], "acc0"), (extras["z_std"], "z_std")):
+        assert maxabs(ours, T(g["render/blender/" + key])) <= 3e-5, key
+    # fine raw: the resampled depths differ in their last bits and the 2^9 encoding octave amplifies that
+    assert maxabs(extras["raw"], T(g["render/blender/raw"])) <= 5e-3
+    r = _renderer(use_viewdirs=False, N_importance=64, white_bkgd=False, ndc=True, near=0.0, far=1.0)
+    with torch.no_grad():
+        rgb, disp, acc, extras = r.render(6, 8, g["render/llff_ndc/K"], m5, m5f, chunk=32, c2w=cuda(g["render/llff_ndc/c2w"])[:3, :4])
+    assert maxabs(rgb, T(g["render/llff_ndc/rgb"])) <= 3e-5
+    assert maxabs(acc, T(g["render/llff_ndc/acc"])) <= 3e-5
+    # a larger ragged batch (not a multiple of the 64-sample tile) against the oracle
+    rng = np.random.default_rng(3)
+    big = torch.from_numpy(rng.uniform(-3, 3, size=(37, 67, 3)).astype(np.float32))
+    with torch.no_grad():
+        ours = m5(big.cuda(), None)
+    assert maxabs(ours, O.nerf_query(O.make_params(31, output_ch=5), big, None)) <= 3e-5
+
+
 def test_render_stress_weights(golden):
     """matrices x1.59: saturating alpha; fp32 path must still match tightly"""
     rb = cuda(golden["rr/ray_batch"])

@@ -185,6 +185,25 @@ def test_render_image(golden):
     np.testing.assert_allclose(acc.numpy(), g["render/llff_ndc/acc"], rtol=0, atol=1e-5)
 
 
+def test_no_viewdirs_model_and_render(golden_noview):
+    """use_viewdirs=False: trunk -> output_linear (nerf.py:131-132), 8-column ray rows (render_utils.py:225)"""
+    g = golden_noview
+    pts = T(g["mlp/pts"])
+    np.testing.assert_allclose(O.nerf_query(O.make_params(31, output_ch=5), pts, None).numpy(), g["mlp/raw5_seed31"],
+                               rtol=0, atol=2e-6)
+    np.testing.assert_allclose(O.nerf_query(O.make_params(33, output_ch=4), pts, None).numpy(), g["mlp/raw4_seed33"],
+                               rtol=0, atol=2e-6)
+    pc, pf = O.make_params(31, output_ch=5), O.make_params(32, output_ch=5)
+    rgb, disp, acc = O.render_image(pc, pf, 6, 7, g["render/blender/K"], T(g["render/blender/c2w"])[:3, :4], 2.0, 6.0,
+                                    n_importance=128, white_bkgd=True)
+    np.testing.assert_allclose(rgb.numpy(), g["render/blender/rgb"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(acc.numpy(), g["render/blender/acc"], rtol=0, atol=1e-5)
+    rgb, disp, acc = O.render_image(pc, pf, 6, 8, g["render/llff_ndc/K"], T(g["render/llff_ndc/c2w"])[:3, :4], 0.0, 1.0,
+                                    ndc=True, n_importance=64, white_bkgd=False)
+    np.testing.assert_allclose(rgb.numpy(), g["render/llff_ndc/rgb"], rtol=0, atol=1e-5)
+    np.testing.assert_allclose(acc.numpy(), g["render/llff_ndc/acc"], rtol=0, atol=1e-5)
+
+
 def test_train_step_grads(golden):
     rb = T(golden["rr/ray_batch"])
     ro, rd = rb[:, 0:3].contiguous(), rb[:, 3:6].contiguous()
