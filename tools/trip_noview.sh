@@ -1,3 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_render.py tests/test_gpu_mlp.py -x -q -m gpu > gpurun_out/noview_pytest.log 2>&1; echo "pytest exit $?"; tail -25 gpurun_out/noview_pytest.log
+timeout 600 python tools/fit_curve.py --impl ours --steps 600 > gpurun_out/fit_ours.txt 2>gpurun_out/fit_ours.err; echo "fit exit $?"; cat gpurun_out/fit_ours.txt; tail -3 gpurun_out/fit_ours.err
