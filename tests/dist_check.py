@@ -1,4 +1,4 @@
-"""torchrun --nproc-per-node N tools/dist_check.py : N-rank results == 1-rank results on real GPUs.
+"""torchrun --nproc-per-node N tests/dist_check.py : N-rank results == 1-rank results on real GPUs.
 (a) row-sharded render == single-GPU render (bitwise: per-ray work is independent of the split);
 (b) N ranks on equal ray shards + flat-gradient all-reduce + Adam == one rank on the whole batch."""
 import os

@@ -1,6 +1,6 @@
 """CLI of tests/fit_scene.py: the loss curve of the training loop on the analytic sphere scene.
-    python tools/fit_curve.py --impl ours --steps 300 > gpurun_out/fit_ours.txt                  (GPU box)
-    python tools/fit_curve.py --impl reference --steps 300 > tests/golden/reference_fit_curve.txt  (build container, CPU)
+    python tests/fit_curve.py --impl ours --steps 300 > gpurun_out/fit_ours.txt                  (GPU box)
+    python tests/fit_curve.py --impl reference --steps 300 > tests/golden/reference_fit_curve.txt  (build container, CPU)
 """
 import argparse
 import os

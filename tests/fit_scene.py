@@ -1,7 +1,7 @@
 """Loss curve of main.py's training loop on an analytic scene (unit sphere at the origin shaded by its normal, white
 background, 6 training views of 64x64, one held-out view).  `run("ours", ...)` drives train.GraphedTrainStep on cuda:0;
 `run("reference", ...)` drives the UNMODIFIED reference (/root/reference, CPU, build container only) on the same ray
-selections -- that is how tests/golden/reference_fit_curve.txt was made (tools/fit_curve.py --impl reference).
+selections -- that is how tests/golden/reference_fit_curve.txt was made (tests/fit_curve.py --impl reference).
 Random draws inside the renderer (perturb = 1) differ between the two, so the curves agree statistically, not step by
 step.  Test infrastructure."""
 import contextlib

@@ -344,7 +344,7 @@ def test_large_batch_gradient_is_mean_of_shard_gradients():
 def test_training_loss_curve_follows_the_reference():
     """main.py's loop (graphed step, perturb = 1, 1,024 random rays of 6 views per step) on a 3-D consistent analytic
     scene, against the loss curve the UNMODIFIED reference produced on the same ray selections
-    (tests/golden/reference_fit_curve.txt, made by tools/fit_curve.py --impl reference): the end-to-end check that
+    (tests/golden/reference_fit_curve.txt, made by tests/fit_curve.py --impl reference): the end-to-end check that
     gradients, Adam and the weight re-packing move the model the way the reference's autograd + torch.optim.Adam do.
     The stratified / importance draws differ between the two, hence a statistical tolerance per 25-step mean."""
     import os

@@ -4,7 +4,7 @@ import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench
 from nerf_shared_b200 import utils
-from oracle import nerf_oracle as O
+
 dev = torch.device("cuda:0"); utils.device = dev
 args = bench.Args()
 K, poses, images = bench.synth_scene()
