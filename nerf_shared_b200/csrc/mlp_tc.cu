@@ -591,7 +591,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFwdThreads, 1)
 static int build_pack_args(const NbMlpWeights* w, PackArgs& a) {
   const int in_ch = 3 + 6 * w->L_pts, in_views = 3 + 6 * w->L_dirs;
   if (in_ch > 64 || in_views > 32 || w->L_pts < 0 || w->L_dirs < 0) {
-    set_error("tensor-core MLP supports multires <= 10 and multires_views <= 4 (got %d, %d); use the fp32 path",
+    set_error("tensor-core MLP supports multires <= 10 and multires_views <= 4 (got %d, %d); use the fp32 path: nerf.set_default_precision(\"fp32\") or NERF_B200_PRECISION=fp32, inference only",
               w->L_pts, w->L_dirs);
     return NB_E_UNSUPPORTED;
   }
@@ -658,7 +658,8 @@ int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, c
   NB_REQUIRE(packed && pts && viewdirs && raw && S >= 1, "nb_mlp_fwd_tc: bad arguments");
   NB_REQUIRE(M % S == 0, "nb_mlp_fwd_tc: M=%lld is not a multiple of S=%d", (long long)M, S);
   if (L_pts != 10 || L_dirs != 4) {
-    set_error("nb_mlp_fwd_tc: only multires=10 / multires_views=4 is instantiated (got %d, %d)", L_pts, L_dirs);
+    set_error("nb_mlp_fwd_tc: only multires=10 / multires_views=4 is instantiated (got %d, %d); other widths run on the fp32 kernel "
+              "(nerf.set_default_precision(\"fp32\") or NERF_B200_PRECISION=fp32, inference only)", L_pts, L_dirs);
     return NB_E_UNSUPPORTED;
   }
   const int64_t tiles = (M + kTileM - 1) / kTileM;

@@ -1,5 +1,6 @@
 """Generate tests/golden/reference_noview_golden.npz by running the UNMODIFIED reference (/root/reference)
-with use_viewdirs=False (nerf.py:93-94,131-132; render_utils.py:205,225: ray rows of 8 columns).
+with use_viewdirs=False (nerf.py:93-94,131-132; render_utils.py:205,225: ray rows of 8 columns), plus the model of
+configs/stonehenge.txt (multires 15 / 6).
 
 Run in the build container only:  python tests/golden/make_golden_noview.py
 Every array written here comes out of reference code; inputs come from oracle.nerf_oracle's seeded generators.
@@ -44,6 +45,16 @@ with torch.no_grad():
     out["mlp/pts"] = npy(pts)
     out["mlp/raw5_seed31"] = npy(ref_model(p5c, 5)(pts, None))
     out["mlp/raw4_seed33"] = npy(ref_model(p4, 4)(pts, None))
+
+# configs/stonehenge.txt: multires = 15, multires_views = 6 (93- and 39-wide encodings), use_viewdirs=True
+p156 = O.make_params(41, input_ch=93, input_ch_views=39)
+m156 = nerf.NeRF(D=8, W=256, output_ch=5, skips=[4], use_viewdirs=True, multires=15, multires_views=6)
+m156.load_state_dict(p156, strict=True)
+pts156 = torch.from_numpy(rng.uniform(-1.5, 1.5, size=(5, 24, 3)).astype(np.float32))
+vd156 = torch.nn.functional.normalize(torch.from_numpy(rng.normal(size=(5, 3)).astype(np.float32)), dim=-1)
+with torch.no_grad():
+    out["mlp156/pts"], out["mlp156/viewdirs"] = npy(pts156), npy(vd156)
+    out["mlp156/raw_seed41"] = npy(m156(pts156, vd156))
 
 for tag, (H, W, K, c2w, kw) in {
     "blender": (6, 7, O.blender_intrinsics(6, 7), O.pose_spherical(10.0, -30.0, 4.0),

@@ -126,6 +126,26 @@ def test_no_viewdirs_forward_and_render_golden(golden_noview):
     assert maxabs(ours, O.nerf_query(O.make_params(31, output_ch=5), big, None)) <= 3e-5
 
 
+def test_wide_encoding_model_on_the_fp32_kernel(golden_noview):
+    """configs/stonehenge.txt (multires 15 / 6: 93- and 39-wide encodings): evaluated by the fp32 kernel; the
+    tensor-core kernels tile 63 / 27 only and must say so instead of computing something else"""
+    from nerf_shared_b200 import nerf
+    g = golden_noview
+    m = nerf.NeRF(D=8, W=256, output_ch=5, skips=[4], use_viewdirs=True, multires=15, multires_views=6)
+    m.load_state_dict(O.make_params(41, input_ch=93, input_ch_views=39), strict=True)
+    m = m.cuda()
+    pts, vd = cuda(g["mlp156/pts"]), cuda(g["mlp156/viewdirs"])
+    m.precision = "fp32"
+    with torch.no_grad():
+        raw = m(pts, vd)
+    # sin / cos of arguments up to 2^14 * 1.5: the device functions and ATen's differ in the last bits there
+    assert maxabs(raw, T(g["mlp156/raw_seed41"])) <= 2e-4
+    m.precision = "bf16"
+    with pytest.raises(Exception) as e, torch.no_grad():
+        m(pts, vd)
+    assert "multires" in str(e.value) or "octaves" in str(e.value) or "encoding" in str(e.value), str(e.value)
+
+
 def test_render_stress_weights(golden):
     """matrices x1.59: saturating alpha; fp32 path must still match tightly"""
     rb = cuda(golden["rr/ray_batch"])

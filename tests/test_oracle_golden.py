@@ -204,6 +204,14 @@ def test_no_viewdirs_model_and_render(golden_noview):
     np.testing.assert_allclose(acc.numpy(), g["render/llff_ndc/acc"], rtol=0, atol=1e-5)
 
 
+def test_wide_encoding_model(golden_noview):
+    """configs/stonehenge.txt: multires 15 / 6"""
+    g = golden_noview
+    raw = O.nerf_query(O.make_params(41, input_ch=93, input_ch_views=39), T(g["mlp156/pts"]), T(g["mlp156/viewdirs"]),
+                       multires=15, multires_views=6)
+    np.testing.assert_allclose(raw.numpy(), g["mlp156/raw_seed41"], rtol=0, atol=2e-6)
+
+
 def test_train_step_grads(golden):
     rb = T(golden["rr/ray_batch"])
     ro, rd = rb[:, 0:3].contiguous(), rb[:, 3:6].contiguous()
