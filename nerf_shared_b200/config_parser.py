@@ -10,9 +10,24 @@ try:
 except Exception:  # pragma: no cover
     _cap = None
 
+
+
+def _str2bool(v):
+    """`tensorboard = False` in a config file must mean False (argparse's type=bool maps every non-empty string,
+    including "False", to True: config_parser.py:113 of the reference has that trap)."""
+    if isinstance(v, bool):
+        return v
+    if str(v).strip().lower() in ("1", "true", "yes", "y", "on"):
+        return True
+    if str(v).strip().lower() in ("0", "false", "no", "n", "off", ""):
+        return False
+    raise argparse.ArgumentTypeError("expected a boolean, got %r" % (v,))
+
+
 # (flag, kwargs)
 _OPTIONS = [
-    ("--training", dict(type=bool, default=True, help="run training")),
+    # store_true as in the reference (config_parser.py:14): configs without `training = True` (e.g. fern.txt) do not train
+    ("--training", dict(action="store_true", help="run the training loop of main.py")),
     ("--expname", dict(type=str, help="experiment name")),
     ("--basedir", dict(type=str, default="./logs/", help="where to store ckpts and logs")),
     ("--datadir", dict(type=str, default="./data/llff/fern", help="input data directory")),
@@ -39,7 +54,7 @@ _OPTIONS = [
     ("--i_print", dict(type=int, default=100)), ("--i_img", dict(type=int, default=500)),
     ("--i_weights", dict(type=int, default=10000)), ("--i_testset", dict(type=int, default=50000)),
     ("--i_video", dict(type=int, default=50000)),
-    ("--tensorboard", dict(type=bool, default=False)),
+    ("--tensorboard", dict(type=_str2bool, default=False)),
 ]
 
 

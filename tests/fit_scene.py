@@ -30,8 +30,9 @@ def _scene(utils, dev, thetas):
     return ro, rd, torch.where((disc > 0)[:, None], 0.5 + 0.5 * normal, torch.ones_like(normal))
 
 
-def run(impl, steps, every=25, log=None):
-    """-> ([(step, mean loss of the last `every` steps)], PSNR of the held-out view in dB)"""
+def run(impl, steps, every=25, log=None, return_models=False):
+    """-> ([(step, mean loss of the last `every` steps)], PSNR of the held-out view in dB)
+    (return_models=True: also the trained coarse / fine modules)"""
     if impl == "reference":
         here = os.path.dirname(os.path.abspath(__file__))
         sys.path.insert(0, os.path.join(here, "golden"))
@@ -89,4 +90,5 @@ def run(impl, steps, every=25, log=None):
     with torch.no_grad():
         rgb = r.render_from_rays(H, W, K, chunk=32768, rays=torch.stack([to, td], 0), coarse_model=mc, fine_model=mf,
                                  retraw=False)[0]
-    return curve, float(utils.mse2psnr(utils.img2mse(rgb, truth)))
+    psnr = float(utils.mse2psnr(utils.img2mse(rgb, truth)))
+    return (curve, psnr, mc, mf) if return_models else (curve, psnr)
