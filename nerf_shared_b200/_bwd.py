@@ -57,6 +57,13 @@ def nerf_mlp_backward(ctx, g_raw):
         in_place = target is not None and target[0].device == dev
         if in_place:
             grads, offs = target
+            # model.zero_grad() / p.grad = None since the last backward (set_to_none is torch's default): the user
+            # asked for fresh gradients, so clear this model's slices before accumulating into them, and hand the
+            # views back afterwards -- otherwise p.grad stays None and the optimizer would discard the result
+            cleared = [i for i, p in enumerate(params) if p.grad is None and ctx.needs_input_grad[5 + i]]
+            if cleared:
+                for i in cleared:
+                    grads[offs[i]:offs[i] + params[i].numel()].zero_()
         else:
             offs, total = grad_layout(model)
             grads = torch.zeros((total,), device=dev, dtype=torch.float32)
@@ -75,6 +82,9 @@ def nerf_mlp_backward(ctx, g_raw):
             d_vd = torch.zeros((M // S, 3), device=dev, dtype=torch.float32)
             check(lib.nb_mlp_bwd_inputs(ptr(packed_ingrad(model)), L, Lv, ptr(dA), ptr(pts), ptr(viewdirs), M, S,
                                         ptr(d_pts), ptr(d_vd), stream_ptr()), "nb_mlp_bwd_inputs")
+    if need_w and in_place:
+        for i in cleared:
+            params[i].grad = grads[offs[i]:offs[i] + params[i].numel()].view_as(params[i])
     out = []
     for i, p in enumerate(params):
         use = need_w and ctx.needs_input_grad[5 + i] and not in_place

@@ -69,7 +69,10 @@ class FlatAdam(torch.optim.Optimizer):
         self.flat_g.zero_()
 
     def _regather(self):
-        """Someone replaced a p.grad (set_to_none, external assignment): copy back into the flat buffer."""
+        """Someone replaced a p.grad (set_to_none, external assignment): bring the flat buffer and the views back in
+        line.  A parameter whose .grad is None has had no backward since it was cleared -- the in-place
+        weight-gradient path (_bwd.py) re-attaches the views of every parameter it writes -- so its slice is zeroed,
+        which is what "no gradient" means to the flat kernel."""
         with torch.no_grad():
             for p, o in zip(self._params, self._offsets):
                 view = self.flat_g[o:o + p.numel()].view(p.shape)
@@ -78,6 +81,27 @@ class FlatAdam(torch.optim.Optimizer):
                 elif p.grad.data_ptr() != view.data_ptr():
                     view.copy_(p.grad)
                 p.grad = view
+
+    def grad_view(self, p):
+        """The slice of the flat gradient buffer that is `p.grad` (None for foreign parameters)."""
+        o = self._by_id.get(id(p))
+        return None if o is None else self.flat_g[o:o + p.numel()].view(p.shape)
+
+    def _segments(self):
+        """[(offset, count)] of the trainable parameters, neighbours merged.  torch.optim.Adam skips parameters
+        without a gradient (requires_grad=False); one launch per segment keeps their weights and moments untouched."""
+        key = tuple(p.requires_grad for p in self._params)
+        if getattr(self, "_seg_key", None) != key:
+            segs = []
+            for p, o in zip(self._params, self._offsets):
+                if not p.requires_grad:
+                    continue
+                if segs and segs[-1][0] + segs[-1][1] == o:
+                    segs[-1] = (segs[-1][0], segs[-1][1] + p.numel())
+                else:
+                    segs.append((o, p.numel()))
+            self._seg_key, self._segs = key, segs
+        return self._segs
 
     def _lr(self):
         g0 = self.param_groups[0]
@@ -121,23 +145,24 @@ class FlatAdam(torch.optim.Optimizer):
     @torch.no_grad()
     def step(self, closure=None):
         loss = closure() if closure is not None else None
+        lib = _lib.load()
         if self.in_graph:
-            lib = _lib.load()
             with torch.cuda.device(self.flat_p.device):
-                check(lib.nb_adam_step_dev(ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq),
-                                           self._n, ptr(self._hyper), stream_ptr()), "nb_adam_step_dev")
+                for o, n in self._segments():
+                    check(lib.nb_adam_step_dev(ptr(self.flat_p[o:]), ptr(self.flat_g[o:]), ptr(self.exp_avg[o:]),
+                                               ptr(self.exp_avg_sq[o:]), n, ptr(self._hyper), stream_ptr()), "nb_adam_step_dev")
             return loss
         if not self._grads_are_flat():
             self._regather()
         g0 = self._lr()
         self._step += 1
         b1, b2 = g0["betas"]
-        lib = _lib.load()
         _lib.ensure_device(self.flat_p.device)
         with torch.cuda.device(self.flat_p.device):
-            check(lib.nb_adam_step(ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq), self._n,
-                                   float(g0["lr"]), float(b1), float(b2), float(g0["eps"]), int(self._step),
-                                   float(self.grad_scale), stream_ptr()), "nb_adam_step")
+            for o, n in self._segments():
+                check(lib.nb_adam_step(ptr(self.flat_p[o:]), ptr(self.flat_g[o:]), ptr(self.exp_avg[o:]),
+                                       ptr(self.exp_avg_sq[o:]), n, float(g0["lr"]), float(b1), float(b2), float(g0["eps"]),
+                                       int(self._step), float(self.grad_scale), stream_ptr()), "nb_adam_step")
         self.bump_versions()
         return loss
 

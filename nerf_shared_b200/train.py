@@ -30,6 +30,12 @@ class GraphedTrainStep:
         self.world = torch.distributed.get_world_size(group) if (
             torch.distributed.is_available() and torch.distributed.is_initialized()) else 1
         dev = optimizer.flat_p.device
+        if self.world > 1:
+            # SUM all-reduce of equal ray shards, averaged inside the Adam kernel; every rank starts from rank 0's weights
+            optimizer.grad_scale = 1.0 / self.world
+            torch.distributed.broadcast(optimizer.flat_p, src=torch.distributed.get_global_rank(group, 0) if group is not None else 0,
+                                        group=group)
+            optimizer.bump_versions()
         self.rays = torch.zeros((2, n_rays, 3), device=dev, dtype=torch.float32)
         self.target = torch.zeros((n_rays, 3), device=dev, dtype=torch.float32)
         self.graph = None

@@ -207,14 +207,21 @@ def _choice_without_replacement(n, k):
 
 
 def _pinned_stage(n):
-    """Two alternating pinned staging buffers per batch size (async H2D must not race the next fill)."""
+    """Rotating pinned staging buffers per batch size.  A stage is refilled only after the H2D copies that read it
+    last time have completed (`ev`, recorded by the caller after issuing them): the training loop never
+    synchronises per step, so without the event the host could run more than a ring ahead of the GPU and tear a
+    batch.  Allocated with device="cpu" explicitly: main.py:151 makes CUDA the default tensor type."""
     st = _stages.get(n)
     if st is None:
-        st = {"i": 0, "bufs": [{"pix": torch.empty(n, dtype=torch.int64).pin_memory(),
-                                 "tgt": torch.empty((n, 3), dtype=torch.float32).pin_memory()} for _ in range(4)]}
+        st = {"i": 0, "bufs": [{"pix": torch.empty(n, dtype=torch.int64, device="cpu", pin_memory=True),
+                                 "tgt": torch.empty((n, 3), dtype=torch.float32, device="cpu", pin_memory=True),
+                                 "ev": None} for _ in range(4)]}
         _stages[n] = st
     st["i"] = (st["i"] + 1) % len(st["bufs"])
-    return st["bufs"][st["i"]]
+    b = st["bufs"][st["i"]]
+    if b["ev"] is not None:
+        b["ev"].synchronize()
+    return b
 
 # ----------------------------------------------------------------------------- batching (utils.py:360-442)
 def batch_training_data(args, poses, hwf, K, images, i_train):
@@ -272,6 +279,9 @@ def sample_random_ray_batch(args, images, poses, rays_rgb, N_rand, use_batching,
         stage["tgt"].copy_(torch.from_numpy(np.ascontiguousarray(tnp[py, px], dtype=np.float32)))
         pix = stage["pix"].to(device, non_blocking=True)
         target_s = stage["tgt"].to(device, non_blocking=True)
+        if stage["ev"] is None:
+            stage["ev"] = torch.cuda.Event()
+        stage["ev"].record(torch.cuda.current_stream(pix.device))
     rays_o, rays_d = get_rays_at(H, W, K, pose, pix)
     return torch.stack([rays_o, rays_d], 0), target_s, rays_rgb, i_batch
 
@@ -296,17 +306,22 @@ def render_path(render_poses, hwf, K, chunk, renderer_and_models, gt_imgs=None, 
         H, W = H // render_factor, W // render_factor
         K = np.array(K, dtype=np.float64) / render_factor
         K[2][2] = 1.0
+    from .render_utils import FrameDownloader, _write_image
     rgbs, disps = [], []
+
+    def finish(n, arrs):                       # frame n's host work runs while the GPU renders frame n + 1
+        rgbs.append(arrs[0])
+        disps.append(arrs[1])
+        if savedir is not None:
+            _write_image(os.path.join(savedir, "{:03d}.png".format(n)), arrs[2])
+
+    down = FrameDownloader(finish)
     with torch.no_grad():
         for n, c2w in enumerate(render_poses):
-            rgb, disp, _, _ = renderer.render_from_pose(H, W, K, chunk, torch.as_tensor(c2w, dtype=torch.float32)[:3, :4],
-                                                        coarse, fine, retraw=False)
-            rgb8 = to8b_device(rgb) if savedir is not None else None     # the PNG's bytes are made on the device
-            rgbs.append(rgb.cpu().numpy())
-            disps.append(disp.cpu().numpy())
-            if savedir is not None:
-                from .render_utils import _write_image
-                _write_image(os.path.join(savedir, "{:03d}.png".format(n)), rgb8.cpu().numpy())
+            c2w = c2w if torch.is_tensor(c2w) else torch.as_tensor(np.asarray(c2w), dtype=torch.float32)
+            rgb, disp, _, _ = renderer.render_from_pose(H, W, K, chunk, c2w[:3, :4], coarse, fine, retraw=False)
+            down.submit(n, (rgb, disp) + ((to8b_device(rgb),) if savedir is not None else ()))   # the PNG's bytes are made on the device
+        down.drain()
     return np.stack(rgbs, 0), np.stack(disps, 0)
 
 
