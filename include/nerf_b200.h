@@ -128,6 +128,18 @@ NB_API int nb_mse_pair_fwd(const float* rgb, const float* rgb0, const float* tar
 NB_API int nb_mse_pair_bwd(const float* rgb, const float* rgb0, const float* target, int64_t n3, const float* g_fine,
                     const float* g_coarse, const float* g_total, float* d_rgb, float* d_rgb0, void* stream);
 
+/* Training fusion: compositing forward + the MSE term of this map against `target` [n,3] + the compositing backward of
+ * that term, one pass over raw.  inv_n3 = 1 / (3 * rays of the GLOBAL batch the mean runs over).  loss_sum (one float,
+ * zeroed by the caller) += sum (rgb_map - target)^2 * inv_n3.  d_raw = d(that MSE term)/d raw.  rgb_map / disp / acc /
+ * weights may be NULL.
+ * replaces: raw2outputs render_utils.py:241-290 + img2mse utils.py:24 (main.py:87,93) + their autograd (main.py:103). */
+NB_API int nb_composite_train(const float* raw, const float* z, const float* rays_d, const float* noise, const float* target,
+                       int64_t n, int S, int white_bkgd, float inv_n3, float* rgb_map, float* disp, float* acc,
+                       float* weights, float* d_raw, float* loss_sum, void* stream);
+/* out4 = { acc_fine[0], acc_coarse[0] (0 when NULL), their sum, -10 log10(acc_fine[0]) }; both accumulators are reset
+ * to zero for the next step.  replaces: main.py:87-99 (loss sum, mse2psnr utils.py:27). */
+NB_API int nb_loss_finalize(float* acc_fine, float* acc_coarse, float* out4, void* stream);
+
 /* ---- frame output ------------------------------------------------------------------------ */
 /* out[i] = (uint8)(255 * clip(x[i], 0, 1)), NumPy's truncating cast.  replaces: utils.to8b utils.py:30 (host NumPy) in
  * render_path / render_from_batch_poses (utils.py:330-357, render_utils.py:293-319). */

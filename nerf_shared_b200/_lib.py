@@ -46,6 +46,8 @@ SIGNATURES = {
     "nb_normalize_fwd": (i32, [vp, i64, vp, vp]),
     "nb_ray_rows": (i32, [vp, vp, vp, f32, f32, i64, vp, vp, vp]),
     "nb_to8b": (i32, [vp, i64, vp, vp]),
+    "nb_composite_train": (i32, [vp, vp, vp, vp, vp, i64, i32, i32, f32, vp, vp, vp, vp, vp, vp, vp]),
+    "nb_loss_finalize": (i32, [vp, vp, vp, vp]),
     "nb_mse_pair_fwd": (i32, [vp, vp, vp, i64, vp, vp]),
     "nb_mse_pair_bwd": (i32, [vp, vp, vp, i64, vp, vp, vp, vp, vp, vp]),
     "nb_normalize_bwd": (i32, [vp, vp, i64, vp, vp]),

@@ -455,3 +455,23 @@ def debug_umma(A: torch.Tensor, B: torch.Tensor) -> torch.Tensor:
     with torch.cuda.device(a.device):
         check(lib.nb_debug_umma(ptr(a), ptr(b), a.shape[1], ptr(D), stream_ptr()), "nb_debug_umma")
     return D
+
+
+def composite_train(raw, z, rays_d, noise, target, white_bkgd, inv_n3, loss_sum, want_weights=False):
+    """Compositing forward + this map's MSE term + its compositing backward in one launch (nb_composite_train):
+    -> (rgb_map, disp, acc, weights or None, d_raw); loss_sum (1 float, zeroed by the caller) accumulates the term."""
+    lib = _lib_for(raw)
+    r, zc, d, t = f32c(raw), f32c(z), f32c(rays_d), f32c(target)
+    nz = f32c(noise) if noise is not None else None
+    n, S = zc.shape
+    dev = r.device
+    rgb = torch.empty((n, 3), device=dev, dtype=torch.float32)
+    disp = torch.empty((n,), device=dev, dtype=torch.float32)
+    acc = torch.empty((n,), device=dev, dtype=torch.float32)
+    weights = torch.empty((n, S), device=dev, dtype=torch.float32) if want_weights else None
+    d_raw = torch.empty_like(r)
+    with torch.cuda.device(dev):
+        check(lib.nb_composite_train(ptr(r), ptr(zc), ptr(d), ptr(nz), ptr(t), n, S, int(bool(white_bkgd)), float(inv_n3),
+                                     ptr(rgb), ptr(disp), ptr(acc), ptr(weights), ptr(d_raw), ptr(loss_sum), stream_ptr()),
+              "nb_composite_train")
+    return rgb, disp, acc, weights, d_raw

@@ -317,6 +317,106 @@ __global__ void __launch_bounds__(256) composite_bwd_kernel(const float* __restr
   }
 }
 
+// Training fusion (main.py:77-103 between the MLP forward and its backward): compositing forward, the MSE term of
+// this map against the target pixels, and the compositing backward of that term, one pass over raw.  The loss is a
+// sum of per-map MSE terms (main.py:87-99), so d loss / d rgb_map = 2 (rgb_map - target) * inv_n3 is known as soon as
+// the ray's own map value is; nothing else of the batch is needed.  Replaces composite_fwd + mse_pair_fwd +
+// mse_pair_bwd + composite_bwd (four launches, raw read twice) on the critical path of the step.
+// loss_sum: one float, += sum over the batch of (rgb_map - target)^2 * inv_n3 (the caller zeroes it).
+template <int C, bool EXACT>
+__global__ void __launch_bounds__(256) composite_train_kernel(const float* __restrict__ raw, const float* __restrict__ z,
+                                                              const float* __restrict__ rays_d,
+                                                              const float* __restrict__ noise,
+                                                              const float* __restrict__ target, int64_t n, int S,
+                                                              int white_bkgd, float inv_n3, float* __restrict__ rgb_map,
+                                                              float* __restrict__ disp, float* __restrict__ acc_out,
+                                                              float* __restrict__ weights, float* __restrict__ d_raw,
+                                                              float* __restrict__ loss_sum) {
+  __shared__ float blk_loss[8];
+  const int lane = threadIdx.x & 31, wid = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+  const int64_t r = (int64_t)blockIdx.x * 8 + wid;
+  float sq = 0.f;
+  if (r < n) {
+    const float t0 = target[r * 3], t1 = target[r * 3 + 1], t2 = target[r * 3 + 2];
+    RayRegs<C, EXACT> ray;
+    ray.load(raw, z, noise, rays_d, r, S, lane);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, adepth = 0.f, aacc = 0.f;
+    float w[C];
+#pragma unroll
+    for (int j = 0; j < C; ++j) {
+      w[j] = ray.alpha[j] * ray.T[j];
+      a0 += w[j] * ray.c[j].x; a1 += w[j] * ray.c[j].y; a2 += w[j] * ray.c[j].z;
+      adepth += w[j] * ray.zz[j];
+      aacc += w[j];
+    }
+    if (weights) {
+      float* wp = weights + r * S + (int64_t)lane * C;
+#pragma unroll
+      for (int j = 0; j < C; ++j)
+        if (ray.valid(j, lane, S)) wp[j] = w[j];
+    }
+    a0 = warp_sum(a0); a1 = warp_sum(a1); a2 = warp_sum(a2);
+    adepth = warp_sum(adepth); aacc = warp_sum(aacc);
+    const float bg = white_bkgd ? (1.0f - aacc) : 0.0f;
+    const float m0 = a0 + bg, m1 = a1 + bg, m2 = a2 + bg;
+    if (lane == 0) {
+      if (rgb_map) { rgb_map[r * 3] = m0; rgb_map[r * 3 + 1] = m1; rgb_map[r * 3 + 2] = m2; }
+      if (acc_out) acc_out[r] = aacc;
+      if (disp) {
+        const float ratio = adepth / aacc;
+        const float m = (ratio != ratio) ? ratio : fmaxf(1e-10f, ratio);
+        disp[r] = 1.0f / m;
+      }
+    }
+    const float e0 = m0 - t0, e1 = m1 - t1, e2 = m2 - t2;
+    sq = (e0 * e0 + e1 * e1 + e2 * e2) * inv_n3;
+    const float s2 = 2.0f * inv_n3;
+    const float gr0 = s2 * e0, gr1 = s2 * e1, gr2 = s2 * e2;
+    const float gacc = white_bkgd ? -(gr0 + gr1 + gr2) : 0.f;
+    float lane_gw = 0.f;
+#pragma unroll
+    for (int j = 0; j < C; ++j) lane_gw += (gr0 * ray.c[j].x + gr1 * ray.c[j].y + gr2 * ray.c[j].z + gacc) * w[j];
+    float suffix = warp_excl_suffix_sum(lane_gw, lane);
+    float4* op = reinterpret_cast<float4*>(d_raw) + r * S + (int64_t)lane * C;
+#pragma unroll
+    for (int j = C - 1; j >= 0; --j) {
+      const float4 c = ray.c[j];
+      const float a = ray.alpha[j], T = ray.T[j];
+      const float g = gr0 * c.x + gr1 * c.y + gr2 * c.z + gacc;
+      const float e = 1.0f - a;
+      const float galpha = g * T - __fdividef(suffix, e + 1e-10f);
+      suffix += g * w[j];
+      const float gsigma = (c.w > 0.f) ? galpha * (ray.dz(j, lane, S) * ray.dnorm) * e : 0.f;
+      if (ray.valid(j, lane, S)) {
+        float4 o;
+        o.x = w[j] * gr0 * c.x * (1.0f - c.x);
+        o.y = w[j] * gr1 * c.y * (1.0f - c.y);
+        o.z = w[j] * gr2 * c.z * (1.0f - c.z);
+        o.w = gsigma;
+        __stcs(op + j, o);
+      }
+    }
+  }
+  if (lane == 0) blk_loss[wid] = sq;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += blk_loss[i];
+    atomicAdd(loss_sum, t);
+  }
+}
+
+// out4 = (mse_fine, mse_coarse, their sum, -10 log10(mse_fine)) from the two accumulators of composite_train, which
+// are reset for the next step (main.py:87-99)
+__global__ void loss_finalize_kernel(float* __restrict__ acc_fine, float* __restrict__ acc_coarse, float* __restrict__ out4) {
+  const float m = acc_fine[0], m0 = acc_coarse ? acc_coarse[0] : 0.f;
+  out4[0] = m; out4[1] = m0; out4[2] = m + m0;
+  out4[3] = -10.0f * logf(m) / logf(10.0f);
+  acc_fine[0] = 0.f;
+  if (acc_coarse) acc_coarse[0] = 0.f;
+}
+
 }  // namespace nb
 
 using namespace nb;
@@ -385,6 +485,42 @@ int nb_composite_bwd(const float* raw, const float* z, const float* rays_d, cons
   else NB_LAUNCH_BWD(16);
 #undef NB_LAUNCH_BWD
   return check_launch("nb_composite_bwd");
+}
+
+int nb_composite_train(const float* raw, const float* z, const float* rays_d, const float* noise, const float* target,
+                       int64_t n, int S, int white_bkgd, float inv_n3, float* rgb_map, float* disp, float* acc,
+                       float* weights, float* d_raw, float* loss_sum, void* stream) {
+  if (n == 0) return 0;
+  NB_REQUIRE(raw && z && rays_d && target && d_raw && loss_sum && S >= 1, "nb_composite_train: bad arguments");
+  if (S > 512) {
+    set_error("nb_composite_train: S=%d > 512 samples per ray is not implemented", S);
+    return NB_E_UNSUPPORTED;
+  }
+  NB_REQUIRE((n + 7) / 8 < (1ll << 31), "nb_composite_train: too many rays for one launch");
+  const unsigned grid = (unsigned)((n + 7) / 8);
+  cudaStream_t st = as_stream(stream);
+#define NB_LAUNCH_TR(C)                                                                                               \
+  do {                                                                                                                \
+    if (S == 32 * C)                                                                                                  \
+      composite_train_kernel<C, true><<<grid, 256, 0, st>>>(raw, z, rays_d, noise, target, n, S, white_bkgd, inv_n3,  \
+                                                            rgb_map, disp, acc, weights, d_raw, loss_sum);            \
+    else                                                                                                              \
+      composite_train_kernel<C, false><<<grid, 256, 0, st>>>(raw, z, rays_d, noise, target, n, S, white_bkgd, inv_n3, \
+                                                             rgb_map, disp, acc, weights, d_raw, loss_sum);           \
+  } while (0)
+  if (S <= 64) NB_LAUNCH_TR(2);
+  else if (S <= 128) NB_LAUNCH_TR(4);
+  else if (S <= 192) NB_LAUNCH_TR(6);
+  else if (S <= 256) NB_LAUNCH_TR(8);
+  else NB_LAUNCH_TR(16);
+#undef NB_LAUNCH_TR
+  return check_launch("nb_composite_train");
+}
+
+int nb_loss_finalize(float* acc_fine, float* acc_coarse, float* out4, void* stream) {
+  NB_REQUIRE(acc_fine && out4, "nb_loss_finalize: bad arguments");
+  loss_finalize_kernel<<<1, 1, 0, as_stream(stream)>>>(acc_fine, acc_coarse, out4);
+  return check_launch("nb_loss_finalize");
 }
 
 }  // extern "C"

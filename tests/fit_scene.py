@@ -30,7 +30,7 @@ def _scene(utils, dev, thetas):
     return ro, rd, torch.where((disc > 0)[:, None], 0.5 + 0.5 * normal, torch.ones_like(normal))
 
 
-def run(impl, steps, every=25, log=None, return_models=False):
+def run(impl, steps, every=25, log=None, return_models=False, raw_noise_std=0.0):
     """-> ([(step, mean loss of the last `every` steps)], PSNR of the held-out view in dB)
     (return_models=True: also the trained coarse / fine modules)"""
     if impl == "reference":
@@ -56,7 +56,7 @@ def run(impl, steps, every=25, log=None, return_models=False):
     mc, mf = model(11), model(12)
     with contextlib.redirect_stdout(io.StringIO()):
         r = render_utils.Renderer(perturb=1.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
-                                  raw_noise_std=0.0, near=2.0, far=6.0)
+                                  raw_noise_std=raw_noise_std, near=2.0, far=6.0)
     r.train()
     if impl == "reference":
         opt = torch.optim.Adam(list(mc.parameters()) + list(mf.parameters()), lr=5e-4, betas=(0.9, 0.999))
@@ -87,6 +87,7 @@ def run(impl, steps, every=25, log=None, return_models=False):
             if log is not None:
                 log("%5d  %.5f" % curve[-1])
     r.perturb = 0.0
+    r.raw_noise_std = 0.0
     with torch.no_grad():
         rgb = r.render_from_rays(H, W, K, chunk=32768, rays=torch.stack([to, td], 0), coarse_model=mc, fine_model=mf,
                                  retraw=False)[0]

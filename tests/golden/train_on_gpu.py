@@ -17,7 +17,8 @@ sys.path.insert(0, ROOT)
 from tests import fit_scene  # noqa: E402
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 4000
-curve, psnr, mc, mf = fit_scene.run("ours", steps, every=250, log=lambda s: print(s, flush=True), return_models=True)
+curve, psnr, mc, mf = fit_scene.run("ours", steps, every=250, log=lambda s: print(s, flush=True), return_models=True,
+                                     raw_noise_std=1.0)   # the seeds-11/12 initialisation has sigma < 0 everywhere: noise lets density start
 out = {"meta/steps": np.int64(steps), "meta/heldout_psnr": np.float64(psnr)}
 for tag, m in (("coarse", mc), ("fine", mf)):
     for k, v in m.state_dict().items():

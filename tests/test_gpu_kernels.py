@@ -373,3 +373,29 @@ def test_to8b_device_matches_numpy(mods):
     got = utils.to8b_device(x.cuda()).cpu().numpy()
     assert got.dtype == np.uint8 and np.array_equal(got, ref)
     assert np.array_equal(utils.to8b_device(x.cuda().reshape(-1)[:1001]).cpu().numpy(), ref.reshape(-1)[:1001])
+
+
+@pytest.mark.parametrize("S,white,with_noise", [(64, True, False), (192, True, True), (128, False, False), (100, True, False)])
+def test_composite_train_equals_separate_kernels(S, white, with_noise):
+    """nb_composite_train (compositing + MSE term + compositing backward in one pass) against nb_composite_fwd ->
+    img2mse -> autograd -> nb_composite_bwd on the same inputs."""
+    from nerf_shared_b200 import _ops
+    n = 777
+    g = torch.Generator().manual_seed(S)
+    raw = (torch.randn(n, S, 4, generator=g) * torch.tensor([1.0, 1.0, 1.0, 2.0])).cuda()
+    z = torch.sort(torch.rand(n, S, generator=g) * 4 + 2, -1)[0].cuda()
+    rd = torch.randn(n, 3, generator=g).cuda()
+    noise = torch.randn(n, S, generator=g).cuda() if with_noise else None
+    tgt = torch.rand(n, 3, generator=g).cuda()
+    raw_a = raw.clone().requires_grad_(True)
+    rgb, disp, acc, w, depth = _ops.Composite.apply(raw_a, z, rd, noise, white)
+    loss = torch.mean((rgb - tgt) ** 2)
+    loss.backward()
+    acc_sum = torch.zeros(1, device="cuda")
+    rgb2, disp2, acc2, w2, d_raw = _ops.composite_train(raw, z, rd, noise, tgt, white, 1.0 / (3 * n), acc_sum, want_weights=True)
+    # (S = 64 composites forward with the half-warp kernel: another reduction order, last-bit differences)
+    assert maxabs(rgb2, rgb) <= 2e-6 and maxabs(acc2, acc) <= 2e-6 and maxabs(w2, w) <= 1e-6
+    assert float(((disp2 - disp) / disp).nan_to_num().abs().max()) <= 1e-5
+    assert abs(float(acc_sum) - float(loss)) <= 2e-6 * float(loss)
+    scale = float(raw_a.grad.abs().max())
+    assert float((d_raw - raw_a.grad).abs().max()) <= 2e-6 * scale, float((d_raw - raw_a.grad).abs().max()) / scale
