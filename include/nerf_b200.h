@@ -37,6 +37,11 @@ NB_API const char* nb_last_error(void);
 /* Checks that `device` is sm_100 and sets the kernels' dynamic shared-memory attributes. */
 NB_API int nb_init(int device);
 NB_API int nb_shutdown(void);
+/* SM budget of the NEXT launches issued by the calling thread (0 = whole GPU): the persistent tensor-core MLP kernels
+ * (forward, dgrad) use at most `mlp_clusters` CTA pairs, the weight-gradient kernel at most `wgrad_ctas` CTAs (placed as
+ * pairs).  Used to run a bandwidth-bound and a tensor-bound kernel side by side on disjoint SMs; results do not depend
+ * on it.  New in this library (the reference has no launch control). */
+NB_API int nb_set_launch_limits(int mlp_clusters, int wgrad_ctas);
 /* Number of kernels this library has launched since load (all streams); for bench.py. */
 NB_API int64_t nb_launch_count(void);
 
@@ -197,6 +202,10 @@ NB_API int nb_mlp_pack_bwd(const NbMlpWeights* w, void* packed_bwd, void* stream
 NB_API int64_t nb_mlp_da_bytes(int64_t M);
 NB_API int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
                          void* dA, const int64_t* grad_off_host24, float* grads, void* stream);
+/* The same in two separately launchable parts (bit 0: the dgrad chain, writes dA; bit 1: weight gradients + head
+ * gradients from acts / dA / d_raw), so that a caller can put other work between them or on another stream. */
+NB_API int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
+                        void* dA, const int64_t* grad_off_host24, float* grads, int parts, void* stream);
 
 /* Gradient wrt the MLP's INPUTS from the dA tiles nb_mlp_bwd_tc left behind (pose estimation:
  * demo_est_rel_pose.py:87-97 backpropagates through frozen weights to the sample positions and view

@@ -39,6 +39,7 @@ SIGNATURES = {
     "nb_last_error": (C.c_char_p, []),
     "nb_init": (i32, [i32]),
     "nb_shutdown": (i32, []),
+    "nb_set_launch_limits": (i32, [i32, i32]),
     "nb_launch_count": (i64, []),
     "nb_get_rays_fwd": (i32, [i32, i32, f32, f32, f32, f32, vp, i32, vp, vp, vp, vp]),
     "nb_get_rays_sel_fwd": (i32, [i32, i32, f32, f32, f32, f32, vp, i32, vp, i64, vp, vp, vp, vp]),
@@ -71,6 +72,7 @@ SIGNATURES = {
     "nb_mlp_pack_bwd": (i32, [C.POINTER(NbMlpWeights), vp, vp]),
     "nb_mlp_da_bytes": (i64, [i64]),
     "nb_mlp_bwd_tc": (i32, [vp, i32, i32, vp, vp, i64, vp, C.POINTER(i64), vp, vp]),
+    "nb_mlp_bwd_tc_parts": (i32, [vp, i32, i32, vp, vp, i64, vp, C.POINTER(i64), vp, i32, vp]),
     "nb_mlp_ingrad_packed_bytes": (i64, [i32, i32]),
     "nb_mlp_pack_ingrad": (i32, [C.POINTER(NbMlpWeights), vp, vp]),
     "nb_mlp_bwd_inputs": (i32, [vp, i32, i32, vp, vp, vp, i64, i32, vp, vp, vp]),

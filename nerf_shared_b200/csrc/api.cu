@@ -17,6 +17,10 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static thread_local int g_limit_mlp_clusters = 0, g_limit_wgrad_ctas = 0;
+int limit_mlp_clusters() { return g_limit_mlp_clusters; }
+int limit_wgrad_ctas() { return g_limit_wgrad_ctas; }
+
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 int check_launch(const char* what) {
@@ -75,5 +79,15 @@ int nb_init(int device) {
 }
 
 int nb_shutdown(void) { return 0; }
+
+int nb_set_launch_limits(int mlp_clusters, int wgrad_ctas) {
+  if (mlp_clusters < 0 || wgrad_ctas < 0) {
+    nb::set_error("nb_set_launch_limits: negative limit");
+    return NB_E_ARG;
+  }
+  nb::g_limit_mlp_clusters = mlp_clusters;
+  nb::g_limit_wgrad_ctas = wgrad_ctas;
+  return 0;
+}
 
 }  // extern "C"

@@ -17,6 +17,8 @@ namespace nb {
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 int check_launch(const char* what);  // cudaGetLastError -> return code, records message
+int limit_mlp_clusters();            // nb_set_launch_limits (0 = whole GPU)
+int limit_wgrad_ctas();
 
 #define NB_REQUIRE(cond, ...)              \
   do {                                     \

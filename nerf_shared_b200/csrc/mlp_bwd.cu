@@ -849,7 +849,13 @@ int nb_mlp_pack_bwd(const NbMlpWeights* w, void* packed_bwd, void* stream) {
 
 int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
                   void* dA, const int64_t* grad_off_host24, float* grads, void* stream) {
+  return nb_mlp_bwd_tc_parts(packed_bwd, L_pts, L_dirs, acts, d_raw, M, dA, grad_off_host24, grads, 3, stream);
+}
+
+int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
+                        void* dA, const int64_t* grad_off_host24, float* grads, int parts, void* stream) {
   if (M == 0) return 0;
+  NB_REQUIRE(parts >= 1 && parts <= 3, "nb_mlp_bwd_tc_parts: parts must be 1 (dgrad), 2 (wgrad + heads) or 3 (both)");
   NB_REQUIRE(packed_bwd && acts && d_raw && dA, "nb_mlp_bwd_tc: null pointer");
   if (L_pts != 10 || L_dirs != 4) {
     set_error("nb_mlp_bwd_tc: only multires=10 / multires_views=4 is instantiated (got %d, %d)", L_pts, L_dirs);
@@ -860,17 +866,18 @@ int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* act
   const int64_t tiles = (M + kTileM - 1) / kTileM;
   const int64_t quads = (tiles + 3) / 4;
   NB_REQUIRE(quads < (1ll << 30), "nb_mlp_bwd_tc: M too large for one launch");
-  {
+  if (parts & 1) {
     CUtensorMap wmap;
     int rc = make_slab_tmap(&wmap, packed_bwd, kBwdSlabs);
     if (rc) return rc;
-    const int clusters = (int)(quads < kNumSMs / 2 ? quads : kNumSMs / 2);
+    int clusters = (int)(quads < kNumSMs / 2 ? quads : kNumSMs / 2);
+    if (limit_mlp_clusters() > 0 && clusters > limit_mlp_clusters()) clusters = limit_mlp_clusters();
     mlp_dgrad_kernel<<<2 * clusters, kBwdThreads, kBSmemBytes, st>>>(wmap, (const uint8_t*)packed_bwd, (const uint8_t*)acts, d_raw,
                                                              M, (uint8_t*)dA, (int)quads);
     rc = check_launch("mlp_dgrad_kernel");
     if (rc) return rc;
   }
-  if (!grads) return 0;  // frozen weights: only the dA chain was wanted
+  if (!grads || !(parts & 2)) return 0;  // frozen weights / dgrad-only call: only the dA chain was wanted
   NB_REQUIRE(grad_off_host24, "nb_mlp_bwd_tc: gradient offsets missing");
   const int64_t* off = grad_off_host24;  // 0..7 pts_w, 8..15 pts_b, 16 feat_w, 17 feat_b, 18 alpha_w, 19 alpha_b,
                                          // 20 views_w, 21 views_b, 22 rgb_w, 23 rgb_b
@@ -901,8 +908,26 @@ int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const void* act
       if (lim > 0 && lim < grid) grid = lim;
     }
     if (grid < 1) grid = 1;
-    mlp_wgrad_kernel<<<(int)grid, 384, kWSmemBytes, st>>>(jobs, split, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles,
-                                                          grads);
+    if (limit_wgrad_ctas() > 0 && grid > limit_wgrad_ctas()) {
+      // SM-limited launch (a concurrent kernel owns the other SMs): CTAs are placed as pairs so that they fill whole
+      // TPCs and leave the remaining TPCs free for the 2-CTA clusters of the forward / dgrad kernels
+      grid = limit_wgrad_ctas() & ~1;
+      if (grid < 2) grid = 2;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)grid);
+      cfg.blockDim = dim3(384);
+      cfg.dynamicSmemBytes = kWSmemBytes;
+      cfg.stream = st;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at;
+      cfg.numAttrs = 1;
+      cudaLaunchKernelEx(&cfg, mlp_wgrad_kernel, jobs, split, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, grads);
+    } else {
+      mlp_wgrad_kernel<<<(int)grid, 384, kWSmemBytes, st>>>(jobs, split, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles,
+                                                            grads);
+    }
     int rc = check_launch("mlp_wgrad_kernel");
     if (rc) return rc;
   }

@@ -668,7 +668,8 @@ int nb_mlp_fwd_tc(const void* packed, int L_pts, int L_dirs, const float* pts, c
   CUtensorMap wmap;
   int rc = make_slab_tmap(&wmap, packed, kNumSlabs);
   if (rc) return rc;
-  const int clusters = (int)(quads < kNumSMs / 2 ? quads : kNumSMs / 2);
+  int clusters = (int)(quads < kNumSMs / 2 ? quads : kNumSMs / 2);
+  if (limit_mlp_clusters() > 0 && clusters > limit_mlp_clusters()) clusters = limit_mlp_clusters();
   mlp_fwd_tc_kernel<10, 4><<<2 * clusters, kFwdThreads, kSmemBytes, as_stream(stream)>>>(
       wmap, (const uint8_t*)packed, pts, viewdirs, M, S, raw, (uint8_t*)acts, (int)quads);
   return check_launch("nb_mlp_fwd_tc");

@@ -23,7 +23,14 @@ from . import _ops, render_utils, utils
 
 class GraphedTrainStep:
     def __init__(self, renderer, coarse_model, fine_model, optimizer, H, W, K, n_rays, chunk=1024 * 32, group=None,
-                 warmup=2, overlap=None):
+                 warmup=2, overlap=None, mode=None):
+        """mode: "autograd" (default: the step driven through the autograd wrappers, exactly the calls main.py makes),
+        "static" (explicit C-ABI sequence on static buffers with the compositing + loss + compositing-backward fusion,
+        _static.StaticStep), "pipeline" (the static sequence software-pipelined across steps: a call finishes the
+        PREVIOUS batch and starts the coarse pass of the one it is given; flush() finishes the last one).  Measured on
+        B200 (profiles/r2_step_modes.txt): the three are within 4 % of each other -- the step is bound by the SM time of
+        its six tensor-core launches, not by their order -- so the default stays the autograd-driven one.
+        NB_STEP overrides the default."""
         self.renderer, self.coarse, self.fine, self.opt = renderer, coarse_model, fine_model, optimizer
         self.H, self.W, self.K, self.chunk = H, W, K, chunk
         self.group = group
@@ -60,9 +67,30 @@ class GraphedTrainStep:
                 self._n_coarse = n_c
         self.loss = self.psnr = None
         self.launches_per_replay = 0
+        if mode is None and overlap is not None and not overlap:
+            mode = "autograd"                 # the single-stream form exists for the autograd-driven step only
+        mode = mode or os.environ.get("NB_STEP", "autograd")
+        if mode not in ("static", "pipeline", "autograd"):
+            raise ValueError("GraphedTrainStep mode must be static, pipeline or autograd (got %r)" % (mode,))
+        self.static = None
+        if mode != "autograd" and n_rays <= render_utils.MIN_CHUNK:
+            from . import _lib, _static
+            try:
+                self.static = _static.StaticStep(renderer, coarse_model, fine_model, optimizer, H, W, K, n_rays, group=group,
+                                                 pipeline=(mode == "pipeline"))
+            except _lib.NerfB200Error:
+                if mode == "pipeline":
+                    raise
+                self.static = None            # configurations outside the explicit sequence run through autograd
+        self.mode = "autograd" if self.static is None else mode
+        if self.static is not None:
+            self.rays, self.target = self.static.inbox.rays, self.static.inbox.target
+            self.overlap = True               # the explicit sequence always runs the coarse backward as a second branch
 
     # main.py:77-104 with the optimizer in graph mode
     def _step(self):
+        if self.static is not None:
+            return self.static.body_pipelined() if self.mode == "pipeline" else self.static.body_sequential()
         if self.overlap:
             return self._step_overlap()
         opt = self.opt
@@ -131,6 +159,8 @@ class GraphedTrainStep:
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream(dev))
             with torch.cuda.stream(side):
+                if self.mode == "pipeline":
+                    self.static.prime()
                 for _ in range(self._warmup):       # allocator / packing caches / lazy init, then undone
                     opt.push_hyper()
                     self._step()
@@ -149,6 +179,8 @@ class GraphedTrainStep:
                 self.loss, self.psnr = self._step()
             self.launches_per_replay = _lib.launch_count() - l0     # libnerf_b200 kernels in the graph
             self.graph = g
+            if self.static is not None:
+                self.static.primed = False          # the warm-up's pending coarse pass used weights that were rolled back
         finally:
             opt.in_graph = False
 
@@ -162,6 +194,14 @@ class GraphedTrainStep:
             self.target.copy_(target, non_blocking=True)
             self._capture()
         dev = self.rays.device
+        if self.mode == "pipeline" and not self.static.primed:
+            # first batch (or first after flush()): only its coarse pass runs; its loss comes out of the next call
+            self.rays.copy_(torch.as_tensor(batch_rays) if not torch.is_tensor(batch_rays) else batch_rays, non_blocking=True)
+            self.target.copy_(target, non_blocking=True)
+            self.static.prime()
+            self.loss.fill_(float("nan"))
+            self.psnr.fill_(float("nan"))
+            return self.loss, self.psnr
         if (torch.is_tensor(batch_rays) and batch_rays.device == dev and batch_rays.dtype == torch.float32
                 and batch_rays.is_contiguous() and target.device == dev and target.dtype == torch.float32
                 and target.is_contiguous()):
@@ -172,4 +212,15 @@ class GraphedTrainStep:
             self.opt.push_hyper()
         self.graph.replay()
         self.opt.bump_versions()
+        return self.loss, self.psnr
+
+    def flush(self):
+        """pipeline mode: finish the step whose coarse pass is pending (the replay's coarse pass for a "next" batch runs
+        on the previous inbox and is discarded).  -> (loss, psnr) of the last batch, or None if nothing is pending."""
+        if self.mode != "pipeline" or self.graph is None or not self.static.primed:
+            return None
+        self.opt.push_hyper()
+        self.graph.replay()
+        self.opt.bump_versions()
+        self.static.primed = False
         return self.loss, self.psnr

@@ -357,3 +357,59 @@ def test_training_loss_curve_follows_the_reference():
         assert i == int(j) and abs(ours - theirs) <= 0.05 * theirs, (i, ours, theirs)
     assert curve[-1][1] < 0.6 * curve[0][1]          # and the loss does fall
     assert np.isfinite(psnr)
+
+
+def _run_mode(mode, rays, targets, lrs, H, W, K, perturb=0.0):
+    from nerf_shared_b200 import render_utils, train, utils
+
+    class A:
+        lrate = 5e-4
+    mc, mf = make_model(11), make_model(12)
+    r = render_utils.Renderer(perturb=perturb, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                              raw_noise_std=0.0, near=2.0, far=6.0)
+    r.train()
+    opt = utils.get_optimizer(mc, mf, A())
+    step = train.GraphedTrainStep(r, mc, mf, opt, H, W, K, rays.shape[1], mode=mode)
+    assert step.mode == mode
+    losses = []
+    # the pipelined step reads the lr of the call that FINISHES a batch (call j finishes batch j-1)
+    call_lrs = [lrs[0]] + lrs[:-1] if mode == "pipeline" else lrs
+    for tgt, lr in zip(targets, call_lrs):
+        for pg in opt.param_groups:
+            pg["lr"] = lr
+        loss, psnr = step(rays, tgt)
+        losses.append((float(loss), float(psnr)))
+    if mode == "pipeline":
+        for pg in opt.param_groups:
+            pg["lr"] = lrs[-1]
+        out = step.flush()
+        losses.append((float(out[0]), float(out[1])))
+    torch.cuda.synchronize()
+    return losses, opt.flat_p.clone(), opt._step, step.launches_per_replay
+
+
+def test_static_and_pipelined_steps_match_the_autograd_step(golden):
+    """The explicit C-ABI step (composite_train fusion) and its software-pipelined form (coarse pass of batch k+1 beside
+    the fine weight gradients of batch k) against the autograd-driven graph on the same batches: same losses, same
+    parameters after every update (deterministic sampling).  In pipeline mode the loss of batch k is returned by call
+    k+1 (the first call returns NaN) and flush() finishes the last batch."""
+    H = W = 8
+    K = O.blender_intrinsics(H, W)
+    rb = cuda(golden["rr/ray_batch"])
+    rays = torch.stack([rb[:, 0:3], rb[:, 3:6]], 0).contiguous()
+    g = torch.Generator().manual_seed(3)
+    targets = [torch.rand(rays.shape[1], 3, generator=g).cuda() for _ in range(5)]
+    lrs = [5e-4, 4e-4, 3e-4, 2e-4, 1e-4]
+    la, pa, sa, na = _run_mode("autograd", rays, targets, lrs, H, W, K)
+    ls, ps, ss, ns = _run_mode("static", rays, targets, lrs, H, W, K)
+    lp, pp, sp, np_ = _run_mode("pipeline", rays, targets, lrs, H, W, K)
+    print("launches per replay: autograd %d, static %d, pipeline %d" % (na, ns, np_))
+    assert sa == ss == sp == 5
+    assert np.isnan(lp[0][0]) and len(lp) == 6
+    for (a, pa_), (b, pb) in zip(la, ls):
+        assert abs(a - b) <= 1e-4 * abs(a) and abs(pa_ - pb) <= 1e-3, (la, ls)
+    for (a, pa_), (b, pb) in zip(la, lp[1:]):
+        assert abs(a - b) <= 1e-4 * abs(a) and abs(pa_ - pb) <= 1e-3, (la, lp)
+    for other in (ps, pp):
+        assert float((other - pa).abs().max()) <= 2.5e-3 and float((other - pa).abs().mean()) <= 2e-5
+    assert ns < na

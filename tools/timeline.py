@@ -38,11 +38,11 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     torch.cuda.synchronize()
 evs = [e for e in prof.events() if e.device_type == torch.autograd.DeviceType.CUDA]
 evs.sort(key=lambda e: e.time_range.start)
-adam = [i for i, e in enumerate(evs) if "adam_dev" in e.name]
-if len(adam) >= 2:
-    evs = evs[adam[-2] + 1:adam[-1] + 1]
+marks = [i for i, e in enumerate(evs) if "step_prologue" in e.name]      # one per call, in front of the replay
+if len(marks) >= 2:
+    evs = evs[marks[-2]:marks[-1]]
 t0 = evs[0].time_range.start
-print("# one replay of the %d-ray step: start us, duration us, stream, kernel (overlap=%s)" % (n_rays, step.overlap))
+print("# one replay of the %d-ray step: start us, duration us, stream, kernel (mode=%s)" % (n_rays, step.mode))
 for e in evs:
     print("%9.1f %8.1f  s%-3s %s" % (e.time_range.start - t0, e.time_range.end - e.time_range.start,
                                     getattr(e, "device_resource_id", "?"), e.name[:90]))
