@@ -37,19 +37,35 @@ def packed_ingrad(model) -> torch.Tensor:
     return buf
 
 
-def nerf_mlp_backward(ctx, g_raw):
-    model, S = ctx.model, ctx.S
-    pts, viewdirs, acts = ctx.saved_tensors
+def prepare_inplace(model, need_param):
+    """In-place gradient target (FlatAdam): parameters whose .grad was cleared since the last backward (model.zero_grad(),
+    p.grad = None -- torch's set_to_none default) get their slice of the flat buffer zeroed and the view re-attached, so
+    that the weight-gradient kernels start from fresh gradients and the optimizer sees the result.  -> True if the model
+    has an in-place target."""
+    target = model.__dict__.get("_nb_grad_target")
+    if target is None:
+        return False
+    grads, offs = target
+    for i, p in enumerate(_ops.mlp_params(model)):
+        if p.grad is None and need_param[i]:
+            view = grads[offs[i]:offs[i] + p.numel()].view_as(p)
+            view.zero_()
+            p.grad = view
+    return True
+
+
+def mlp_backward(model, pts, viewdirs, acts, S, g_raw, need_in, need_param, packed_bwd=None):
+    """The MLP's backward kernels for one forward call: -> (d_pts, d_viewdirs, [24 parameter gradients]).
+    need_param[i]: whether parameter i (in _ops.mlp_params order) wants a gradient.  With a FlatAdam optimizer
+    registered on the model the weight-gradient kernels accumulate in place and the list holds None."""
     lib = _ops._lib_for(pts)
     M = pts.shape[0]
     params = _ops.mlp_params(model)
-    need_in = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
-    need_w = any(ctx.needs_input_grad[5:])
-    none5 = (None, None, None, None, None)
+    need_w = any(need_param)
     if not (need_w or need_in):
-        return none5 + (None,) * len(params)
+        return None, None, [None] * len(params)
     dev = pts.device
-    grads, offs, in_place = None, [0] * 24, False
+    grads, offs, in_place, cleared = None, [0] * 24, False, []
     if need_w:
         # a FlatAdam optimizer registers its flat gradient buffer on the model: the wgrad kernels then
         # accumulate in place (every p.grad is a view of that buffer) and autograd gets no tensors
@@ -60,15 +76,15 @@ def nerf_mlp_backward(ctx, g_raw):
             # model.zero_grad() / p.grad = None since the last backward (set_to_none is torch's default): the user
             # asked for fresh gradients, so clear this model's slices before accumulating into them, and hand the
             # views back afterwards -- otherwise p.grad stays None and the optimizer would discard the result
-            cleared = [i for i, p in enumerate(params) if p.grad is None and ctx.needs_input_grad[5 + i]]
-            if cleared:
-                for i in cleared:
-                    grads[offs[i]:offs[i] + params[i].numel()].zero_()
+            cleared = [i for i, p in enumerate(params) if p.grad is None and need_param[i]]
+            for i in cleared:
+                grads[offs[i]:offs[i] + params[i].numel()].zero_()
         else:
             offs, total = grad_layout(model)
             grads = torch.zeros((total,), device=dev, dtype=torch.float32)
     dA = torch.empty((int(lib.nb_mlp_da_bytes(M)),), device=dev, dtype=torch.uint8)
-    packed_bwd = _ops.packed_weights(model, backward=True)
+    if packed_bwd is None:               # (a CUDA-graph caller packs into its own buffer inside the capture)
+        packed_bwd = _ops.packed_weights(model, backward=True)
     off_arr = (C.c_int64 * 24)(*offs)
     g = f32c(g_raw).view(-1, 4)
     L, Lv = int(model.multires), int(model.multires_views)
@@ -82,13 +98,19 @@ def nerf_mlp_backward(ctx, g_raw):
             d_vd = torch.zeros((M // S, 3), device=dev, dtype=torch.float32)
             check(lib.nb_mlp_bwd_inputs(ptr(packed_ingrad(model)), L, Lv, ptr(dA), ptr(pts), ptr(viewdirs), M, S,
                                         ptr(d_pts), ptr(d_vd), stream_ptr()), "nb_mlp_bwd_inputs")
-    if need_w and in_place:
-        for i in cleared:
-            params[i].grad = grads[offs[i]:offs[i] + params[i].numel()].view_as(params[i])
+    for i in cleared:
+        params[i].grad = grads[offs[i]:offs[i] + params[i].numel()].view_as(params[i])
     out = []
     for i, p in enumerate(params):
-        use = need_w and ctx.needs_input_grad[5 + i] and not in_place
+        use = need_w and need_param[i] and not in_place
         out.append(grads[offs[i]:offs[i] + p.numel()].view_as(p) if use else None)
-    ctx.model._nb_last_dA = dA if getattr(ctx.model, "_nb_keep_dA", False) else None
+    model._nb_last_dA = dA if getattr(model, "_nb_keep_dA", False) else None
+    return d_pts, d_vd, out
+
+
+def nerf_mlp_backward(ctx, g_raw):
+    pts, viewdirs, acts = ctx.saved_tensors
+    d_pts, d_vd, out = mlp_backward(ctx.model, pts, viewdirs, acts, ctx.S, g_raw,
+                                    ctx.needs_input_grad[0] or ctx.needs_input_grad[1], list(ctx.needs_input_grad[5:]))
     return (d_pts if ctx.needs_input_grad[0] else None, d_vd if ctx.needs_input_grad[1] else None, None, None,
             None) + tuple(out)

@@ -326,16 +326,22 @@ def packed_weights(model, backward: bool = False) -> torch.Tensor:
     transposed slabs of the dgrad chain), re-packed whenever a parameter changed (its autograd
     version counter or storage moved)."""
     params = mlp_params(model)
-    for p in params:
-        if p.dtype != torch.float32 or not p.is_contiguous():
-            raise _lib.NerfB200Error("NeRF parameters must be contiguous fp32 tensors")
     dev = params[0].device
-    lib = _lib_for(params[0])
-    key = tuple((p.data_ptr(), p._version) for p in params)
+    # Staleness key, evaluated on every forward / backward: version counters only grow, so their sum changes whenever
+    # any parameter is written in place (optimizer step, load_state_dict, `p += ...` under no_grad); the storage of the
+    # first and the last parameter catches a re-homing of the parameters (FlatAdam moves them into its flat buffer).
+    v = 0
+    for p in params:
+        v += p._version
+    key = (v, params[0].data_ptr(), params[23].data_ptr())
     slot = "_nb_packed_bwd" if backward else "_nb_packed"
     cache = model.__dict__.get(slot)
     if cache is not None and cache[0] == key and cache[1].device == dev:
         return cache[1]
+    for p in params:
+        if p.dtype != torch.float32 or not p.is_contiguous():
+            raise _lib.NerfB200Error("NeRF parameters must be contiguous fp32 tensors")
+    lib = _lib_for(params[0])
     size_fn = lib.nb_mlp_bwd_packed_bytes if backward else lib.nb_mlp_packed_bytes
     nbytes = int(size_fn(int(model.multires), int(model.multires_views)))
     buf = cache[1] if (cache is not None and cache[1].device == dev and cache[1].numel() == nbytes) else \

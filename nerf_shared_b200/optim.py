@@ -49,6 +49,7 @@ class FlatAdam(torch.optim.Optimizer):
                 self.flat_p[o:o + n].copy_(p.detach().reshape(-1))
                 p.data = self.flat_p[o:o + n].view(p.shape)
                 p.grad = self.flat_g[o:o + n].view(p.shape)
+        self._views = [p.grad for p in ps]          # identity check in _grads_are_flat (48 `is` tests, no data_ptr calls)
         self._by_id = {id(p): o for p, o in zip(ps, self._offsets)}
 
     # the weight-gradient kernels look this up to accumulate in place (see _bwd.py)
@@ -56,10 +57,11 @@ class FlatAdam(torch.optim.Optimizer):
         return self._by_id.get(id(p))
 
     def _grads_are_flat(self):
-        for p, o in zip(self._params, self._offsets):
-            g = p.grad
-            if g is None or g.data_ptr() != self.flat_g.data_ptr() + 4 * o:
-                return False
+        for p, v in zip(self._params, self._views):
+            if p.grad is not v:
+                g = p.grad                         # (a re-attached view of the same slice is as good)
+                if g is None or g.data_ptr() != v.data_ptr() or g.shape != v.shape:
+                    return False
         return True
 
     def zero_grad(self, set_to_none: bool = False):
@@ -81,6 +83,7 @@ class FlatAdam(torch.optim.Optimizer):
                 elif p.grad.data_ptr() != view.data_ptr():
                     view.copy_(p.grad)
                 p.grad = view
+            self._views = [p.grad for p in self._params]
 
     def grad_view(self, p):
         """The slice of the flat gradient buffer that is `p.grad` (None for foreign parameters)."""

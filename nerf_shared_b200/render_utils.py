@@ -12,7 +12,7 @@ import os
 import numpy as np
 import torch
 
-from . import _ops
+from . import _fused, _ops
 from . import nerf   # noqa: F401  (the reference module exposes it; demos star-import this file)
 from . import utils
 
@@ -161,6 +161,17 @@ class Renderer(torch.nn.Module):
                 rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
             rays_o = rays_o.reshape(-1, 3).float().contiguous()
             rays_d = rays_d.reshape(-1, 3).float().contiguous()
+            if self._after_coarse is None and _fused.eligible(self, coarse_model, fine_model, rays_o, rays_d, rays_d.shape[0],
+                                                              max(int(chunk), MIN_CHUNK)):
+                # training batch: the whole coarse + fine render as one autograd node (_fused.py)
+                out = _fused.FusedRender.apply(self, coarse_model, fine_model, rays_o, rays_d, view_src.float().contiguous(),
+                                               *_ops.mlp_params(coarse_model), *_ops.mlp_params(fine_model))
+                rgb, disp, acc, rgb0, disp0, acc0, z_std, raw = out
+                shp = lambda t: t.reshape(out_shape + list(t.shape[1:]))
+                extras = {"rgb0": shp(rgb0), "disp0": shp(disp0), "acc0": shp(acc0), "z_std": shp(z_std)}
+                if retraw:
+                    extras["raw"] = shp(raw)
+                return [shp(rgb), shp(disp), shp(acc), extras]
             ray_rows, viewdirs = _ops.ray_rows(rays_o, rays_d, view_src, self.near, self.far)
             parts = (rays_o, rays_d, viewdirs)
 

@@ -155,6 +155,8 @@ class GraphedTrainStep:
         keep = [t.clone() for t in (opt.flat_p, opt.exp_avg, opt.exp_avg_sq)]
         step0 = opt._step
         opt.in_graph = True
+        from . import _fused
+        lazy, _fused.GRAPHS_ENABLED = _fused.GRAPHS_ENABLED, False      # no nested captures inside this one's warm-up
         try:
             side = torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream(dev))
@@ -183,6 +185,7 @@ class GraphedTrainStep:
                 self.static.primed = False          # the warm-up's pending coarse pass used weights that were rolled back
         finally:
             opt.in_graph = False
+            _fused.GRAPHS_ENABLED = lazy
 
     def __call__(self, batch_rays, target):
         shp = tuple(torch.as_tensor(batch_rays).shape) if not torch.is_tensor(batch_rays) else tuple(batch_rays.shape)

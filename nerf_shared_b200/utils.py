@@ -19,8 +19,25 @@ device = torch.device("cuda" if torch.cuda.is_available() else "cpu")
 DEBUG = False
 
 # ----------------------------------------------------------------------------- misc (utils.py:24-30)
-img2mse = lambda x, y: torch.mean((x - y) ** 2)
-mse2psnr = lambda x: -10. * torch.log(x) / torch.log(torch.tensor([10.], device=x.device))
+def img2mse(x, y):
+    """mean((x - y)^2) (utils.py:24).  Two fp32 CUDA tensors of one shape take one launch forward and one backward
+    (nb_mse_pair_*) instead of three elementwise kernels and their autograd nodes each way."""
+    if (torch.is_tensor(x) and torch.is_tensor(y) and x.is_cuda and y.is_cuda and x.dtype == torch.float32
+            and y.dtype == torch.float32 and x.shape == y.shape and 0 < x.numel() <= (1 << 18) and not y.requires_grad):   # (one-block kernel: batches, not whole frames)
+        return _ops.MsePair.apply(x, None, y)[1]
+    return torch.mean((x - y) ** 2)
+
+
+_NEG10_OVER_LN10 = -10.0 / float(np.log(10.0))
+
+
+def mse2psnr(x):
+    """-10 log10(x) (utils.py:27), shaped [1] for a scalar like the reference's division by a 1-element tensor; the
+    constant is a Python float (the reference builds a tensor from a list on every call: a host-to-device copy)."""
+    r = torch.log(x) * _NEG10_OVER_LN10
+    return r.reshape(1) if r.dim() == 0 else r
+
+
 to8b = lambda x: (255 * np.clip(x, 0, 1)).astype(np.uint8)
 
 

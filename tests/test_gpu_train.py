@@ -413,3 +413,164 @@ def test_static_and_pipelined_steps_match_the_autograd_step(golden):
     for other in (ps, pp):
         assert float((other - pa).abs().max()) <= 2.5e-3 and float((other - pa).abs().mean()) <= 2e-5
     assert ns < na
+
+
+def test_fused_render_node_equals_per_stage_path(golden):
+    """Renderer.render on a training batch takes the single-node path (_fused.FusedRender); with the hook that disables
+    it the per-stage autograd wrappers run.  Same outputs bit for bit, same gradients up to atomics order -- with
+    torch.optim.Adam (gradients returned to autograd) and with the flat optimizer (accumulated in place), including
+    model.zero_grad(set_to_none=True) between steps."""
+    from nerf_shared_b200 import _fused, render_utils, utils
+    H = W = 8
+    K = O.blender_intrinsics(H, W)
+    rb = cuda(golden["rr/ray_batch"])
+    rays = torch.stack([rb[:, 0:3], rb[:, 3:6]], 0).contiguous()
+    tgt = torch.rand(rays.shape[1], 3, generator=torch.Generator().manual_seed(9)).cuda()
+
+    def run(fused, flat):
+        mc, mf = make_model(13, scale=1.59), make_model(14, scale=1.59)
+        r = render_utils.Renderer(perturb=1.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                                  raw_noise_std=1.0, near=2.0, far=6.0)
+        r.train()
+        if not fused:
+            r._after_coarse = lambda rgb0, tensors: None          # any hook routes render() to the per-stage wrappers
+        params = list(mc.parameters()) + list(mf.parameters())
+        if flat:
+            class A:
+                lrate = 5e-4
+            opt = utils.get_optimizer(mc, mf, A())
+        else:
+            opt = torch.optim.Adam(params, lr=5e-4)
+        outs = []
+        for it in range(2):
+            torch.manual_seed(100 + it)
+            torch.cuda.manual_seed(100 + it)
+            rgb, disp, acc, extras = r.render_from_rays(H, W, K, chunk=32768, rays=rays, coarse_model=mc, fine_model=mf, retraw=True)
+            assert set(extras) == {"raw", "rgb0", "disp0", "acc0", "z_std"}
+            if it == 0:
+                opt.zero_grad()
+            else:
+                mc.zero_grad(set_to_none=True)
+                mf.zero_grad(set_to_none=True)
+            loss = utils.img2mse(rgb, tgt) + utils.img2mse(extras["rgb0"], tgt) + 0.1 * acc.mean() + 0.05 * extras["raw"][..., 3].mean()
+            loss.backward()
+            g = torch.cat([p.grad.reshape(-1) for p in params]).clone()
+            opt.step()
+            outs.append((rgb.detach().clone(), extras["raw"].detach().clone(), extras["z_std"].clone(), g, float(loss)))
+        return outs
+
+    ref = run(False, False)
+    for fused, flat in ((True, False), (True, True), (False, True)):
+        got = run(fused, flat)
+        for it, ((a_rgb, a_raw, a_zs, a_g, a_l), (b_rgb, b_raw, b_zs, b_g, b_l)) in enumerate(zip(ref, got)):
+            if it == 0:       # same weights, same draws: the same kernels produce the same bits
+                assert torch.equal(a_rgb, b_rgb) and torch.equal(a_raw, b_raw) and torch.equal(a_zs, b_zs), (fused, flat)
+                assert abs(a_l - b_l) <= 1e-6 * abs(a_l)
+                assert float((a_g - b_g).abs().max()) <= 2e-5 * float(a_g.abs().max()), (fused, flat)
+            else:             # after one Adam step on gradients that differ in their last bits (atomics order)
+                assert maxabs(a_rgb, b_rgb) <= 2e-3 and abs(a_l - b_l) <= 1e-3 * abs(a_l), (fused, flat)
+                assert float((a_g - b_g).norm() / a_g.norm()) <= 2e-2, (fused, flat)
+            assert float(a_g.abs().max()) > 0
+
+
+def test_main_py_loop_runs_on_lazily_captured_graphs():
+    """With utils.get_optimizer's flat optimizer the unchanged main.py loop replays a forward and a backward CUDA graph
+    (_fused._Graphs): same parameters after 6 steps as with the capture disabled, p.grad = None between steps honoured,
+    a second forward before the first backward falls back to the uncaptured path."""
+    import os
+    from nerf_shared_b200 import render_utils, utils
+    H = W = 32
+    K = O.blender_intrinsics(H, W)
+    c2w = cuda(O.pose_spherical(20.0, -30.0, 4.0))[:3, :4]
+    pix = torch.from_numpy(np.random.default_rng(3).choice(H * W, 512, replace=False)).cuda()
+    ro, rd = utils.get_rays_at(H, W, K, c2w, pix)
+    rays = torch.stack([ro, rd], 0)
+    tgts = [torch.rand(512, 3, generator=torch.Generator().manual_seed(40 + i)).cuda() for i in range(6)]
+
+    def run(graph):
+        os.environ["NB_EAGER_GRAPH"] = "1" if graph else "0"
+        try:
+            class A:
+                lrate = 5e-4
+            mc, mf = make_model(13, scale=1.59), make_model(14, scale=1.59)
+            opt = utils.get_optimizer(mc, mf, A())
+            r = render_utils.Renderer(perturb=0.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                                      raw_noise_std=0.0, near=2.0, far=6.0)
+            r.train()
+            losses = []
+            for i, tgt in enumerate(tgts):
+                rgb, _, _, extras = r.render_from_rays(H, W, K, chunk=32768, rays=rays, coarse_model=mc, fine_model=mf, retraw=True)
+                if i == 3:                                   # torch's default way of clearing gradients
+                    mc.zero_grad(set_to_none=True)
+                    mf.zero_grad(set_to_none=True)
+                else:
+                    opt.zero_grad()
+                loss = utils.img2mse(rgb, tgt) + utils.img2mse(extras["rgb0"], tgt)
+                loss.backward()
+                opt.step()
+                losses.append(float(loss))
+            used = len(r.__dict__.get("_nb_graphs", {}))
+            # two forwards, then two backwards (gradient accumulation): the second forward must not clobber the first
+            opt.zero_grad()
+            a = r.render_from_rays(H, W, K, chunk=32768, rays=rays, coarse_model=mc, fine_model=mf, retraw=True)
+            b = r.render_from_rays(H, W, K, chunk=32768, rays=rays, coarse_model=mc, fine_model=mf, retraw=True)
+            (utils.img2mse(a[0], tgts[0]) + utils.img2mse(a[3]["rgb0"], tgts[0])).backward()
+            (utils.img2mse(b[0], tgts[1]) + utils.img2mse(b[3]["rgb0"], tgts[1])).backward()
+            g2 = opt.flat_g.clone()
+            torch.cuda.synchronize()
+            return losses, opt.flat_p.clone(), g2, used
+        finally:
+            os.environ.pop("NB_EAGER_GRAPH", None)
+
+    l0, p0, g0, used0 = run(False)
+    l1, p1, g1, used1 = run(True)
+    assert used0 == 0 and used1 == 1
+    for a, b in zip(l0, l1):
+        assert abs(a - b) <= 1e-4 * abs(a), (l0, l1)
+    assert float((p1 - p0).abs().max()) <= 2.5e-3 and float((p1 - p0).abs().mean()) <= 2e-5
+    assert float((g1 - g0).norm() / g0.norm()) <= 2e-2 and float(g0.abs().max()) > 0
+
+
+def test_lazily_captured_graphs_draw_fresh_random_numbers():
+    """perturb = 1 and raw_noise_std > 0 through the captured forward graph: every replay must draw NEW stratified
+    offsets / noise (graph-safe Philox offsets), and with the generator re-seeded before a step the replayed graph must
+    reproduce the uncaptured path's draws for that step."""
+    import os
+    from nerf_shared_b200 import render_utils, utils
+    H = W = 16
+    K = O.blender_intrinsics(H, W)
+    c2w = cuda(O.pose_spherical(20.0, -30.0, 4.0))[:3, :4]
+    pix = torch.arange(256).cuda()
+    ro, rd = utils.get_rays_at(H, W, K, c2w, pix)
+    rays = torch.stack([ro, rd], 0)
+    tgt = torch.rand(256, 3, generator=torch.Generator().manual_seed(1)).cuda()
+
+    def run(graph, reseed):
+        os.environ["NB_EAGER_GRAPH"] = "1" if graph else "0"
+        try:
+            class A:
+                lrate = 0.0                      # frozen trajectory: only the draws change from step to step
+            mc, mf = make_model(13, scale=1.59), make_model(14, scale=1.59)
+            opt = utils.get_optimizer(mc, mf, A())
+            r = render_utils.Renderer(perturb=1.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                                      raw_noise_std=1.0, near=2.0, far=6.0)
+            r.train()
+            out = []
+            for i in range(5):
+                if reseed:
+                    torch.cuda.manual_seed(777)
+                rgb, _, _, extras = r.render_from_rays(H, W, K, chunk=32768, rays=rays, coarse_model=mc, fine_model=mf, retraw=True)
+                opt.zero_grad()
+                loss = utils.img2mse(rgb, tgt) + utils.img2mse(extras["rgb0"], tgt)
+                loss.backward()
+                opt.step()
+                out.append(float(loss))
+            return out
+        finally:
+            os.environ.pop("NB_EAGER_GRAPH", None)
+
+    fresh = run(True, False)
+    assert len(set(fresh[1:])) == len(fresh[1:]), fresh            # different draws on every replay
+    same_g, same_e = run(True, True), run(False, True)
+    assert max(abs(a - same_g[2]) for a in same_g[2:]) <= 1e-6, same_g          # same seed -> same draws, replay after replay
+    assert abs(same_g[3] - same_e[3]) <= 1e-5 * abs(same_e[3]), (same_g, same_e)   # and the uncaptured path's draws
