@@ -46,8 +46,9 @@ def parse():
     ap.add_argument("--rays", type=int, default=1024, help="N_rand per GPU (weak scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-render", action="store_true")
-    ap.add_argument("--large-rays", type=int, default=8192,
-                    help="rays per GPU of the large-batch leg (configs[2]: 65,536 rays/step over 8 GPUs); 0 = skip")
+    ap.add_argument("--no-sustained", action="store_true")
+    ap.add_argument("--large-rays", type=int, default=65536,
+                    help="global batch of the configs[2] leg (65,536 rays per step, sharded over the GPUs); 0 = skip")
     return ap.parse_args()
 
 
@@ -57,6 +58,13 @@ def peaks():
         d = json.load(open(p))
         return d.get("bf16_tflops", 1590.0), d.get("bf16_tflops_sustained", 1400.0), d.get("hbm_gbs", 6650.0), "measured"
     return 1590.0, 1400.0, 6650.0, "fallback"
+
+
+def workload_config(rays, world):
+    """`config` of the JSON line, identical for the B200 arm and the reference arm."""
+    return {"workload": "lego-shaped synthetic Blender training step (BASELINE.json configs[1]): N_rand=%d rays/GPU, "
+                        "64 coarse + 128 fine samples, D8 W256 coarse+fine fwd/bwd + Adam" % rays,
+            "global_rays_per_step": world * rays, "parallelism": "dp%d (ray-sharded, flat-gradient all-reduce)" % world}
 
 
 class ClockSampler:
@@ -114,23 +122,24 @@ class Args:  # the subset of config_parser flags the API helpers read (configs/l
     precrop_iters, precrop_frac, chunk = 0, 0.5, 32768
 
 
-def large_batch_leg(a, args, renderer, coarse, fine, opt, K, poses_d, images, dev, world, flush, steps=5):
-    """BASELINE.json configs[2]: 65,536 rays per step ray-sharded over the GPUs of one box.  Each rank trains
-    `--large-rays` rays per step (8,192 = the share of one of 8 GPUs; device-resident batches, same graphed step,
-    gradient all-reduce inside the graph).  At this size the MLP kernels run ~40 waves, so the wave quantisation of
-    the 1,024-ray step is gone and the figure shows the per-GPU rate the kernels sustain."""
+def large_batch_leg(a, args, renderer, coarse, fine, opt, K, poses_d, images, dev, world, flush, steps=3):
+    """BASELINE.json configs[2] as written: ONE optimizer step on a fixed global batch of 65,536 rays, ray-sharded over the
+    GPUs of the box (strong scaling: 65,536 / N rays per GPU).  The saved activations of a whole shard do not fit in HBM
+    at N <= 2 (168 GB at 65,536 rays), so every rank accumulates the gradient over chunks of 8,192 rays
+    (train.ChunkedBatchStep: main.py's calls per chunk, one all-reduce + Adam per step)."""
     import torch.distributed as dist
     from nerf_shared_b200 import train, utils
-    n = int(a.large_rays)
-    step = train.GraphedTrainStep(renderer, coarse, fine, opt, H, W, K, n, chunk=args.chunk)
-    pool = []
-    for i in range(2):
-        pix = torch.from_numpy(np.random.choice(H * W, n, replace=False)).to(dev)
-        ro, rd = utils.get_rays_at(H, W, K, poses_d[i % N_IMAGES, :3, :4], pix)
-        tgt = torch.from_numpy(images[i % N_IMAGES].reshape(-1, 3)[pix.cpu().numpy()]).to(dev)
-        pool.append((torch.stack([ro, rd], 0), tgt))
-    for i in range(3):
-        step(*pool[i % 2])
+    total = int(a.large_rays)
+    if total % world != 0:
+        return None
+    n = total // world
+    step = train.ChunkedBatchStep(renderer, coarse, fine, opt, H, W, K, chunk_rays=min(8192, n))
+    pix = torch.from_numpy(np.random.choice(H * W, n, replace=False)).to(dev)
+    ro, rd = utils.get_rays_at(H, W, K, poses_d[0, :3, :4], pix)
+    tgt = torch.from_numpy(images[0].reshape(-1, 3)[pix.cpu().numpy()]).to(dev)
+    rays = torch.stack([ro, rd], 0)
+    for _ in range(2):
+        step(rays, tgt)
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -138,26 +147,26 @@ def large_batch_leg(a, args, renderer, coarse, fine, opt, K, poses_d, images, de
     for i in range(steps):
         flush.zero_()
         ev[i][0].record()
-        loss, _ = step(*pool[i % 2])
+        loss = step(rays, tgt)
         ev[i][1].record()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     assert np.isfinite(float(loss))
-    ms = sum(s.elapsed_time(e) for s, e in ev) / steps
+    ms = sum(s_.elapsed_time(e) for s_, e in ev) / steps
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     samples = n * (args.N_samples + args.N_samples + args.N_importance)
-    step.graph = None                      # releases the graph's private pool (and its NCCL capture) now
-    del step
+    renderer.__dict__.pop("_nb_graphs", None)        # release the chunk-sized graphs
     import gc
     gc.collect()
     torch.cuda.empty_cache()
-    return {"workload": "training step, %d rays/GPU x %d GPU(s) = %d rays/step (configs[2] is 65,536 rays/step)" % (n, world, n * world),
-            "rays_per_s": world * n / (ms * 1e-3), "ms_per_step": ms, "steps": steps,
-            "mlp_train_tflops_per_gpu": samples * 3489024 / (ms * 1e-3) / 1e12}
+    return {"workload": "BASELINE.json configs[2]: one training step on a fixed global batch of %d rays, %d rays per GPU on %d GPU(s), "
+                        "gradient accumulated over %d-ray chunks, one all-reduce + Adam" % (total, n, world, min(8192, n)),
+            "scaling": "strong", "rays_per_s": total / (ms * 1e-3), "ms_per_step": ms, "steps": steps,
+            "mlp_train_tflops_per_gpu": samples * FLOP_TRAIN / (ms * 1e-3) / 1e12}
 
 
 def run_b200(a):
@@ -255,6 +264,34 @@ def run_b200(a):
     ms_step = float(t.item())
     value = world * a.rays / (ms_step * 1e-3)
 
+    # ---- sustained leg: the rate a 200k-iteration run lives at (power-capped clocks), not the 26 ms burst above -------
+    # >= 2 s of back-to-back steps (no flush: a step streams ~5 GB, 40x the L2), per-step CUDA events, median
+    sustained = None
+    if not a.no_sustained:
+        n_sus = max(200, int(2.5 / (ms_step * 1e-3)))
+        sampler2 = ClockSampler(local)
+        if rank == 0:
+            sampler2.start()
+        for i in range(50):
+            step(*pool[i % n_pool])
+        sync_all()
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(n_sus + 1)]
+        t0 = time.perf_counter()
+        evs[0].record()
+        for i in range(n_sus):
+            step(*pool[i % n_pool])
+            evs[i + 1].record()
+        sync_all()
+        wall = time.perf_counter() - t0
+        per = np.array([evs[i].elapsed_time(evs[i + 1]) for i in range(n_sus)])
+        t = torch.tensor([float(np.median(per)), float(per.mean())], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        med, mean = float(t[0].item()), float(t[1].item())
+        sustained = {"steps": n_sus, "seconds": wall, "ms_per_step_median": med, "ms_per_step_mean": mean,
+                     "rays_per_s": world * a.rays / (med * 1e-3), "clocks": sampler2.stop() if rank == 0 else None,
+                     "mlp_tflops_per_gpu": a.rays * (S_COARSE + S_FINE) * FLOP_TRAIN / (med * 1e-3) / 1e12}
+
     # ---- end to end through the public API (e2e) -----------------------------------------------
     # host images (pinned) -> utils.sample_random_ray_batch (pixel ids + targets H2D) -> graphed step ->
     # loss.item() (D2H) every step
@@ -299,31 +336,45 @@ def run_b200(a):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    e2e_ms = time_e2e(step)
+    graph_ms = time_e2e(step)
     eager_ms = time_e2e(eager_step)
     h2d = a.rays * 8 + a.rays * 3 * 4      # int64 pixel ids + fp32 targets per step
-    e2e = {"value": world * a.rays / (e2e_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-           "ms_per_step": e2e_ms, "api": "utils.sample_random_ray_batch -> train.GraphedTrainStep -> loss D2H (pinned, read one step later)",
-           "eager_main_py_loop": {"value": world * a.rays / (eager_ms * 1e-3), "ms_per_step": eager_ms}}
+    # The headline e2e is the loop the reference's main.py executes, call by call through the reference API
+    # (utils.sample_random_ray_batch -> Renderer.render_from_rays -> utils.img2mse x2 -> backward -> optimizer.step);
+    # train.GraphedTrainStep (not a reference API: the whole step as one CUDA graph) is reported beside it.
+    e2e = {"value": world * a.rays / (eager_ms * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+           "ms_per_step": eager_ms,
+           "api": "main.py:72-104 unchanged: utils.sample_random_ray_batch (host pixel sampling, pinned H2D) -> render_from_rays -> "
+                  "img2mse x2 -> loss.backward() -> optimizer.step() -> loss D2H (pinned, read one step later)",
+           "graphed_step": {"value": world * a.rays / (graph_ms * 1e-3), "ms_per_step": graph_ms,
+                            "api": "utils.sample_random_ray_batch -> train.GraphedTrainStep -> loss D2H"}}
 
+    cfg = workload_config(a.rays, world)          # identical in the reference arm (the driver compares the two)
+    how = {"l2": "256 MiB flush between timed iterations", "timing": "CUDA events per step, max over ranks",
+           "launch": "one CUDA graph per step (train.GraphedTrainStep, mode %s%s)" % (
+               step.mode, ", coarse backward captured as a parallel branch beside the fine pass" if step.overlap else "")}
     out = {"metric": "train_rays_per_s", "value": value, "unit": "rays/s", "n_gpus": world, "steps": a.steps,
            "warmup": max(a.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
-           "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-           "config": {"workload": "lego-shaped synthetic Blender training step (BASELINE.json configs[1]): N_rand=%d rays/GPU, "
-                                  "64 coarse + 128 fine samples, D8 W256 coarse+fine fwd/bwd + Adam" % a.rays,
-                      "global_rays_per_step": world * a.rays, "parallelism": "dp%d (ray-sharded, flat-gradient all-reduce)" % world,
-                      "l2": "256 MiB flush between timed iterations", "timing": "CUDA events per step, max over ranks",
-                      "launch": "one CUDA graph per step (train.GraphedTrainStep%s)" % (
-                          ", coarse backward captured as a parallel branch beside the fine pass" if step.overlap else "")},
-           "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+           "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": cfg,
+           "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "measurement": how}
+    if sustained is not None:
+        out["sustained"] = sustained
 
     large = None if (a.no_render or a.large_rays <= 0) else large_batch_leg(a, args, renderer, coarse, fine, opt, K, poses_d,
                                                                              images, dev, world, flush)
     if large is not None:
         out["large_batch"] = large
+        out["e2e"]["configs2_strong_scaling"] = large         # BASELINE.json configs[2] as written, in a driver-parsed field
     render = None if a.no_render else render_leg(renderer, coarse, fine, K, poses_d, dev, world)   # all ranks (row-sharded)
     if rank == 0:
         out.update(kernel_breakdown(a, coarse, fine, pool[0], dev))
+        burst, sus_peak, _, _ = peaks()
+        step_flop = a.rays * (S_COARSE + S_FINE) * FLOP_TRAIN
+        out["roofline"]["step"] = {"algorithmic_tflop": step_flop / 1e12, "tflops": step_flop / (ms_step * 1e-3) / 1e12,
+                                   "frac_of_burst_peak": step_flop / (ms_step * 1e-3) / 1e12 / burst,
+                                   "frac_of_sustained_peak": step_flop / (ms_step * 1e-3) / 1e12 / sus_peak,
+                                   "sustained_leg_frac_of_sustained_peak": (None if sustained is None else
+                                                                            sustained["mlp_tflops_per_gpu"] / sus_peak)}
         if render is not None:
             out["render"] = render
         if world == 1 and not a.no_render:
@@ -332,7 +383,7 @@ def run_b200(a):
             import bench_stream
             out["stream_kernels"] = bench_stream.run(quiet=True)
         if not a.no_cpu_baseline and world == 1:     # the CPU baseline is reported at N=1 only
-            out["cpu_baseline"] = cpu_train_baseline(budget_s=15.0)
+            out["cpu_baseline"] = cpu_train_baseline()
         print(json.dumps(out), file=_real_stdout, flush=True)
     # teardown: a CUDA graph that captured NCCL kernels must be released before its communicator;
     # if anything in the teardown still blocks, dump the stacks and leave (the result is already printed)
@@ -394,32 +445,36 @@ def kernel_breakdown(a, coarse, fine, batch, dev):
     t_inf = timed(lambda: _ops.mlp_forward_tc(fine, pts_i, vd_i, S_FINE, save_acts=False), reps=5)
     del pts_i, vd_i
     dgrad_flop = FLOP_FWD - 2 * (63 * 256 * 2 + 27 * 128 + 256 + 384)
-    # algorithmic bytes per sample: saved activations 40 slabs, dA 38 slabs of 128 B per row
-    act_b, da_b, mask_b = 40 * 128 + 288, 38 * 128, 288   # + relu' bit masks (9 groups x 8 words per row)
+    # design traffic per sample (NOT the algorithmic 20 B/sample of SURVEY 8d): saved activations 40 slabs,
+    # dA 38 slabs of 128 B per row, relu' bit masks 288 B
+    act_b, da_b, mask_b = 40 * 128 + 288, 38 * 128, 288
     kern = {
         "mlp_fwd_tc(fine, saves activations)": (t_fwd, FLOP_FWD * M, (12 + 16 + act_b) * M),
         "mlp_dgrad(fine)": (t_dgrad, dgrad_flop * M, (16 + mask_b + da_b) * M),
-        "mlp_wgrad+small(fine)": (t_wgrad, FLOP_FWD * M, (40 * 128 + da_b + 768 + 16) * M),
+        "mlp_wgrad+heads(fine)": (t_wgrad, FLOP_FWD * M, (40 * 128 + da_b + 768 + 16) * M),
         "mlp_fwd_tc(inference 32768x192)": (t_inf, FLOP_FWD * Mi, 28 * Mi),
     }
     traffic = ncu_traffic()
     per = {}
     for k, (t, fl, by) in kern.items():
         tf, gb = fl / t / 1e9, by / t / 1e6
-        per[k] = {"ms": round(t, 4), "tflops": round(tf, 1), "frac_tensor": round(tf / burst, 3), "algorithmic_GBps": round(gb, 1),
-                  "frac_hbm": round(gb / hbm, 3), "algorithmic_bytes": int(by)}
+        per[k] = {"ms": round(t, 4), "algorithmic_flop": int(fl), "tflops": round(tf, 1), "frac_tensor_burst": round(tf / burst, 3),
+                  "design_traffic_bytes": int(by), "design_traffic_GBps": round(gb, 1), "design_traffic_frac_hbm": round(gb / hbm, 3)}
+    # The path is tensor-bound by its algorithm (the MLP is the only dense contraction, its algorithmic
+    # HBM I/O is 20 B/sample): the roofline of the dominant kernel is ALGORITHMIC FLOP / launch time / measured bf16 peak.
     train_k = [k for k in kern if "inference" not in k]
     top = max(train_k, key=lambda k: kern[k][0])
     t, fl, by = kern[top]
-    tens, mem = fl / t / 1e9 / burst, by / t / 1e6 / hbm
-    if mem >= tens:   # the roofline that binds is the one the kernel sits closer to
-        roof = {"bound": "hbm", "kernel": top, "achieved": by / t / 1e6, "peak": hbm, "unit": "GB/s", "frac": mem,
-                "peak_source": src + " copy bandwidth"}
-    else:
-        roof = {"bound": "tensor", "kernel": top, "achieved": fl / t / 1e9, "peak": burst, "unit": "TFLOP/s", "frac": tens,
-                "peak_source": src + " bf16 burst (kernel timed alone)"}
+    roof = {"bound": "tensor", "kernel": top, "achieved": fl / t / 1e9, "peak": burst, "unit": "TFLOP/s", "frac": fl / t / 1e9 / burst,
+            "peak_source": src + " bf16 burst (kernel timed alone, CUDA events on the launching stream)",
+            "algorithmic_flop_per_launch": int(fl), "launch_ms": t}
     roof["traffic"] = traffic.get(top.split("(")[0].split("+")[0] + "_kernel")
     roof["traffic_source"] = "profiles/ (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch)" if roof["traffic"] else None
+    roof["algorithmic_bytes_per_launch"] = int(20 * M)
+    # secondary view: why the kernel sits where it does -- the DESIGN moves saved activations and activation gradients
+    # through HBM, and that traffic (not the algorithm's) is what the weight-gradient kernel is limited by
+    roof["hbm_design_traffic"] = {"bytes_per_launch": int(by), "GBps": by / t / 1e6, "frac_of_copy_peak": by / t / 1e6 / hbm,
+                                  "peak": hbm, "note": "design traffic (saved bf16 activations + activation gradients), not algorithmic bytes"}
     roof["per_kernel"] = per
     roof["mlp_tensor_pipe"] = {"kernel": "mlp_fwd_tc(inference 32768x192)", "tflops": per["mlp_fwd_tc(inference 32768x192)"]["tflops"],
                                "frac_of_burst_peak": round(FLOP_FWD * Mi / t_inf / 1e9 / burst, 3),
@@ -506,6 +561,38 @@ def render_leg(renderer, coarse, fine, K, poses_d, dev, world=1):
         done[(n2 - 1) & 1].synchronize()
         checksum += int(host[(n2 - 1) & 1][400, 400, 0])
         e2e_ms = (time.perf_counter() - t0) * 1e3 / n2
+        extra = {}
+        if world == 1:
+            # configs[0] on the GPU: the 400x400 view the CPU arm renders (bench.py --impl reference, configs0_frame)
+            K4 = datasets.synthetic_blender(400, 400, 1)[3]
+            for _ in range(2):
+                renderer.render_from_pose(400, 400, K4, 32768, poses_d[0, :3, :4], coarse, fine, retraw=False)
+            torch.cuda.synchronize()
+            f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            f0.record()
+            for i in range(4):
+                renderer.render_from_pose(400, 400, K4, 32768, poses_d[i % N_IMAGES, :3, :4], coarse, fine, retraw=False)
+            f1.record()
+            torch.cuda.synchronize()
+            ms4 = f0.elapsed_time(f1) / 4
+            extra["configs0_400x400"] = {"ms_per_frame": ms4, "fps": 1e3 / ms4, "rays_per_s": 160000 / (ms4 * 1e-3)}
+            # the product API with its asynchronous frame tail: Renderer.render_from_batch_poses writes PNG files
+            # (render_utils.py:293-319); frame i's D2H + PNG encode overlap frame i+1's kernels
+            import shutil
+            import tempfile
+            tmp = tempfile.mkdtemp(prefix="nb_frames_")
+            try:
+                batch = poses_d[:6, :3, :4]
+                renderer.render_from_batch_poses(800, 800, K8, 32768, batch[:1], coarse, fine, False, tmp)
+                torch.cuda.synchronize()
+                tb = time.perf_counter()
+                renderer.render_from_batch_poses(800, 800, K8, 32768, batch, coarse, fine, False, tmp)
+                torch.cuda.synchronize()
+                msb = (time.perf_counter() - tb) * 1e3 / batch.shape[0]
+                extra["render_from_batch_poses_800x800_png"] = {"ms_per_frame": msb, "fps": 1e3 / msb, "frames": int(batch.shape[0]),
+                                                                 "what": "wall clock incl. uint8 conversion, pinned D2H and PNG encoding of every frame"}
+            finally:
+                shutil.rmtree(tmp, ignore_errors=True)
     renderer.perturb = perturb
     t = torch.tensor([e0.elapsed_time(e1) / n, e2e_ms], device=dev, dtype=torch.float64)
     if world > 1:
@@ -516,7 +603,8 @@ def render_leg(renderer, coarse, fine, K, poses_d, dev, world=1):
     return {"workload": "800x800 Blender render, 64+128 samples, rows split over %d GPU(s)" % world, "fps": 1e3 / ms,
             "ms_per_frame": ms, "mlp_tflops": tf, "frac_of_sustained_peak": tf / (sustained * world),
             "e2e": {"fps": 1e3 / e2e_ms, "ms_per_frame": e2e_ms, "h2d_bytes_per_frame": 64, "d2h_bytes_per_frame": 800 * 800 * 3,
-                    "api": "host pose -> dist.render_sharded -> utils.to8b_device -> pinned uint8 frame (wall clock)"}}
+                    "api": "host pose -> dist.render_sharded -> utils.to8b_device -> pinned uint8 frame (wall clock)"},
+            **extra}
 
 
 def pose_leg(dev, n_rays=512, steps=20):
@@ -607,31 +695,64 @@ def cpu_step_fn():
     return step
 
 
-def pick_rays(step, total_steps, budget_s):
-    probe = step(32)                                    # warm-up + calibration (time ~ linear in rays)
-    n = int(32 * budget_s / max(total_steps * probe, 1e-6))
-    n = max(32, min(1024, n))
-    return 1 << int(np.log2(n))
+CPU_SAMPLE_RAYS = 256      # fixed: the CPU arm times this many rays of the 1,024-ray step (rays/s is batch-flat on the CPU)
 
 
-def cpu_train_baseline(budget_s=15.0):
+def cpu_train_baseline():
     step = cpu_step_fn()
-    n = pick_rays(step, 3, budget_s)
+    n = CPU_SAMPLE_RAYS
+    step(n)                                             # discarded: thread pool / allocator warm-up
     best = min(step(n) for _ in range(3))
     return {"value": n / best, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
-            "sample": "%d-ray training step (coarse+fine fwd/bwd + Adam) x3, best; oracle port, torch %s CPU fp32" % (n, torch.__version__),
+            "sample": "%d rays of the 1,024-ray training step (coarse+fine fwd/bwd + Adam), 1 discarded + best of 3; oracle port, "
+                      "torch %s CPU fp32" % (n, torch.__version__),
             "s_per_step": best}
+
+
+def cpu_frame_leg(budget_s=240.0):
+    """BASELINE.json configs[0] / BASELINE.md section 3: the 400 x 400 lego-shaped view (64 + 128 samples, random-init weights,
+    perturb = 0, chunk = 32,768) rendered forward by the reference's CPU path (oracle port), one warm-up chunk and then the
+    frame.  If the warm-up chunk projects the frame beyond `budget_s`, whole chunks are rendered up to the budget and the
+    sample is stated."""
+    from oracle import nerf_oracle as O
+    torch.set_num_threads(os.cpu_count() or 1)
+    pc, pf = O.make_params(11), O.make_params(12)
+    K = O.blender_intrinsics(H, W)
+    c2w = torch.from_numpy(O.pose_spherical(40.0, -30.0, 4.0))[:3, :4]
+    ro, rd = O.get_rays(H, W, K, c2w)
+    vd = O.unit_viewdirs(rd)
+    ro, rd = ro.reshape(-1, 3).float(), rd.reshape(-1, 3).float()
+    chunk, n = 32768, H * W
+
+    def render(b, e):
+        with torch.no_grad():
+            return O.render_rays(pc, pf, ro[b:e], rd[b:e], vd[b:e], 2.0, 6.0)["rgb_map"]
+
+    t0 = time.perf_counter()
+    render(0, chunk)                                    # warm-up chunk (BASELINE.md section 3)
+    warm = time.perf_counter() - t0
+    n_chunks = (n + chunk - 1) // chunk
+    do = n_chunks if warm * n_chunks <= budget_s else max(1, int(budget_s / warm))
+    t0 = time.perf_counter()
+    done = 0
+    for c in range(do):
+        done += render(c * chunk, min((c + 1) * chunk, n)).shape[0]
+    dt = time.perf_counter() - t0
+    return {"workload": "BASELINE.json configs[0]: 400x400 lego-shaped view, 64+128 samples, forward render on the host cores",
+            "rays_per_s": done / dt, "s_per_frame": dt * n / done, "rays_timed": done, "full_frame": done == n,
+            "cores": torch.get_num_threads(), "kind": "port", "torch": torch.__version__}
 
 
 def run_reference(a):
     """--impl reference: the reference's own CPU implementation of the step (oracle port) timed on
-    the host cores; rank 0 only.  Every step is a bounded sample (n rays) of the 1024-ray step."""
+    the host cores; rank 0 only.  Every step is a bounded sample (256 rays) of the 1024-ray step."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     world = int(os.environ.get("WORLD_SIZE", "1"))
     step = cpu_step_fn()
-    n = pick_rays(step, a.steps + a.warmup, 150.0)
+    n = CPU_SAMPLE_RAYS
+    step(n)                                             # discarded (cold thread pool)
     for _ in range(a.warmup):
         step(n)
     t0 = time.perf_counter()
@@ -639,14 +760,16 @@ def run_reference(a):
         step(n)
     per = (time.perf_counter() - t0) / a.steps
     v = n / per
-    sample = "%d rays per step x %d steps; oracle port of main.py:72-112, torch %s CPU fp32" % (n, a.steps, torch.__version__)
+    sample = "%d rays of the 1,024-ray step per timed step x %d steps (1 discarded + %d warm-up); oracle port of main.py:72-112, torch %s CPU fp32" % (
+        n, a.steps, a.warmup, torch.__version__)
     out = {"impl": "reference", "metric": "train_rays_per_s", "value": v, "unit": "rays/s", "n_gpus": world, "steps": a.steps,
            "warmup": a.warmup, "ms_per_step": per * 1e3, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": "lego-shaped synthetic Blender training step (BASELINE.json configs[1]), N_rand=1024; "
-                                  "timed on a bounded sample of %d rays per step" % n},
+           "config": workload_config(a.rays, world),
            "cpu_baseline": {"kind": "port", "cores": torch.get_num_threads(), "sample": sample, "value": v, "unit": "rays/s"},
            "e2e": {"value": v, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if world == 1 and os.environ.get("NB_REF_FRAME", "1") != "0":
+        out["configs0_frame"] = cpu_frame_leg()
     print(json.dumps(out), file=_real_stdout, flush=True)
 
 

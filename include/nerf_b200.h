@@ -246,10 +246,8 @@ NB_API int nb_debug_umma(const float* A, const float* B, int K, float* D, void* 
 /* D[128,128] = A[K,128]^T * B[K,128] with both operands MN-major (the wgrad operand mode); K in {64,128}. */
 NB_API int nb_debug_umma_mn(const float* A, const float* B, int K, float* D, void* stream);
 
-/* Micro-benchmark: `iters` back-to-back tcgen05.mma on `ctas` SMs with the kernels' operand layouts;
- * cycles[2*i] = SM cycles until the last MMA retired, cycles[2*i+1] = cycles spent issuing.  mode: see
- * csrc/umma_rate.cu.  Used by tools/umma_rate.py to calibrate the tensor-pipe ceiling of this part. */
-NB_API int nb_debug_umma_rate(int mode, int iters, int ctas, long long* cycles, void* stream);
+/* (The tensor-pipe micro-benchmark nb_debug_umma_rate lives in csrc/umma_rate.cu and is NOT part of the default build:
+ * `make EXTRA_SRCS=umma_rate.cu`; tools/umma_rate.py declares its prototype itself.) */
 
 #ifdef __cplusplus
 }

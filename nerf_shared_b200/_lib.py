@@ -82,7 +82,6 @@ SIGNATURES = {
     "nb_train_step_prologue": (i32, [vp, f32, f32, f32, f32, i32, f32, vp, vp, i64, vp, vp, i64, vp]),
     "nb_adam_step_dev": (i32, [vp, vp, vp, vp, i64, vp, vp]),
     "nb_debug_umma": (i32, [vp, vp, i32, vp, vp]),
-    "nb_debug_umma_rate": (i32, [i32, i32, i32, vp, vp]),
 }
 
 
@@ -107,8 +106,33 @@ def load():
             fn = getattr(lib, name)
             fn.restype = res
             fn.argtypes = args
-        _lib = lib
+        _lib = _NvtxLib(lib) if os.environ.get("NB_NVTX", "0") not in ("0", "") else lib
     return _lib
+
+
+class _NvtxLib:
+    """NB_NVTX=1: every C-ABI call is bracketed by an NVTX range named after the entry point, so that nsys / ncu
+    timelines show the library's calls (ranges are pushed on the calling thread, around the asynchronous launch)."""
+
+    def __init__(self, lib):
+        self._lib = lib
+        self._cache = {}
+
+    def __getattr__(self, name):
+        fn = self._cache.get(name)
+        if fn is None:
+            raw = getattr(self._lib, name)
+            if name in ("nb_last_error", "nb_launch_count", "nb_version"):
+                fn = raw
+            else:
+                def fn(*a, _raw=raw, _name=name):
+                    torch.cuda.nvtx.range_push(_name)
+                    try:
+                        return _raw(*a)
+                    finally:
+                        torch.cuda.nvtx.range_pop()
+            self._cache[name] = fn
+        return fn
 
 
 def last_error() -> str:

@@ -137,7 +137,8 @@ using namespace nb;
 extern "C" {
 
 // cycles: 2 int64 per CTA (pair): [total incl. drain, issue only]
-int nb_debug_umma_rate(int mode, int iters, int ctas, long long* cycles, void* stream) {
+// opt-in symbol (not in include/nerf_b200.h): exported explicitly
+__attribute__((visibility("default"))) int nb_debug_umma_rate(int mode, int iters, int ctas, long long* cycles, void* stream) {
   NB_REQUIRE(cycles && iters > 0 && mode >= 0 && mode <= 9 && ctas >= 1 && ctas <= kNumSMs, "nb_debug_umma_rate: bad arguments");
   cudaError_t e;
   if (mode == 0 || mode == 2 || mode >= 4) {

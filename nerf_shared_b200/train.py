@@ -227,3 +227,44 @@ class GraphedTrainStep:
         self.opt.bump_versions()
         self.static.primed = False
         return self.loss, self.psnr
+
+
+class ChunkedBatchStep:
+    """One optimizer step on a ray batch too large to keep its saved activations resident (BASELINE.json configs[2]:
+    65,536 rays per step are 16.8 M samples x 10 KB of bf16 activations + activation gradients = 168 GB): the batch is
+    cut into chunks of `chunk_rays`, every chunk runs main.py:77-103 (render_from_rays -> the two MSE terms -> backward)
+    with its loss weighted by its share of the batch, the weight gradients accumulate in the flat buffer, and ONE
+    all-reduce + Adam step follows -- the gradient of the mean loss over the whole (global) batch.  The chunks replay
+    the lazily captured graphs of _fused.py, so a chunk costs two graph launches.
+
+        step = ChunkedBatchStep(renderer, coarse, fine, optimizer, H, W, K, chunk_rays=8192)
+        loss = step(batch_rays, target)           # batch_rays [2, n, 3], target [n, 3]: this rank's shard
+    """
+
+    def __init__(self, renderer, coarse_model, fine_model, optimizer, H, W, K, chunk_rays=8192, group=None):
+        self.renderer, self.coarse, self.fine, self.opt = renderer, coarse_model, fine_model, optimizer
+        self.H, self.W, self.K, self.chunk_rays, self.group = H, W, K, int(chunk_rays), group
+        self.world = torch.distributed.get_world_size(group) if (
+            torch.distributed.is_available() and torch.distributed.is_initialized()) else 1
+        if self.world > 1:
+            optimizer.grad_scale = 1.0 / self.world
+
+    def __call__(self, batch_rays, target):
+        from . import utils
+        n = batch_rays.shape[1]
+        opt = self.opt
+        opt.zero_grad()
+        total = None
+        for b in range(0, n, self.chunk_rays):
+            e = min(b + self.chunk_rays, n)
+            rays = batch_rays[:, b:e].contiguous()
+            tgt = target[b:e].contiguous()
+            rgb, _, _, extras = self.renderer.render_from_rays(self.H, self.W, self.K, chunk=self.chunk_rays, rays=rays,
+                                                               coarse_model=self.coarse, fine_model=self.fine, retraw=False)
+            loss = (utils.img2mse(rgb, tgt) + utils.img2mse(extras["rgb0"], tgt)) * ((e - b) / n)
+            loss.backward()
+            total = loss.detach() if total is None else total + loss.detach()
+        if self.world > 1:
+            torch.distributed.all_reduce(opt.flat_g, group=self.group)
+        opt.step()
+        return total

@@ -2,7 +2,10 @@
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from nerf_shared_b200 import _lib
-lib = _lib.load(); _lib.ensure_device("cuda:0")
+lib = _lib.load()
+import ctypes as _C
+lib.nb_debug_umma_rate.restype = _C.c_int   # opt-in symbol: make -C nerf_shared_b200/csrc EXTRA_SRCS=umma_rate.cu
+lib.nb_debug_umma_rate.argtypes = [_C.c_int, _C.c_int, _C.c_int, _C.c_void_p, _C.c_void_p]; _lib.ensure_device("cuda:0")
 for mode, nw in ((8, 4), (9, 1)):
     iters = 256
     cyc = torch.zeros(2 * 148, dtype=torch.int64, device="cuda")

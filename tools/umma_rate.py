@@ -2,7 +2,10 @@
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from nerf_shared_b200 import _lib
-lib = _lib.load(); _lib.ensure_device("cuda:0")
+lib = _lib.load()
+import ctypes as _C
+lib.nb_debug_umma_rate.restype = _C.c_int   # opt-in symbol: make -C nerf_shared_b200/csrc EXTRA_SRCS=umma_rate.cu
+lib.nb_debug_umma_rate.argtypes = [_C.c_int, _C.c_int, _C.c_int, _C.c_void_p, _C.c_void_p]; _lib.ensure_device("cuda:0")
 names = {5: "cg2 ring3 commit-wait", 6: "cg2 ring1 commit-wait", 7: "cg2 ring3 via producer", 0: "cg2 M256 N256", 1: "cg1 M128 N256", 2: "cg2 M256 N128", 3: "cg1 M128 N128", 4: "cg2 M256 N256 commit/4"}
 for ctas in (2, 148):
     for mode in (0, 4, 5, 6, 7):
