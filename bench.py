@@ -660,12 +660,41 @@ def pose_leg(dev, n_rays=512, steps=20):
     gn = float(pose.grad.norm())            # D2H read of the result
     ms = (time.perf_counter() - t0) * 1e3 / steps
     assert np.isfinite(gn) and np.isfinite(float(loss))
+
+    # the same step as one CUDA graph (train.GraphedPoseStep): rays of the 512 selected pixels only, render with frozen
+    # weights, MSE, backward to the pose; per step the host copies (pose, pixel ids, targets) into the static inputs,
+    # replays, and applies a gradient step to the pose (the demo's optimizer acts on a 7-parameter twist instead)
+    from nerf_shared_b200 import train
+    gstep = train.GraphedPoseStep(r, mc, mf, Hf, Wf, Kf, n_rays)
+    cur = pose0.clone()
+    cur4 = torch.eye(4, device=dev)
+
+    def gstep_once():
+        pix = torch.randint(0, Hf * Wf, (n_rays,), generator=g).to(dev, non_blocking=True)
+        cur4[:3] = cur
+        loss_g, grad = gstep(cur4, pix, target[pix])
+        cur.sub_(1e-4 * grad[:3])
+        return loss_g
+
+    for _ in range(5):
+        gstep_once()
+    torch.cuda.synchronize()
+    gsteps = 100
+    t0 = time.perf_counter()
+    for _ in range(gsteps):
+        loss_g = gstep_once()
+    lg = float(loss_g)                      # D2H read of the result
+    gms = (time.perf_counter() - t0) * 1e3 / gsteps
+    assert np.isfinite(lg)
     return {"workload": "fern-shaped LLFF NDC scene 504x378, 64+64 samples (configs[4])",
             "render_fps": 1e3 / frame_ms, "render_ms_per_frame": frame_ms,
             "render_mlp_tflops": Hf * Wf * (64 + 128) * FLOP_FWD / frame_ms / 1e9,
-            "pose_step": {"rays": n_rays, "ms_per_step": ms, "steps_per_s": 1e3 / ms,
-                          "what": "get_rays(full grid, pose requires grad) -> 512-pixel batch -> render (frozen weights) -> "
-                                  "MSE -> backward to the 3x4 pose; eager, wall clock incl. the host"}}
+            "pose_step": {"rays": n_rays, "ms_per_step": gms, "steps_per_s": 1e3 / gms, "launches_per_replay": gstep.launches_per_replay,
+                          "what": "train.GraphedPoseStep: get_rays_at(512 pixels, pose requires grad) -> render (frozen weights) -> "
+                                  "MSE -> backward to the pose as one CUDA graph + a gradient step on the pose; wall clock incl. the host",
+                          "unchanged_demo_loop": {"ms_per_step": ms, "steps_per_s": 1e3 / ms,
+                                                  "what": "demo_est_rel_pose.py:80-97 call by call: get_rays(full 504x378 grid, pose requires "
+                                                          "grad) -> 512-pixel batch -> render -> img2mse -> backward; eager, wall clock"}}}
 
 
 def cpu_step_fn():

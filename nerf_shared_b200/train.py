@@ -268,3 +268,68 @@ class ChunkedBatchStep:
             torch.distributed.all_reduce(opt.flat_g, group=self.group)
         opt.step()
         return total
+
+
+class GraphedPoseStep:
+    """The pose-estimation step of examples/relative_pose_estimation_demo/demo_est_rel_pose.py:80-97 as ONE CUDA graph:
+    rays of the selected pixels from a pose that requires grad (utils.get_rays_at: only those pixels, not the H x W grid
+    the demo builds and differentiates) -> Renderer.render_from_rays with frozen networks -> img2mse -> backward to the
+    pose.  Captured through the same public objects the demo uses; a call copies (pose, pixel ids, target colours) into
+    the static inputs and replays.
+
+        step = train.GraphedPoseStep(renderer, coarse, fine, H, W, K, n_rays=512)
+        pose = cam_transf(start_pose)                       # any differentiable parametrisation of the 4x4 pose
+        loss, grad_pose = step(pose.detach(), pix, target)  # device tensors, overwritten by the next call
+        pose.backward(grad_pose)                            # chain rule into the parametrisation; optimizer.step()
+    """
+
+    def __init__(self, renderer, coarse_model, fine_model, H, W, K, n_rays, chunk=1024 * 32, warmup=2):
+        self.renderer, self.coarse, self.fine = renderer, coarse_model, fine_model
+        self.H, self.W, self.K, self.chunk = H, W, K, chunk
+        dev = next(coarse_model.parameters()).device
+        self.pose = torch.eye(4, device=dev, dtype=torch.float32).requires_grad_(True)
+        self.pix = torch.zeros(n_rays, device=dev, dtype=torch.int64)
+        self.target = torch.zeros((n_rays, 3), device=dev, dtype=torch.float32)
+        self.graph, self.loss, self.grad = None, None, None
+        self._warmup = warmup
+        self.launches_per_replay = 0
+
+    def _step(self):
+        self.pose.grad = None
+        rays_o, rays_d = utils.get_rays_at(self.H, self.W, self.K, self.pose, self.pix)
+        rgb = self.renderer.render_from_rays(self.H, self.W, self.K, chunk=self.chunk, rays=torch.stack([rays_o, rays_d], 0),
+                                             coarse_model=self.coarse, fine_model=self.fine, retraw=True)[0]
+        loss = utils.img2mse(rgb, self.target)
+        loss.backward()
+        return loss.detach(), self.pose.grad
+
+    def _capture(self):
+        from . import _lib
+        dev = self.pose.device
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(self._warmup):
+                self._step()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        g = torch.cuda.CUDAGraph()
+        l0 = _lib.launch_count()
+        with torch.cuda.graph(g):
+            self.loss, self.grad = self._step()
+        self.launches_per_replay = _lib.launch_count() - l0
+        self.graph = g
+
+    def __call__(self, pose, pix, target):
+        with torch.no_grad():
+            p = torch.as_tensor(pose, dtype=torch.float32)
+            if tuple(p.shape) == (3, 4):
+                self.pose[:3].copy_(p, non_blocking=True)
+            else:
+                self.pose.copy_(p, non_blocking=True)
+            self.pix.copy_(torch.as_tensor(pix), non_blocking=True)
+            self.target.copy_(target, non_blocking=True)
+        if self.graph is None:
+            self._capture()
+        self.graph.replay()
+        return self.loss, self.grad

@@ -177,3 +177,36 @@ def test_pose_adam_steps_reduce_loss():
     print("pose optimisation losses:", ["%.3e" % l for l in losses])
     # a random-init field is bumpy at the scale of the offset: require progress, not convergence
     assert min(losses[3:]) < 0.8 * losses[0], losses
+
+
+def test_graphed_pose_step_equals_the_eager_step():
+    """train.GraphedPoseStep (selected-pixel rays -> render with frozen networks -> MSE -> backward to the pose, one CUDA
+    graph) against the demo's eager sequence (demo_est_rel_pose.py:80-97: full-grid get_rays, index, render, img2mse,
+    backward) on a model with a non-zero pose gradient."""
+    from nerf_shared_b200 import render_utils, train, utils
+    from tests.gpu_util import make_model
+    H = W = 24
+    K = O.blender_intrinsics(H, W)
+    mc, mf = make_model(13, scale=1.59), make_model(14, scale=1.59)
+    for p in list(mc.parameters()) + list(mf.parameters()):
+        p.requires_grad_(False)
+    r = render_utils.Renderer(perturb=0.0, N_importance=64, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                              raw_noise_std=0.0, near=2.0, far=6.0)
+    step = train.GraphedPoseStep(r, mc, mf, H, W, K, 128)
+    g = torch.Generator().manual_seed(0)
+    for it in range(3):
+        pose = cuda(O.pose_spherical(30.0 + 5 * it, -30.0, 4.0)).clone().requires_grad_(True)
+        pix = torch.randperm(H * W, generator=g)[:128].cuda()
+        tgt = torch.rand(128, 3, generator=g).cuda()
+        loss_g, grad_g = step(pose.detach(), pix, tgt)
+        loss_g, grad_g = float(loss_g), grad_g.clone()
+        rays_o, rays_d = utils.get_rays(H, W, K, pose)
+        ys, xs = (pix // W).cpu().numpy(), (pix % W).cpu().numpy()
+        rgb = r.render_from_rays(H, W, K, chunk=32768, rays=torch.stack([rays_o[ys, xs], rays_d[ys, xs]], 0), coarse_model=mc,
+                                 fine_model=mf, retraw=True)[0]
+        loss = utils.img2mse(rgb, tgt)
+        loss.backward()
+        assert abs(float(loss) - loss_g) <= 1e-6 * abs(float(loss))
+        assert float(pose.grad.abs().max()) > 1e-3
+        assert float((pose.grad - grad_g).abs().max()) <= 1e-4 * float(pose.grad.abs().max()), (pose.grad, grad_g)
+    assert step.launches_per_replay > 10
