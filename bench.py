@@ -203,7 +203,7 @@ def run_b200(a):
             dist.barrier()
         torch.cuda.synchronize()
 
-    from nerf_shared_b200 import train
+    from nerf_shared_b200 import dist as nd_, train
     step = train.GraphedTrainStep(renderer, coarse, fine, opt, H, W, K, a.rays, chunk=args.chunk)
 
     def eager_step(batch_rays, target):
@@ -214,8 +214,9 @@ def run_b200(a):
         loss = utils.img2mse(rgb, target) + utils.img2mse(extras["rgb0"], target)
         loss.backward()
         if world > 1:
-            dist.all_reduce(opt.flat_g)
-        opt.step()
+            nd_.step_with_allreduce(opt)      # fused all-reduce + Adam over peer memory when available, else NCCL + step
+        else:
+            opt.step()
         return loss
 
     # ---- device-resident batches (value) ------------------------------------------------------

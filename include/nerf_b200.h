@@ -230,14 +230,25 @@ NB_API int nb_adam_step(float* p, const float* g, float* m, float* v, int64_t n,
  * into `hyper` (8 device floats); nb_adam_step_dev (inside the graph) reads them from there.
  * replaces: Adam.step + the per-iteration lr write main.py:104-112. */
 NB_API int nb_adam_hyper(float* hyper, float lr, float beta1, float beta2, float eps, int step, float grad_scale,
-                         void* stream);
+                         int epoch, void* stream);
 /* nb_adam_hyper plus the copy of a training step's two inputs (n1 floats src1 -> dst1: the ray batch; n2 floats
  * src2 -> dst2: the target colours) into the static buffers a captured step graph reads, in ONE launch
  * (train.GraphedTrainStep issues it in front of every replay). */
 NB_API int nb_train_step_prologue(float* hyper, float lr, float beta1, float beta2, float eps, int step, float grad_scale,
-                                  const float* src1, float* dst1, int64_t n1, const float* src2, float* dst2, int64_t n2,
+                                  int epoch, const float* src1, float* dst1, int64_t n1, const float* src2, float* dst2, int64_t n2,
                                   void* stream);
 NB_API int nb_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, const float* hyper, void* stream);
+/* Multi-GPU: the gradient all-reduce fused with the Adam update, one launch per rank over NVLink peer memory
+ * (two-shot all-reduce in place on the ranks' symmetric gradient buffers, then the replicated update; see adam.cu).
+ * peer_grads[world] / peer_flags[world]: HOST arrays of device pointers to every rank's gradient buffer (n floats, n a
+ * multiple of 4, 16-byte aligned) and flag block (32 zero-initialised ints), own rank included, mapped into this
+ * process (torch symmetric memory / CUDA IPC); done_counter: one zero-initialised device uint32 of this rank; hyper as
+ * nb_adam_step_dev, with hyper[6] = `epoch` of nb_adam_hyper / nb_train_step_prologue: a counter that grows by one per call of this
+ * function and never repeats (unlike `step`, which a caller may roll back), identical on all ranks.
+ * Every rank must launch it once per step.  replaces: the dist.all_reduce a data-parallel main.py would add before
+ * optimizer.step() (main.py:103-104) + Adam.step. */
+NB_API int nb_adam_allreduce_p2p(float* p, float* m, float* v, int64_t n, const float* hyper, void* const* peer_grads,
+                                 void* const* peer_flags, int rank, int world, unsigned int* done_counter, void* stream);
 
 /* ---- self test ------------------------------------------------------------------------- */
 /* D[128,128] = A[128,K] * B[128,K]^T (bf16-rounded operands, fp32 accumulate) through the same

@@ -93,6 +93,8 @@ class StaticStep:
         self.side = torch.cuda.Stream(device=dev)
         self.primed = False
         # SM budgets while the next step's coarse pass runs beside the fine weight-gradient kernel (pipeline mode)
+        self.fused_ar = self.world > 1 and group is None and getattr(opt, "p2p", None) is not None \
+            and os.environ.get("NB_FUSED_AR", "1") != "0" and not self.pipeline
         self.lim_wgrad = _env_int("NB_PIPE_WGRAD_CTAS", 104)
         self.lim_fwd = _env_int("NB_PIPE_FWD_CLUSTERS", 22)
         self.wait_for_wgrad = os.environ.get("NB_PIPE_WAIT", "1") != "0"
@@ -224,12 +226,16 @@ class StaticStep:
         with torch.cuda.stream(side):
             self._pack("c", True)
             self._mlp_bwd("c", self.S)
-            self._allreduce(opt.flat_g[:self.n_c])
+            if not self.fused_ar:
+                self._allreduce(opt.flat_g[:self.n_c])
         self._pack("f", True)
         self._mlp_bwd("f", self.F)
         main.wait_stream(side)
-        self._allreduce(opt.flat_g[self.n_c:])
-        self._adam(0, opt.flat_g.numel())
+        if self.fused_ar:
+            opt.step_allreduce()              # all-reduce + Adam: one kernel over NVLink peer memory
+        else:
+            self._allreduce(opt.flat_g[self.n_c:])
+            self._adam(0, opt.flat_g.numel())
         check(self.lib.nb_loss_finalize(ptr(self.acc[0:1]), ptr(self.acc[1:2]), ptr(self.out_f), stream_ptr()), "nb_loss_finalize")
         return self.out_f[2], self.out_f[3]
 

@@ -39,8 +39,9 @@ __global__ void __launch_bounds__(256) adam_dev_kernel(float* __restrict__ p, co
 }
 
 __global__ void adam_hyper_kernel(float* __restrict__ hyper, float step_size, float beta1, float beta2, float eps,
-                                  float inv_sqrt_bc2, float grad_scale) {
+                                  float inv_sqrt_bc2, float grad_scale, int step) {
   hyper[0] = step_size; hyper[1] = beta1; hyper[2] = beta2; hyper[3] = eps; hyper[4] = inv_sqrt_bc2; hyper[5] = grad_scale;
+  hyper[6] = __int_as_float(step);   // epoch of the cross-GPU flags of adam_allreduce_p2p_kernel (never repeats)
 }
 
 }  // namespace nb
@@ -58,11 +59,11 @@ extern "C" int nb_adam_step(float* p, const float* g, float* m, float* v, int64_
 }
 
 extern "C" int nb_adam_hyper(float* hyper, float lr, float beta1, float beta2, float eps, int step, float grad_scale,
-                             void* stream) {
+                             int epoch, void* stream) {
   NB_REQUIRE(hyper && step >= 1, "nb_adam_hyper: bad arguments");
   double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
   adam_hyper_kernel<<<1, 1, 0, as_stream(stream)>>>(hyper, (float)(lr / bc1), beta1, beta2, eps, (float)(1.0 / sqrt(bc2)),
-                                                    grad_scale);
+                                                    grad_scale, epoch);
   return check_launch("nb_adam_hyper");
 }
 
@@ -71,13 +72,14 @@ extern "C" int nb_adam_hyper(float* hyper, float lr, float beta1, float beta2, f
 // between two replays of a 1.3 ms step.
 namespace nb {
 __global__ void __launch_bounds__(256) step_prologue_kernel(float* __restrict__ hyper, float lr_c, float b1, float b2,
-                                                            float eps, float inv_sqrt_bc2, float grad_scale,
+                                                            float eps, float inv_sqrt_bc2, float grad_scale, int step,
                                                             const float* __restrict__ src1, float* __restrict__ dst1,
                                                             int64_t n1, const float* __restrict__ src2,
                                                             float* __restrict__ dst2, int64_t n2) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i == 0) {
     hyper[0] = lr_c; hyper[1] = b1; hyper[2] = b2; hyper[3] = eps; hyper[4] = inv_sqrt_bc2; hyper[5] = grad_scale;
+    hyper[6] = __int_as_float(step);
   }
   if (i < n1) dst1[i] = src1[i];
   else if (i < n1 + n2) dst2[i - n1] = src2[i - n1];
@@ -85,14 +87,14 @@ __global__ void __launch_bounds__(256) step_prologue_kernel(float* __restrict__ 
 }  // namespace nb
 
 extern "C" int nb_train_step_prologue(float* hyper, float lr, float beta1, float beta2, float eps, int step,
-                                      float grad_scale, const float* src1, float* dst1, int64_t n1, const float* src2,
+                                      float grad_scale, int epoch, const float* src1, float* dst1, int64_t n1, const float* src2,
                                       float* dst2, int64_t n2, void* stream) {
   NB_REQUIRE(hyper && step >= 1 && n1 >= 0 && n2 >= 0 && (n1 == 0 || (src1 && dst1)) && (n2 == 0 || (src2 && dst2)),
              "nb_train_step_prologue: bad arguments");
   double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
   const int64_t n = n1 + n2 > 1 ? n1 + n2 : 1;
   nb::step_prologue_kernel<<<(unsigned)((n + 255) / 256), 256, 0, nb::as_stream(stream)>>>(
-      hyper, (float)(lr / bc1), beta1, beta2, eps, (float)(1.0 / sqrt(bc2)), grad_scale, src1, dst1, n1, src2, dst2, n2);
+      hyper, (float)(lr / bc1), beta1, beta2, eps, (float)(1.0 / sqrt(bc2)), grad_scale, epoch, src1, dst1, n1, src2, dst2, n2);
   return nb::check_launch("nb_train_step_prologue");
 }
 
@@ -102,4 +104,124 @@ extern "C" int nb_adam_step_dev(float* p, const float* g, float* m, float* v, in
   NB_REQUIRE(p && g && m && v && hyper, "nb_adam_step_dev: bad arguments");
   adam_dev_kernel<<<grid_for(n, 256), 256, 0, as_stream(stream)>>>(p, g, m, v, n, hyper);
   return check_launch("nb_adam_step_dev");
+}
+
+// ------------------------------------------------------------------------------------------
+// Gradient all-reduce FUSED with the optimizer step, over NVLink peer memory ("one
+// all-reduce of the flat gradient buffer ... fused into the epilogue").  Replaces, for world > 1,
+//     ncclAllReduce(flat_g) ; adam(flat_p, flat_g)        (two launches, the first a 50-60 us NCCL ring at 4.8 MB)
+// by ONE kernel per rank working on the symmetric gradient buffers of all ranks:
+//   barrier A   every rank's weight-gradient kernels have finished (stream order + a flag per peer);
+//   phase 1     two-shot all-reduce: rank r sums slice r of ALL ranks' gradients with coalesced 16-byte peer loads
+//               and writes the reduced slice back into slice r of EVERY rank's buffer (peer stores).  Slice r of any
+//               buffer is read and written by rank r only, so the exchange is race-free in place;
+//   barrier B   all slices have landed everywhere (grid-wide locally, flag per peer across ranks);
+//   phase 2     Adam on the full buffer from the reduced gradient: replicated, bit-identical on every rank.
+// Per rank 2 (W-1)/W x 4.8 MB cross NVLink instead of a ring's latency chain.  Flags carry the step number as epoch
+// (monotonic, hyper[6], identical on all ranks), so nothing has to be reset between steps.  Spins are bounded: a
+// rank that never arrives traps the kernel instead of hanging the GPU.
+// ------------------------------------------------------------------------------------------
+namespace nb {
+
+constexpr int kMaxPeers = 16;
+struct PeerPtrs {
+  float* grad[kMaxPeers];   // every rank's symmetric gradient buffer
+  int* flags[kMaxPeers];    // every rank's flag block: [0..W) = barrier A, [16..16+W) = barrier B
+};
+
+__device__ __forceinline__ void st_release_sys(int* p, int v) {
+  asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_sys(const int* p) {
+  int v;
+  asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// all W flags of `mine` (written by the peers) have reached `epoch`
+__device__ __forceinline__ void wait_flags(const int* mine, int world, int epoch) {
+  if (threadIdx.x < world) {
+    long long spins = 0;
+    while (ld_acquire_sys(mine + threadIdx.x) < epoch) {
+      if (++spins > (1ll << 25)) __trap();   // ~ 10 s: a peer is gone
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(256) adam_allreduce_p2p_kernel(PeerPtrs peers, int rank, int world, float* __restrict__ p,
+                                                                  float* __restrict__ m, float* __restrict__ v, int64_t n,
+                                                                  const float* __restrict__ hyper,
+                                                                  unsigned int* __restrict__ done_counter) {
+  const int epoch = __float_as_int(hyper[6]);
+  int* my_flags = peers.flags[rank];
+  // ---- barrier A: tell every peer that this rank's gradients are complete (they are: this kernel is stream-ordered
+  //      behind the weight-gradient kernels), wait until every peer said so
+  if (blockIdx.x == 0 && threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(peers.flags[threadIdx.x] + rank, epoch);
+  }
+  wait_flags(my_flags, world, epoch);
+
+  // ---- phase 1: reduce slice `rank` over all ranks, write it back to everyone (float4 granularity)
+  const int64_t n4 = n >> 2;                                  // n is padded to a multiple of 4 by the caller
+  const int64_t per = (n4 + world - 1) / world;
+  const int64_t lo = per * rank, hi = (lo + per < n4) ? lo + per : n4;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = lo + tid; i < hi; i += nth) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int q = 0; q < world; ++q) {                         // fixed rank order: the same sum bit for bit on every step
+      const float4 g = reinterpret_cast<const float4*>(peers.grad[q])[i];
+      acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
+    }
+    for (int q = 0; q < world; ++q) reinterpret_cast<float4*>(peers.grad[q])[i] = acc;
+  }
+  // ---- barrier B: this rank's slice is visible everywhere once all its blocks are past the stores
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int arrived = atomicAdd(done_counter, 1u);
+    if (arrived == gridDim.x - 1) {                           // last block of this rank
+      *done_counter = 0u;                                     // (next step)
+      __threadfence_system();
+      for (int q = 0; q < world; ++q) st_release_sys(peers.flags[q] + 16 + rank, epoch);
+    }
+  }
+  wait_flags(my_flags + 16, world, epoch);
+
+  // ---- phase 2: Adam from the reduced gradient (now in this rank's own buffer)
+  const float step_size = hyper[0], beta1 = hyper[1], beta2 = hyper[2], eps = hyper[3], inv_sqrt_bc2 = hyper[4],
+              grad_scale = hyper[5];
+  const float* g = peers.grad[rank];
+  for (int64_t i = tid; i < n; i += nth) {
+    const float gi = __ldcv(g + i) * grad_scale;              // written by peers: bypass stale L1 lines
+    const float mi = beta1 * m[i] + (1.0f - beta1) * gi;
+    const float vi = beta2 * v[i] + (1.0f - beta2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] = p[i] - step_size * (mi / (sqrtf(vi) * inv_sqrt_bc2 + eps));
+  }
+}
+
+}  // namespace nb
+
+extern "C" int nb_adam_allreduce_p2p(float* p, float* m, float* v, int64_t n, const float* hyper, void* const* peer_grads,
+                                     void* const* peer_flags, int rank, int world, unsigned int* done_counter,
+                                     void* stream) {
+  NB_REQUIRE(p && m && v && hyper && peer_grads && peer_flags && done_counter, "nb_adam_allreduce_p2p: null pointer");
+  NB_REQUIRE(world >= 1 && world <= nb::kMaxPeers && rank >= 0 && rank < world, "nb_adam_allreduce_p2p: bad rank / world (max %d ranks)",
+             nb::kMaxPeers);
+  NB_REQUIRE(n > 0 && (n & 3) == 0, "nb_adam_allreduce_p2p: n must be a positive multiple of 4 (pad the flat buffers)");
+  nb::PeerPtrs pp;
+  for (int q = 0; q < nb::kMaxPeers; ++q) {
+    pp.grad[q] = q < world ? (float*)peer_grads[q] : nullptr;
+    pp.flags[q] = q < world ? (int*)peer_flags[q] : nullptr;
+    NB_REQUIRE(q >= world || (pp.grad[q] && pp.flags[q] && ((uintptr_t)pp.grad[q] & 15) == 0),
+               "nb_adam_allreduce_p2p: peer %d: null or unaligned pointer", q);
+  }
+  // one block per SM at most: every block spins on the flags, so all of them have to be resident
+  int grid = (int)((n / 4 + 255) / 256);
+  if (grid > nb::kNumSMs) grid = nb::kNumSMs;
+  nb::adam_allreduce_p2p_kernel<<<grid, 256, 0, nb::as_stream(stream)>>>(pp, rank, world, p, m, v, n, hyper, done_counter);
+  return nb::check_launch("nb_adam_allreduce_p2p");
 }

@@ -69,6 +69,22 @@ def allreduce_gradients(optimizer, group=None):
     return optimizer.flat_g
 
 
+def step_with_allreduce(optimizer, group=None):
+    """Gradient exchange + optimizer step of a data-parallel main.py loop (the line pair a user adds at main.py:103-104).
+    With the optimizer's symmetric gradient buffer (NCCL, default group) this is ONE kernel per rank: two-shot all-reduce
+    over NVLink peer memory fused with Adam (FlatAdam.step_allreduce); otherwise NCCL all-reduce + optimizer.step()."""
+    rank, world = world_info(group)
+    optimizer.grad_scale = 1.0 / world
+    if world > 1 and group is None and getattr(optimizer, "p2p", None) is not None:
+        optimizer.push_hyper()
+        optimizer.step_allreduce()
+        optimizer.bump_versions()
+        return
+    if world > 1:
+        dist.all_reduce(optimizer.flat_g, op=dist.ReduceOp.SUM, group=group)
+    optimizer.step()
+
+
 def gather_rows(local: torch.Tensor, H: int, group=None) -> torch.Tensor:
     """local: this rank's rows [r1 - r0, ...] (shard_bounds(H, rank, world)) -> the full [H, ...] tensor on
     every rank.  Rows are padded to the largest shard so one all_gather_into_tensor moves everything."""

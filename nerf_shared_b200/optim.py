@@ -33,11 +33,19 @@ class FlatAdam(torch.optim.Optimizer):
             self._offsets.append(total)
             total += p.numel()
         self._n = total
-        self.flat_p = torch.empty(total, device=dev, dtype=torch.float32)
-        self.flat_g = torch.zeros(total, device=dev, dtype=torch.float32)
-        self.exp_avg = torch.zeros(total, device=dev, dtype=torch.float32)
-        self.exp_avg_sq = torch.zeros(total, device=dev, dtype=torch.float32)
+        n_pad = (total + 3) // 4 * 4              # the fused all-reduce + Adam kernel moves float4s
+        self._n_pad = n_pad
+        self._p_store = torch.zeros(n_pad, device=dev, dtype=torch.float32)
+        self._m_store = torch.zeros(n_pad, device=dev, dtype=torch.float32)
+        self._v_store = torch.zeros(n_pad, device=dev, dtype=torch.float32)
+        self.p2p = None                           # multi-GPU: symmetric gradient buffer + peer pointers (_setup_p2p)
+        self._g_store = self._setup_p2p(n_pad, dev)
+        if self._g_store is None:
+            self._g_store = torch.zeros(n_pad, device=dev, dtype=torch.float32)
+        self.flat_p, self.flat_g = self._p_store[:total], self._g_store[:total]
+        self.exp_avg, self.exp_avg_sq = self._m_store[:total], self._v_store[:total]
         self._step = 0
+        self._epoch = 0            # flag epoch of the fused all-reduce kernel: one per pushed step, never rolled back
         self.grad_scale = 1.0      # e.g. 1/world_size after a SUM all-reduce of flat_g
         # CUDA-graph mode (train.GraphedTrainStep): step() launches the kernel that reads its scalars
         # from this device buffer and does no host bookkeeping; push_hyper() advances the step
@@ -51,6 +59,59 @@ class FlatAdam(torch.optim.Optimizer):
                 p.grad = self.flat_g[o:o + n].view(p.shape)
         self._views = [p.grad for p in ps]          # identity check in _grads_are_flat (48 `is` tests, no data_ptr calls)
         self._by_id = {id(p): o for p, o in zip(ps, self._offsets)}
+
+    # ---- multi-GPU: gradient all-reduce fused with the update over NVLink peer memory (csrc/adam.cu) ------------------
+    def _setup_p2p(self, n_pad, dev):
+        """With torch.distributed initialised on NCCL and more than one rank, the gradient buffer is allocated as
+        symmetric memory (every rank maps every other rank's buffer), so that nb_adam_allreduce_p2p can reduce the
+        gradients with peer loads / stores inside the optimizer kernel.  Collective: every rank builds its optimizer at
+        the same point of the program (SPMD).  Returns the [n_pad] gradient tensor, or None (single process, gloo,
+        NB_P2P_ADAM=0, or no symmetric memory on this system: NCCL all-reduce + nb_adam_step_dev are used then)."""
+        import os
+        import torch.distributed as dist
+        if os.environ.get("NB_P2P_ADAM", "1") == "0" or dev.type != "cuda":
+            return None
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() < 2 or dist.get_backend() != "nccl":
+            return None
+        try:
+            import ctypes as C
+            import torch.distributed._symmetric_memory as symm
+            world, rank = dist.get_world_size(), dist.get_rank()
+            if world > 16:
+                return None
+            buf = symm.empty(n_pad + 64, dtype=torch.float32, device=dev)       # gradients | 32 flag ints (+ slack)
+            buf.zero_()
+            hdl = symm.rendezvous(buf, dist.group.WORLD.group_name)
+            ptrs = [int(x) for x in hdl.buffer_ptrs]
+            if len(ptrs) != world or any(x == 0 for x in ptrs):
+                return None
+            grads = (C.c_void_p * world)(*ptrs)
+            flags = (C.c_void_p * world)(*[x + 4 * n_pad for x in ptrs])
+            counter = torch.zeros(1, device=dev, dtype=torch.int32)
+            torch.cuda.synchronize(dev)
+            dist.barrier()                       # every rank's flags are zero before anybody can signal
+            self.p2p = {"buf": buf, "hdl": hdl, "grads": grads, "flags": flags, "counter": counter, "rank": rank, "world": world}
+            return buf[:n_pad]
+        except Exception as e:                   # pragma: no cover  (no NVLink peer mapping: NCCL path)
+            if os.environ.get("NB_P2P_ADAM") == "1":
+                raise
+            print("nerf_shared_b200: symmetric-memory gradient buffer unavailable (%s: %s); using NCCL all-reduce" %
+                  (type(e).__name__, e))
+            self.p2p = None
+            return None
+
+    def step_allreduce(self):
+        """world > 1, inside a step whose scalars were pushed (push_hyper*): ONE launch that all-reduces the flat
+        gradient over NVLink peer memory and applies Adam with 1/world scaling (grad_scale).  Every rank must call it once
+        per step, in the same order relative to push_hyper."""
+        if self.p2p is None:
+            raise _lib.NerfB200Error("step_allreduce() needs the symmetric gradient buffer (NCCL, world > 1)")
+        q = self.p2p
+        lib = _lib.load()
+        with torch.cuda.device(self._p_store.device):
+            check(lib.nb_adam_allreduce_p2p(ptr(self._p_store), ptr(self._m_store), ptr(self._v_store), self._n_pad,
+                                            ptr(self._hyper), q["grads"], q["flags"], q["rank"], q["world"], ptr(q["counter"]),
+                                            stream_ptr()), "nb_adam_allreduce_p2p")
 
     # the weight-gradient kernels look this up to accumulate in place (see _bwd.py)
     def grad_offset(self, p):
@@ -118,22 +179,24 @@ class FlatAdam(torch.optim.Optimizer):
         arguments are taken at launch, so there is no host buffer to race with."""
         g0 = self._lr()
         self._step += 1
+        self._epoch += 1
         b1, b2 = g0["betas"]
         lib = _lib.load()
         with torch.cuda.device(self.flat_p.device):
             check(lib.nb_adam_hyper(ptr(self._hyper), float(g0["lr"]), float(b1), float(b2), float(g0["eps"]),
-                                    int(self._step), float(self.grad_scale), stream_ptr()), "nb_adam_hyper")
+                                    int(self._step), float(self.grad_scale), int(self._epoch), stream_ptr()), "nb_adam_hyper")
 
     def push_hyper_and_inputs(self, src1, dst1, src2, dst2):
         """push_hyper() and the copies src1 -> dst1, src2 -> dst2 (contiguous fp32 CUDA tensors of equal sizes) as one
         launch: what train.GraphedTrainStep does in front of every replay."""
         g0 = self._lr()
         self._step += 1
+        self._epoch += 1
         b1, b2 = g0["betas"]
         lib = _lib.load()
         with torch.cuda.device(self.flat_p.device):
             check(lib.nb_train_step_prologue(ptr(self._hyper), float(g0["lr"]), float(b1), float(b2), float(g0["eps"]),
-                                             int(self._step), float(self.grad_scale), ptr(src1), ptr(dst1), src1.numel(),
+                                             int(self._step), float(self.grad_scale), int(self._epoch), ptr(src1), ptr(dst1), src1.numel(),
                                              ptr(src2), ptr(dst2), src2.numel(), stream_ptr()), "nb_train_step_prologue")
 
     def bump_versions(self):

@@ -67,6 +67,9 @@ class GraphedTrainStep:
                 self._n_coarse = n_c
         self.loss = self.psnr = None
         self.launches_per_replay = 0
+        # all-reduce fused with the optimizer kernel over peer memory (optim.FlatAdam._setup_p2p), default group only
+        self._fused_ar = self.world > 1 and group is None and getattr(optimizer, "p2p", None) is not None \
+            and os.environ.get("NB_FUSED_AR", "1") != "0"
         if mode is None and overlap is not None and not overlap:
             mode = "autograd"                 # the single-stream form exists for the autograd-driven step only
         mode = mode or os.environ.get("NB_STEP", "autograd")
@@ -87,6 +90,18 @@ class GraphedTrainStep:
             self.rays, self.target = self.static.inbox.rays, self.static.inbox.target
             self.overlap = True               # the explicit sequence always runs the coarse backward as a second branch
 
+    def _reduce_and_step(self, already_reduced=0):
+        """Gradient exchange + Adam at the end of a step.  With the optimizer's symmetric gradient buffer (NCCL, world > 1)
+        both are ONE kernel over NVLink peer memory (FlatAdam.step_allreduce); otherwise an NCCL all-reduce of the part
+        of the flat buffer that is not reduced yet, then the Adam launch."""
+        opt = self.opt
+        if self._fused_ar:
+            opt.step_allreduce()
+            return
+        if self.world > 1:
+            torch.distributed.all_reduce(opt.flat_g[already_reduced:], group=self.group)
+        opt.step()
+
     # main.py:77-104 with the optimizer in graph mode
     def _step(self):
         if self.static is not None:
@@ -100,9 +115,7 @@ class GraphedTrainStep:
         # img2mse(rgb) + img2mse(rgb0) and mse2psnr (main.py:87-99) as one launch, one launch backward
         loss, _, _, psnr = _ops.MsePair.apply(rgb, extras.get("rgb0"), self.target)
         loss.backward()
-        if self.world > 1:
-            torch.distributed.all_reduce(opt.flat_g, group=self.group)
-        opt.step()
+        self._reduce_and_step()
         return loss.detach(), psnr
 
     def _step_overlap(self):
@@ -136,16 +149,14 @@ class GraphedTrainStep:
         torch.cuda.set_stream(side)
         try:
             box["m0"].backward()
-            if self._n_coarse:                # coarse gradients are final here: reduce them under the fine backward
+            if self._n_coarse and not self._fused_ar:   # coarse gradients are final here: reduce them under the fine backward
                 torch.distributed.all_reduce(opt.flat_g[:self._n_coarse], group=self.group)
         finally:
             torch.cuda.set_stream(main)
         m.backward()
         main.wait_stream(side)                # join
         alive.clear()                         # only now may the coarse pass's tensors go back to the allocator
-        if self.world > 1:
-            torch.distributed.all_reduce(opt.flat_g[self._n_coarse:], group=self.group)
-        opt.step()
+        self._reduce_and_step(self._n_coarse)
         loss = m.detach() + box["m0"].detach()     # main.py:99 (after the update: nothing waits for the sum)
         return loss, psnr
 
@@ -264,9 +275,14 @@ class ChunkedBatchStep:
             loss = (utils.img2mse(rgb, tgt) + utils.img2mse(extras["rgb0"], tgt)) * ((e - b) / n)
             loss.backward()
             total = loss.detach() if total is None else total + loss.detach()
-        if self.world > 1:
-            torch.distributed.all_reduce(opt.flat_g, group=self.group)
-        opt.step()
+        if self.world > 1 and self.group is None and getattr(opt, "p2p", None) is not None:
+            opt.push_hyper()                  # (advances the step counter: the fused kernel reads its scalars from the device)
+            opt.step_allreduce()
+            opt.bump_versions()
+        else:
+            if self.world > 1:
+                torch.distributed.all_reduce(opt.flat_g, group=self.group)
+            opt.step()
         return total
 
 
