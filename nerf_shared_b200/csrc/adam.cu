@@ -149,7 +149,7 @@ __device__ __forceinline__ void wait_flags(const int* mine, int world, int epoch
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(256) adam_allreduce_p2p_kernel(PeerPtrs peers, int rank, int world, float* __restrict__ p,
+__global__ void __launch_bounds__(512) adam_allreduce_p2p_kernel(PeerPtrs peers, int rank, int world, float* __restrict__ p,
                                                                   float* __restrict__ m, float* __restrict__ v, int64_t n,
                                                                   const float* __restrict__ hyper,
                                                                   unsigned int* __restrict__ done_counter) {
@@ -164,15 +164,21 @@ __global__ void __launch_bounds__(256) adam_allreduce_p2p_kernel(PeerPtrs peers,
   wait_flags(my_flags, world, epoch);
 
   // ---- phase 1: reduce slice `rank` over all ranks, write it back to everyone (float4 granularity)
-  const int64_t n4 = n >> 2;                                  // n is padded to a multiple of 4 by the caller
+  const int64_t n4 = n >> 2;                                  // n is a multiple of 4
   const int64_t per = (n4 + world - 1) / world;
   const int64_t lo = per * rank, hi = (lo + per < n4) ? lo + per : n4;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = lo + tid; i < hi; i += nth) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int q = 0; q < world; ++q) {                         // fixed rank order: the same sum bit for bit on every step
-      const float4 g = reinterpret_cast<const float4*>(peers.grad[q])[i];
-      acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
+    for (int q0 = 0; q0 < world; q0 += 8) {                   // all peer loads of a group in flight before the first add
+      float4 g[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        g[j] = (q0 + j < world) ? __ldcv(reinterpret_cast<const float4*>(peers.grad[q0 + j]) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {                           // fixed rank order: the same sum bit for bit on every rank
+        acc.x += g[j].x; acc.y += g[j].y; acc.z += g[j].z; acc.w += g[j].w;
+      }
     }
     for (int q = 0; q < world; ++q) reinterpret_cast<float4*>(peers.grad[q])[i] = acc;
   }
@@ -192,14 +198,24 @@ __global__ void __launch_bounds__(256) adam_allreduce_p2p_kernel(PeerPtrs peers,
   // ---- phase 2: Adam from the reduced gradient (now in this rank's own buffer)
   const float step_size = hyper[0], beta1 = hyper[1], beta2 = hyper[2], eps = hyper[3], inv_sqrt_bc2 = hyper[4],
               grad_scale = hyper[5];
-  const float* g = peers.grad[rank];
-  for (int64_t i = tid; i < n; i += nth) {
-    const float gi = __ldcv(g + i) * grad_scale;              // written by peers: bypass stale L1 lines
-    const float mi = beta1 * m[i] + (1.0f - beta1) * gi;
-    const float vi = beta2 * v[i] + (1.0f - beta2) * gi * gi;
-    m[i] = mi;
-    v[i] = vi;
-    p[i] = p[i] - step_size * (mi / (sqrtf(vi) * inv_sqrt_bc2 + eps));
+  const float4* g4 = reinterpret_cast<const float4*>(peers.grad[rank]);
+  float4* p4 = reinterpret_cast<float4*>(p);
+  float4* m4 = reinterpret_cast<float4*>(m);
+  float4* v4 = reinterpret_cast<float4*>(v);
+  for (int64_t i = tid; i < n4; i += nth) {
+    const float4 gq = __ldcv(g4 + i);                          // written by peers: bypass stale L1 lines
+    float4 mq = m4[i], vq = v4[i], pq = p4[i];
+    const float gi[4] = {gq.x * grad_scale, gq.y * grad_scale, gq.z * grad_scale, gq.w * grad_scale};
+    float* mm = &mq.x; float* vv = &vq.x; float* pp = &pq.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float mi = beta1 * mm[k] + (1.0f - beta1) * gi[k];
+      const float vi = beta2 * vv[k] + (1.0f - beta2) * gi[k] * gi[k];
+      mm[k] = mi;
+      vv[k] = vi;
+      pp[k] = pp[k] - step_size * (mi / (sqrtf(vi) * inv_sqrt_bc2 + eps));
+    }
+    m4[i] = mq; v4[i] = vq; p4[i] = pq;
   }
 }
 
@@ -212,6 +228,7 @@ extern "C" int nb_adam_allreduce_p2p(float* p, float* m, float* v, int64_t n, co
   NB_REQUIRE(world >= 1 && world <= nb::kMaxPeers && rank >= 0 && rank < world, "nb_adam_allreduce_p2p: bad rank / world (max %d ranks)",
              nb::kMaxPeers);
   NB_REQUIRE(n > 0 && (n & 3) == 0, "nb_adam_allreduce_p2p: n must be a positive multiple of 4 (pad the flat buffers)");
+  NB_REQUIRE((((uintptr_t)p | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "nb_adam_allreduce_p2p: p / m / v must be 16-byte aligned");
   nb::PeerPtrs pp;
   for (int q = 0; q < nb::kMaxPeers; ++q) {
     pp.grad[q] = q < world ? (float*)peer_grads[q] : nullptr;
@@ -220,8 +237,8 @@ extern "C" int nb_adam_allreduce_p2p(float* p, float* m, float* v, int64_t n, co
                "nb_adam_allreduce_p2p: peer %d: null or unaligned pointer", q);
   }
   // one block per SM at most: every block spins on the flags, so all of them have to be resident
-  int grid = (int)((n / 4 + 255) / 256);
+  int grid = (int)((n / 4 + 511) / 512);
   if (grid > nb::kNumSMs) grid = nb::kNumSMs;
-  nb::adam_allreduce_p2p_kernel<<<grid, 256, 0, nb::as_stream(stream)>>>(pp, rank, world, p, m, v, n, hyper, done_counter);
+  nb::adam_allreduce_p2p_kernel<<<grid, 512, 0, nb::as_stream(stream)>>>(pp, rank, world, p, m, v, n, hyper, done_counter);
   return nb::check_launch("nb_adam_allreduce_p2p");
 }

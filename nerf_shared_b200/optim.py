@@ -87,7 +87,8 @@ class FlatAdam(torch.optim.Optimizer):
                 return None
             grads = (C.c_void_p * world)(*ptrs)
             flags = (C.c_void_p * world)(*[x + 4 * n_pad for x in ptrs])
-            counter = torch.zeros(1, device=dev, dtype=torch.int32)
+            counter = torch.zeros(2, device=dev, dtype=torch.int32)
+            self._p2p_ptrs = ptrs
             torch.cuda.synchronize(dev)
             dist.barrier()                       # every rank's flags are zero before anybody can signal
             self.p2p = {"buf": buf, "hdl": hdl, "grads": grads, "flags": flags, "counter": counter, "rank": rank, "world": world}
@@ -100,18 +101,35 @@ class FlatAdam(torch.optim.Optimizer):
             self.p2p = None
             return None
 
-    def step_allreduce(self):
+    def step_allreduce(self, lo=0, n=None, instance=0):
         """world > 1, inside a step whose scalars were pushed (push_hyper*): ONE launch that all-reduces the flat
         gradient over NVLink peer memory and applies Adam with 1/world scaling (grad_scale).  Every rank must call it once
-        per step, in the same order relative to push_hyper."""
+        per step, in the same order relative to push_hyper.
+        (lo, n): a sub-range of the flat buffers (multiples of 4 elements) -- a step may update the coarse network's range
+        as soon as its gradients are final and the fine network's at the end; two launches that can overlap in time
+        must use different `instance`s (0 / 1: separate flags and counters)."""
         if self.p2p is None:
             raise _lib.NerfB200Error("step_allreduce() needs the symmetric gradient buffer (NCCL, world > 1)")
+        import ctypes as C
         q = self.p2p
+        if n is None:
+            n = self._n_pad - lo
+        elif lo + n == self._n:
+            n = self._n_pad - lo                  # the tail range takes the padding along
+        if lo % 4 or n % 4 or instance not in (0, 1):
+            raise ValueError("step_allreduce: range must be a multiple of 4 elements, instance 0 or 1")
+        key = (lo, instance)
+        arrs = q.setdefault("ranges", {}).get(key)
+        if arrs is None:
+            w = q["world"]
+            arrs = ((C.c_void_p * w)(*[x + 4 * lo for x in self._p2p_ptrs]),
+                    (C.c_void_p * w)(*[x + 4 * (self._n_pad + 32 * instance) for x in self._p2p_ptrs]))
+            q["ranges"][key] = arrs
         lib = _lib.load()
         with torch.cuda.device(self._p_store.device):
-            check(lib.nb_adam_allreduce_p2p(ptr(self._p_store), ptr(self._m_store), ptr(self._v_store), self._n_pad,
-                                            ptr(self._hyper), q["grads"], q["flags"], q["rank"], q["world"], ptr(q["counter"]),
-                                            stream_ptr()), "nb_adam_allreduce_p2p")
+            check(lib.nb_adam_allreduce_p2p(ptr(self._p_store[lo:]), ptr(self._m_store[lo:]), ptr(self._v_store[lo:]), n,
+                                            ptr(self._hyper), arrs[0], arrs[1], q["rank"], q["world"],
+                                            ptr(q["counter"][instance:]), stream_ptr()), "nb_adam_allreduce_p2p")
 
     # the weight-gradient kernels look this up to accumulate in place (see _bwd.py)
     def grad_offset(self, p):

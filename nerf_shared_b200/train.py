@@ -63,7 +63,7 @@ class GraphedTrainStep:
         if self.overlap and self.world > 1 and os.environ.get("NB_SPLIT_AR", "1") != "0":
             n_c = sum(p.numel() for p in coarse_model.parameters())
             first_fine = next(iter(fine_model.parameters()))
-            if optimizer.grad_offset(first_fine) == n_c and 0 < n_c < optimizer.flat_g.numel():
+            if optimizer.grad_offset(first_fine) == n_c and 0 < n_c < optimizer.flat_g.numel() and n_c % 4 == 0:
                 self._n_coarse = n_c
         self.loss = self.psnr = None
         self.launches_per_replay = 0
@@ -96,7 +96,7 @@ class GraphedTrainStep:
         of the flat buffer that is not reduced yet, then the Adam launch."""
         opt = self.opt
         if self._fused_ar:
-            opt.step_allreduce()
+            opt.step_allreduce(already_reduced, opt.flat_g.numel() - already_reduced, instance=0)
             return
         if self.world > 1:
             torch.distributed.all_reduce(opt.flat_g[already_reduced:], group=self.group)
@@ -149,8 +149,11 @@ class GraphedTrainStep:
         torch.cuda.set_stream(side)
         try:
             box["m0"].backward()
-            if self._n_coarse and not self._fused_ar:   # coarse gradients are final here: reduce them under the fine backward
-                torch.distributed.all_reduce(opt.flat_g[:self._n_coarse], group=self.group)
+            if self._n_coarse:                # coarse gradients are final here: reduce them under the fine backward
+                if self._fused_ar:            # (fused with the coarse network's Adam update: nothing later reads its weights)
+                    opt.step_allreduce(0, self._n_coarse, instance=1)
+                else:
+                    torch.distributed.all_reduce(opt.flat_g[:self._n_coarse], group=self.group)
         finally:
             torch.cuda.set_stream(main)
         m.backward()
