@@ -245,10 +245,12 @@ NB_API int nb_adam_step_dev(float* p, const float* g, float* m, float* v, int64_
  * process (torch symmetric memory / CUDA IPC); done_counter: one zero-initialised device uint32 of this rank; hyper as
  * nb_adam_step_dev, with hyper[6] = `epoch` of nb_adam_hyper / nb_train_step_prologue: a counter that grows by one per call of this
  * function and never repeats (unlike `step`, which a caller may roll back), identical on all ranks.
- * Every rank must launch it once per step.  replaces: the dist.all_reduce a data-parallel main.py would add before
+ * multicast_grads: the NVLS multicast mapping of the same gradient buffers (the NVSwitch then reduces and broadcasts:
+ * multimem.ld_reduce / multimem.st) or NULL (peer loads / stores).  Every rank must launch it once per step.  replaces: the dist.all_reduce a data-parallel main.py would add before
  * optimizer.step() (main.py:103-104) + Adam.step. */
 NB_API int nb_adam_allreduce_p2p(float* p, float* m, float* v, int64_t n, const float* hyper, void* const* peer_grads,
-                                 void* const* peer_flags, int rank, int world, unsigned int* done_counter, void* stream);
+                                 void* const* peer_flags, void* multicast_grads, int rank, int world,
+                                 unsigned int* done_counter, void* stream);
 
 /* ---- self test ------------------------------------------------------------------------- */
 /* D[128,128] = A[128,K] * B[128,K]^T (bf16-rounded operands, fp32 accumulate) through the same

@@ -127,7 +127,20 @@ constexpr int kMaxPeers = 16;
 struct PeerPtrs {
   float* grad[kMaxPeers];   // every rank's symmetric gradient buffer
   int* flags[kMaxPeers];    // every rank's flag block: [0..W) = barrier A, [16..16+W) = barrier B
+  float* mc;                // multicast (NVLS) mapping of the same buffers, or NULL: the NVSwitch reduces / broadcasts
 };
+
+// NVLink SHARP: one load returns the sum over all ranks' copies (reduced inside the switch), one store writes all copies
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* p) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st(float* p, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
 
 __device__ __forceinline__ void st_release_sys(int* p, int v) {
   asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -168,6 +181,10 @@ __global__ void __launch_bounds__(512) adam_allreduce_p2p_kernel(PeerPtrs peers,
   const int64_t per = (n4 + world - 1) / world;
   const int64_t lo = per * rank, hi = (lo + per < n4) ? lo + per : n4;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  if (peers.mc != nullptr) {
+    // in-switch reduction: 1/W of the buffer per rank crosses this GPU's links once in each direction
+    for (int64_t i = lo + tid; i < hi; i += nth) multimem_st(peers.mc + 4 * i, multimem_ld_reduce_add(peers.mc + 4 * i));
+  } else
   for (int64_t i = lo + tid; i < hi; i += nth) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int q0 = 0; q0 < world; q0 += 8) {                   // all peer loads of a group in flight before the first add
@@ -222,14 +239,16 @@ __global__ void __launch_bounds__(512) adam_allreduce_p2p_kernel(PeerPtrs peers,
 }  // namespace nb
 
 extern "C" int nb_adam_allreduce_p2p(float* p, float* m, float* v, int64_t n, const float* hyper, void* const* peer_grads,
-                                     void* const* peer_flags, int rank, int world, unsigned int* done_counter,
-                                     void* stream) {
+                                     void* const* peer_flags, void* multicast_grads, int rank, int world,
+                                     unsigned int* done_counter, void* stream) {
   NB_REQUIRE(p && m && v && hyper && peer_grads && peer_flags && done_counter, "nb_adam_allreduce_p2p: null pointer");
   NB_REQUIRE(world >= 1 && world <= nb::kMaxPeers && rank >= 0 && rank < world, "nb_adam_allreduce_p2p: bad rank / world (max %d ranks)",
              nb::kMaxPeers);
   NB_REQUIRE(n > 0 && (n & 3) == 0, "nb_adam_allreduce_p2p: n must be a positive multiple of 4 (pad the flat buffers)");
   NB_REQUIRE((((uintptr_t)p | (uintptr_t)m | (uintptr_t)v) & 15) == 0, "nb_adam_allreduce_p2p: p / m / v must be 16-byte aligned");
   nb::PeerPtrs pp;
+  pp.mc = (float*)multicast_grads;
+  NB_REQUIRE(((uintptr_t)pp.mc & 15) == 0, "nb_adam_allreduce_p2p: unaligned multicast pointer");
   for (int q = 0; q < nb::kMaxPeers; ++q) {
     pp.grad[q] = q < world ? (float*)peer_grads[q] : nullptr;
     pp.flags[q] = q < world ? (int*)peer_flags[q] : nullptr;

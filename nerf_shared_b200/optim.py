@@ -89,9 +89,17 @@ class FlatAdam(torch.optim.Optimizer):
             flags = (C.c_void_p * world)(*[x + 4 * n_pad for x in ptrs])
             counter = torch.zeros(2, device=dev, dtype=torch.int32)
             self._p2p_ptrs = ptrs
+            mc = 0
+            if os.environ.get("NB_NVLS", "1") != "0":
+                try:
+                    mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+                except Exception:
+                    mc = 0
+            self._p2p_mc = mc
             torch.cuda.synchronize(dev)
             dist.barrier()                       # every rank's flags are zero before anybody can signal
-            self.p2p = {"buf": buf, "hdl": hdl, "grads": grads, "flags": flags, "counter": counter, "rank": rank, "world": world}
+            self.p2p = {"buf": buf, "hdl": hdl, "grads": grads, "flags": flags, "counter": counter, "rank": rank, "world": world,
+                        "nvls": bool(self._p2p_mc)}
             return buf[:n_pad]
         except Exception as e:                   # pragma: no cover  (no NVLink peer mapping: NCCL path)
             if os.environ.get("NB_P2P_ADAM") == "1":
@@ -128,7 +136,8 @@ class FlatAdam(torch.optim.Optimizer):
         lib = _lib.load()
         with torch.cuda.device(self._p_store.device):
             check(lib.nb_adam_allreduce_p2p(ptr(self._p_store[lo:]), ptr(self._m_store[lo:]), ptr(self._v_store[lo:]), n,
-                                            ptr(self._hyper), arrs[0], arrs[1], q["rank"], q["world"],
+                                            ptr(self._hyper), arrs[0], arrs[1],
+                                            C.c_void_p(self._p2p_mc + 4 * lo if self._p2p_mc else 0), q["rank"], q["world"],
                                             ptr(q["counter"][instance:]), stream_ptr()), "nb_adam_allreduce_p2p")
 
     # the weight-gradient kernels look this up to accumulate in place (see _bwd.py)

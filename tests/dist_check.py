@@ -98,8 +98,9 @@ same_p = bool(torch.equal(lo, hi))
 # the fused all-reduce + Adam kernel leaves the reduced (summed) gradient in the flat buffer: compare it with the
 # NCCL-reduced gradient of the eager sharded step
 rel_g = float((opt.flat_g * opt.grad_scale - g_n).norm() / g_n.norm())
-say("graphed step (fused peer-memory all-reduce + Adam: %s, split NCCL all-reduce: %s) vs eager sharded step: reduced gradient rel %.3g, "
-    "params max|d| %.3g ; identical on all ranks: %s" % (step._fused_ar, bool(step._n_coarse) and not step._fused_ar, rel_g, dg, same_p))
+say("graphed step (fused peer-memory all-reduce + Adam: %s [in-switch NVLS reduction: %s], split NCCL all-reduce: %s) vs eager sharded step: "
+    "reduced gradient rel %.3g, params max|d| %.3g ; identical on all ranks: %s"
+    % (step._fused_ar, bool(opt.p2p and opt.p2p.get("nvls")), bool(step._n_coarse) and not step._fused_ar, rel_g, dg, same_p))
 ok &= dg < 1.1e-3 and same_p and (world == 1 or step._fused_ar or step._n_coarse > 0) and (world == 1 or rel_g < 1e-3)
 # a few more replays: the flag epochs advance, parameters stay identical on all ranks
 for _ in range(5):
