@@ -176,6 +176,19 @@ NB_API int nb_mlp_fwd_f32(const NbMlpWeights* w, const float* pts, const float* 
 NB_API int nb_mlp_fwd_f32_noview(const NbMlpWeights* w, const float* out_w, const float* out_b, int out_ch,
                                  const float* pts, int64_t M, float* raw, void* stream);
 
+/* fp32 TRAINING path (CUDA cores, layer-by-layer GEMMs, saved fp32 activations): the model variants the tensor-core
+ * kernels do not tile -- encodings up to multires 15 / 6 (configs/stonehenge.txt) and use_viewdirs=False -- and the
+ * exact-operand reference of the bf16 kernels' gradients.  acts: nb_mlp_f32_act_floats(...) floats.
+ * out_w / out_b / out_ch: output_linear of a use_viewdirs=False model (raw is then [M, out_ch], viewdirs unused), else NULL / 0.
+ * replaces: NeRF.forward / MLP nerf.py:96-134 and its autograd (main.py:103). */
+NB_API int64_t nb_mlp_f32_act_floats(int L_pts, int L_dirs, int noview, int64_t M);
+NB_API int nb_mlp_f32_fwd_train(const NbMlpWeights* w, const float* out_w, const float* out_b, int out_ch, const float* pts,
+                                const float* viewdirs, int64_t M, int S, float* raw, float* acts, void* stream);
+/* Weight / bias gradients ACCUMULATE into grads + off[i], i in the order of nb_mlp_bwd_tc's offsets (use_viewdirs=False:
+ * 16 / 17 = output_linear weight / bias, 18..23 ignored).  scratch: 2 * M * 256 floats. */
+NB_API int nb_mlp_f32_bwd(const NbMlpWeights* w, const float* out_w, int out_ch, const float* acts, const float* d_raw, int64_t M,
+                          const int64_t* off, float* grads, float* scratch, void* stream);
+
 /* Size in bytes of the packed bf16 operand blob + fp32 side table used by the tensor-core
  * kernels for one model. */
 NB_API int64_t nb_mlp_packed_bytes(int L_pts, int L_dirs);

@@ -64,6 +64,9 @@ SIGNATURES = {
     "nb_composite_bwd": (i32, [vp, vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, vp, vp, vp]),
     "nb_mlp_fwd_f32": (i32, [C.POINTER(NbMlpWeights), vp, vp, i64, i32, vp, vp]),
     "nb_mlp_fwd_f32_noview": (i32, [C.POINTER(NbMlpWeights), vp, vp, i32, vp, i64, vp, vp]),
+    "nb_mlp_f32_act_floats": (i64, [i32, i32, i32, i64]),
+    "nb_mlp_f32_fwd_train": (i32, [C.POINTER(NbMlpWeights), vp, vp, i32, vp, vp, i64, i32, vp, vp, vp]),
+    "nb_mlp_f32_bwd": (i32, [C.POINTER(NbMlpWeights), vp, i32, vp, vp, i64, C.POINTER(i64), vp, vp, vp]),
     "nb_mlp_packed_bytes": (i64, [i32, i32]),
     "nb_mlp_pack": (i32, [C.POINTER(NbMlpWeights), vp, vp]),
     "nb_mlp_fwd_tc": (i32, [vp, i32, i32, vp, vp, i64, i32, vp, vp, vp]),

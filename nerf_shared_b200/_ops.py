@@ -481,3 +481,81 @@ def composite_train(raw, z, rays_d, noise, target, white_bkgd, inv_n3, loss_sum,
                                      ptr(rgb), ptr(disp), ptr(acc), ptr(weights), ptr(d_raw), ptr(loss_sum), stream_ptr()),
               "nb_composite_train")
     return rgb, disp, acc, weights, d_raw
+
+
+# ------------------------------------------------------------------------ fp32 training path (csrc/mlp_f32_train.cu)
+def _f32_params(model):
+    """Parameters in the order nb_mlp_f32_bwd's offsets use; (list, output_linear or None)."""
+    if model.use_viewdirs:
+        return mlp_params(model), None
+    pl = list(model.pts_linears)
+    return [l.weight for l in pl] + [l.bias for l in pl] + [model.output_linear.weight, model.output_linear.bias], model.output_linear
+
+
+class NerfMLPf32(torch.autograd.Function):
+    """NeRF.forward with exact fp32 operands and a backward (layer-by-layer CUDA-core GEMMs, saved fp32 activations):
+    encodings up to multires 15 / 6 and use_viewdirs=False models; parameter gradients only."""
+
+    @staticmethod
+    def forward(ctx, pts, viewdirs, S, model, *params):
+        lib = _lib_for(pts)
+        p = f32c(pts).view(-1, 3)
+        M = p.shape[0]
+        ps, out_lin = _f32_params(model)
+        for t in ps:
+            if t.dtype != torch.float32 or not t.is_contiguous() or t.device != p.device:
+                raise _lib.NerfB200Error("NeRF parameters must be contiguous fp32 tensors on the device of the points")
+        w = _lib.NbMlpWeights()
+        for i in range(8):
+            w.pts_w[i], w.pts_b[i] = ps[i].data_ptr(), ps[8 + i].data_ptr()
+        w.L_pts = int(model.multires)
+        noview = out_lin is not None
+        if noview:
+            w.L_dirs, out_ch = 0, int(out_lin.weight.shape[0])
+            v = None
+        else:
+            w.feature_w, w.feature_b, w.alpha_w, w.alpha_b = (ps[16].data_ptr(), ps[17].data_ptr(), ps[18].data_ptr(), ps[19].data_ptr())
+            w.views_w, w.views_b, w.rgb_w, w.rgb_b = ps[20].data_ptr(), ps[21].data_ptr(), ps[22].data_ptr(), ps[23].data_ptr()
+            w.L_dirs, out_ch = int(model.multires_views), 4
+            v = f32c(viewdirs).view(-1, 3)
+        acts = torch.empty((int(lib.nb_mlp_f32_act_floats(w.L_pts, w.L_dirs, int(noview), M)),), device=p.device, dtype=torch.float32)
+        raw = torch.empty((M, out_ch), device=p.device, dtype=torch.float32)
+        with torch.cuda.device(p.device):
+            check(lib.nb_mlp_f32_fwd_train(C.byref(w), ptr(out_lin.weight) if noview else None, ptr(out_lin.bias) if noview else None,
+                                           out_ch if noview else 0, ptr(p), ptr(v), M, int(S), ptr(raw), ptr(acts), stream_ptr()),
+                  "nb_mlp_f32_fwd_train")
+        ctx.w, ctx.model, ctx.M, ctx.noview, ctx.out_ch = w, model, M, noview, out_ch
+        ctx.save_for_backward(acts)
+        return raw
+
+    @staticmethod
+    def backward(ctx, g_raw):
+        (acts,) = ctx.saved_tensors
+        lib = _lib_for(acts)
+        model, M = ctx.model, ctx.M
+        ps, out_lin = _f32_params(model)
+        offs, total = [], 0
+        for t in ps:
+            offs.append(total)
+            total += t.numel()
+        offs = offs + [0] * (24 - len(offs))
+        grads = torch.zeros((total,), device=acts.device, dtype=torch.float32)
+        scratch = torch.empty((2 * M * 256,), device=acts.device, dtype=torch.float32)
+        g = f32c(g_raw).view(M, ctx.out_ch)
+        with torch.cuda.device(acts.device):
+            check(lib.nb_mlp_f32_bwd(C.byref(ctx.w), ptr(out_lin.weight) if ctx.noview else None, ctx.out_ch if ctx.noview else 0,
+                                     ptr(acts), ptr(g), M, (C.c_int64 * 24)(*offs), ptr(grads), ptr(scratch), stream_ptr()),
+                  "nb_mlp_f32_bwd")
+        out = []
+        for i, t in enumerate(ps):
+            out.append(grads[offs[i]:offs[i] + t.numel()].view_as(t) if ctx.needs_input_grad[4 + i] else None)
+        return (None, None, None, None) + tuple(out)
+
+
+def mlp_f32_trainable(model, pts, viewdirs, S):
+    """raw [M, 4 or output_ch] through the fp32 training path; gradients flow to the parameters only."""
+    if pts.requires_grad or (viewdirs is not None and viewdirs.requires_grad):
+        raise NotImplementedError("the fp32 training path differentiates with respect to the network parameters only "
+                                  "(pose / input gradients: use the tensor-core path, precision='bf16')")
+    ps, _ = _f32_params(model)
+    return NerfMLPf32.apply(pts, viewdirs, S, model, *ps)

@@ -68,6 +68,10 @@ class NeRF(nn.Module):
         self.D, self.W, self.skips, self.use_viewdirs = D, W, skips, use_viewdirs
         self.multires, self.multires_views, self.i_embed = multires, multires_views, i_embed
         self.precision = _DEFAULT_PRECISION
+        if multires > 10 or (use_viewdirs and multires_views > 4) or not use_viewdirs:
+            # encodings wider than the tensor-core tiling (63 / 27 columns; configs/stonehenge.txt uses 93 / 39) and the
+            # trunk -> output_linear variant run on the fp32 CUDA-core kernels, forward and backward
+            self.precision = "fp32"
         self.embed_fn, self.input_ch = get_embedder(multires, i_embed)
         self.input_ch_views, self.embeddirs_fn = 0, None
         if use_viewdirs:
@@ -92,13 +96,12 @@ class NeRF(nn.Module):
                 "i_embed=0); got D=%s W=%s skips=%s i_embed=%s" % (self.D, self.W, self.skips, self.i_embed))
 
     def _forward_noview(self, inputs):
-        """use_viewdirs=False (nerf.py:93-94,131-132): trunk -> output_linear, fp32 CUDA-core kernel.
-        Forward only: no shipped config trains this model, so there are no backward kernels for it."""
+        """use_viewdirs=False (nerf.py:93-94,131-132): trunk -> output_linear on the fp32 CUDA-core kernels: the fused
+        forward kernel without gradients, the layer-by-layer training path (csrc/mlp_f32_train.cu) with them."""
         if torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in self.parameters())):
-            raise NotImplementedError(
-                "libnerf_b200 evaluates use_viewdirs=False models forward-only; call under torch.no_grad() "
-                "(training and pose gradients need use_viewdirs=True, as in every reference config)")
-        raw = _ops.mlp_forward_f32_noview(self, inputs.reshape(-1, 3))
+            raw = _ops.mlp_f32_trainable(self, inputs.reshape(-1, 3), None, 1)
+        else:
+            raw = _ops.mlp_forward_f32_noview(self, inputs.reshape(-1, 3))
         return raw.reshape(list(inputs.shape[:-1]) + [raw.shape[-1]])
 
     def forward(self, inputs, viewdirs, netchunk=1024 * 64):
@@ -119,6 +122,10 @@ class NeRF(nn.Module):
         if pts.shape[0] % max(n_rays, 1) != 0:
             raise ValueError("inputs %s do not broadcast against viewdirs %s" % (tuple(inputs.shape), tuple(viewdirs.shape)))
         S = pts.shape[0] // max(n_rays, 1)
+        if self.precision == "fp32" and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            # exact-operand training path (also the only one for multires > 10 / multires_views > 4)
+            raw = _ops.mlp_f32_trainable(self, pts, viewdirs.reshape(-1, 3), S)
+            return raw.reshape(list(inputs.shape[:-1]) + [4])
         raw = _ops.NerfMLP.apply(pts, viewdirs.reshape(-1, 3), S, self, torch.is_grad_enabled(), *_ops.mlp_params(self))
         return raw.reshape(list(inputs.shape[:-1]) + [4])
 

@@ -72,5 +72,45 @@ for tag, (H, W, K, c2w, kw) in {
     for k in ("rgb0", "disp0", "acc0", "z_std", "raw"):
         out["render/%s/%s" % (tag, k)] = npy(extras[k])
 
+# ---- parameter gradients of both variants (the reference's autograd): d/dtheta sum(raw * G) with a fixed cotangent G,
+#      and a full training step of the use_viewdirs=False pair through the Renderer (main.py:77-103)
+def grad_section(tag, model, pts_, vd_, gen_seed):
+    G = torch.from_numpy(np.random.default_rng(gen_seed).normal(size=tuple(pts_.shape[:-1]) + (model(pts_, vd_).shape[-1],)).astype(np.float32))
+    model.zero_grad()
+    (model(pts_, vd_) * G).sum().backward()
+    out["grad/%s/G" % tag] = npy(G)
+    for k, p in model.named_parameters():
+        if p.grad is None:
+            continue
+        out["grad/%s/gnorm/%s" % (tag, k)] = np.float64(p.grad.double().norm().item())
+        out["grad/%s/ghead/%s" % (tag, k)] = npy(p.grad.reshape(-1)[:512])
+
+
+grad_section("noview5", ref_model(p5c, 5), pts, None, 51)
+grad_section("wide156", m156, pts156, vd156, 52)
+
+with contextlib.redirect_stdout(io.StringIO()):
+    r = render_utils.Renderer(perturb=0.0, N_importance=128, N_samples=64, use_viewdirs=False, white_bkgd=True,
+                              raw_noise_std=0.0, near=2.0, far=6.0)
+r.train()
+# (x 1.59 matrices: positive density on a fraction of the samples, non-zero fine gradients)
+p5c_s, p5f_s = O.make_params(31, output_ch=5, scale=1.59), O.make_params(32, output_ch=5, scale=1.59)
+mc, mf = ref_model(p5c_s, 5), ref_model(p5f_s, 5)
+H = W = 8
+K = O.blender_intrinsics(H, W)
+ro, rd = utils.get_rays(H, W, K, torch.Tensor(O.pose_spherical(75.0, -30.0, 4.0)[:3, :4]))
+ro, rd = ro.reshape(-1, 3)[:32].contiguous(), rd.reshape(-1, 3)[:32].contiguous()
+tgt = torch.from_numpy(np.random.default_rng(53).uniform(0, 1, size=(32, 3)).astype(np.float32))
+rgb, _, _, extras = r.render_from_rays(H, W, K, chunk=32768, rays=torch.stack([ro, rd], 0), coarse_model=mc, fine_model=mf, retraw=True)
+loss = utils.img2mse(rgb, tgt) + utils.img2mse(extras["rgb0"], tgt)
+loss.backward()
+out["train_noview/rays_o"], out["train_noview/rays_d"], out["train_noview/target"] = npy(ro), npy(rd), npy(tgt)
+out["train_noview/loss"] = npy(loss)
+for tag, m in (("coarse", mc), ("fine", mf)):
+    for k, p in m.named_parameters():
+        if p.grad is not None:
+            out["train_noview/%s/gnorm/%s" % (tag, k)] = np.float64(p.grad.double().norm().item())
+print("noview train: loss %.5f, |g fine output_linear.weight| %.3e" % (float(loss), out["train_noview/fine/gnorm/output_linear.weight"]))
+
 np.savez_compressed(os.path.join(HERE, "reference_noview_golden.npz"), **out)
 print("wrote", len(out), "arrays,", os.path.getsize(os.path.join(HERE, "reference_noview_golden.npz")), "bytes")

@@ -52,12 +52,12 @@ def test_umma_mn_major_selftest(K):
 def test_fp32_kernel_vs_golden(golden):
     m = make_model(11, precision="fp32")
     raw = m(cuda(golden["mlp/pts"]), cuda(golden["mlp/viewdirs"]))
-    np.testing.assert_allclose(raw.cpu().numpy(), golden["mlp/raw_seed11"], rtol=0, atol=2e-5)
+    np.testing.assert_allclose(raw.detach().cpu().numpy(), golden["mlp/raw_seed11"], rtol=0, atol=2e-5)
     m = make_model(13, scale=1.59, precision="fp32")
     raw = m(cuda(golden["mlp/pts"]), cuda(golden["mlp/viewdirs"]))
-    np.testing.assert_allclose(raw.cpu().numpy(), golden["mlp/raw_seed13x1.59"], rtol=0, atol=2e-4)
+    np.testing.assert_allclose(raw.detach().cpu().numpy(), golden["mlp/raw_seed13x1.59"], rtol=0, atol=2e-4)
     dens = make_model(11, precision="fp32").get_density(cuda(golden["mlp/pts"]))
-    np.testing.assert_allclose(dens.cpu().numpy(), golden["mlp/density_seed11"], rtol=0, atol=2e-5)
+    np.testing.assert_allclose(dens.detach().cpu().numpy(), golden["mlp/density_seed11"], rtol=0, atol=2e-5)
 
 
 def test_fp32_kernel_ragged_sizes():
@@ -68,7 +68,7 @@ def test_fp32_kernel_ragged_sizes():
         ref = O.nerf_query(p, pts, vd)
         out = m(pts.cuda(), vd.cuda())
         assert out.shape == ref.shape
-        np.testing.assert_allclose(out.cpu().numpy(), ref.numpy(), rtol=0, atol=2e-5)
+        np.testing.assert_allclose(out.detach().cpu().numpy(), ref.numpy(), rtol=0, atol=2e-5)
 
 
 def test_tc_layers_vs_bf16_oracle():
@@ -149,3 +149,95 @@ def test_tc_linearity_in_last_layer_full_size():
         m.rgb_linear.weight.mul_(2.0)
         b = m(pts.cuda(), vd.cuda())[..., :3]
     assert torch.equal(b, 2.0 * a)
+
+
+def _grads_vs_oracle(model, params, pts, vd, G, tol, **kw):
+    raw = model(pts.cuda(), None if vd is None else vd.cuda())
+    (raw * G.cuda()).sum().backward()
+    p = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+    ref = O.nerf_query(p, pts, vd, **kw)
+    assert maxabs(raw, ref) <= 2e-4
+    (ref * G).sum().backward()
+    worst = 0.0
+    for k, t in model.named_parameters():
+        e = p[k].grad
+        if e is None or float(e.abs().max()) == 0.0:
+            assert t.grad is None or float(t.grad.abs().max()) == 0.0, k
+            continue
+        rel = float((t.grad.cpu() - e).norm() / e.norm())
+        worst = max(worst, rel)
+        assert rel <= tol, (k, rel)
+    return worst
+
+
+def test_fp32_training_path_noview_and_wide_models(golden_noview):
+    """csrc/mlp_f32_train.cu: forward + parameter gradients of the use_viewdirs=False model (output_ch 5 and 4) and of
+    the multires 15 / 6 model (configs/stonehenge.txt) against the reference's gradients (golden) and the oracle's fp32
+    autograd; ragged sample counts."""
+    from nerf_shared_b200 import nerf
+    g = golden_noview
+    rng = np.random.default_rng(9)
+    # reference goldens
+    for tag, mk, params, pts, vd in (
+            ("noview5", lambda: nerf.NeRF(D=8, W=256, output_ch=5, skips=[4], use_viewdirs=False), O.make_params(31, output_ch=5),
+             T(g["mlp/pts"]), None),
+            ("wide156", lambda: nerf.NeRF(D=8, W=256, output_ch=5, skips=[4], use_viewdirs=True, multires=15, multires_views=6),
+             O.make_params(41, input_ch=93, input_ch_views=39), T(g["mlp156/pts"]), T(g["mlp156/viewdirs"]))):
+        m = mk()
+        m.load_state_dict(params, strict=True)
+        m = m.cuda()
+        assert m.precision == "fp32"
+        raw = m(pts.cuda(), None if vd is None else vd.cuda())
+        (raw * cuda(g["grad/%s/G" % tag])).sum().backward()
+        n = 0
+        for k, t in m.named_parameters():
+            key = "grad/%s/ghead/%s" % (tag, k)
+            if key not in g:
+                continue
+            e = T(g[key])
+            rel = float((t.grad.reshape(-1)[:512].cpu() - e).norm() / (e.norm() + 1e-30))
+            assert rel <= 2e-4, (tag, k, rel)
+            n += 1
+        assert n >= 18
+    # oracle autograd at ragged sizes (not multiples of the 64-row GEMM tile)
+    for out_ch in (5, 4):
+        m = nerf.NeRF(D=8, W=256, output_ch=out_ch, skips=[4], use_viewdirs=False)
+        params = O.make_params(60 + out_ch, output_ch=out_ch, scale=1.3)
+        m.load_state_dict(params, strict=True)
+        pts = torch.from_numpy(rng.uniform(-3, 3, size=(7, 19, 3)).astype(np.float32))
+        G = torch.from_numpy(rng.normal(size=(7, 19, out_ch)).astype(np.float32))
+        print("noview out_ch=%d worst rel grad err %.2e" % (out_ch, _grads_vs_oracle(m.cuda(), params, pts, None, G, 2e-4)))
+    # the standard view-dependent model on the fp32 path (exact-operand reference of the bf16 kernels' gradients)
+    m = make_model(13, scale=1.59, precision="fp32")
+    pts = torch.from_numpy(rng.uniform(-3, 3, size=(5, 67, 3)).astype(np.float32))
+    vd = torch.nn.functional.normalize(torch.from_numpy(rng.normal(size=(5, 3)).astype(np.float32)), dim=-1)
+    G = torch.from_numpy(rng.normal(size=(5, 67, 4)).astype(np.float32))
+    print("viewdirs fp32 worst rel grad err %.2e" % _grads_vs_oracle(m, O.make_params(13, scale=1.59), pts, vd, G, 2e-4))
+
+
+def test_noview_training_step_through_the_renderer(golden_noview):
+    """main.py:77-103 with a use_viewdirs=False coarse / fine pair (8-column ray rows, output_ch 5): loss and every
+    parameter gradient norm against the reference's."""
+    from nerf_shared_b200 import nerf, render_utils, utils
+    g = golden_noview
+    models = []
+    for seed in (31, 32):
+        m = nerf.NeRF(D=8, W=256, output_ch=5, skips=[4], use_viewdirs=False)
+        m.load_state_dict(O.make_params(seed, output_ch=5, scale=1.59), strict=True)
+        models.append(m.cuda())
+    mc, mf = models
+    r = render_utils.Renderer(perturb=0.0, N_importance=128, N_samples=64, use_viewdirs=False, white_bkgd=True,
+                              raw_noise_std=0.0, near=2.0, far=6.0)
+    r.train()
+    rays = torch.stack([cuda(g["train_noview/rays_o"]), cuda(g["train_noview/rays_d"])], 0)
+    tgt = cuda(g["train_noview/target"])
+    rgb, _, _, extras = r.render_from_rays(8, 8, O.blender_intrinsics(8, 8), chunk=32768, rays=rays, coarse_model=mc, fine_model=mf, retraw=True)
+    loss = utils.img2mse(rgb, tgt) + utils.img2mse(extras["rgb0"], tgt)
+    loss.backward()
+    assert abs(float(loss) - float(g["train_noview/loss"])) <= 1e-4 * float(g["train_noview/loss"])
+    for tag, m in (("coarse", mc), ("fine", mf)):
+        for k, p in m.named_parameters():
+            key = "train_noview/%s/gnorm/%s" % (tag, k)
+            if key in g:
+                ref_n = float(g[key])
+                assert ref_n > 0 and abs(float(p.grad.double().norm()) - ref_n) <= 2e-3 * ref_n, (tag, k)

@@ -101,8 +101,8 @@ def test_no_viewdirs_forward_and_render_golden(golden_noview):
     assert raw5.shape == (5, 24, 5) and raw4.shape == (5, 24, 4)
     assert maxabs(raw5, T(g["mlp/raw5_seed31"])) <= 3e-5
     assert maxabs(raw4, T(g["mlp/raw4_seed33"])) <= 3e-5
-    with pytest.raises(NotImplementedError):      # no backward kernels for this model: refuse instead of silently detaching
-        m5(pts, None)
+    # with gradients enabled the same call runs the fp32 training path (csrc/mlp_f32_train.cu): same values
+    assert maxabs(m5(pts, None), T(g["mlp/raw5_seed31"])) <= 3e-5
     with pytest.raises(TypeError), torch.no_grad():
         m5(pts, pts[:, 0])
     r = _renderer(use_viewdirs=False, N_importance=128, white_bkgd=True, ndc=False, near=2.0, far=6.0)

@@ -247,3 +247,29 @@ def test_pose_gradient(golden):
     loss.backward()
     np.testing.assert_allclose(loss.detach().numpy(), golden["pose/loss"], rtol=1e-5)
     np.testing.assert_allclose(pose.grad.numpy(), golden["pose/grad_pose"], rtol=2e-3, atol=1e-7)
+
+
+def test_oracle_gradients_of_the_noview_and_wide_models(golden_noview):
+    """autograd of the oracle's MLP for use_viewdirs=False (output_ch 5) and multires 15 / 6 against the reference's
+    parameter gradients (tests/golden/make_golden_noview.py: d/dtheta sum(raw * G))."""
+    import torch
+    g = golden_noview
+    cases = (("noview5", O.make_params(31, output_ch=5), torch.from_numpy(g["mlp/pts"]), None, {}),
+             ("wide156", O.make_params(41, input_ch=93, input_ch_views=39), torch.from_numpy(g["mlp156/pts"]),
+              torch.from_numpy(g["mlp156/viewdirs"]), dict(multires=15, multires_views=6)))
+    for tag, params, pts, vd, kw in cases:
+        p = {k: v.clone().requires_grad_(True) for k, v in params.items()}
+        raw = O.nerf_query(p, pts, vd, **kw)
+        (raw * torch.from_numpy(g["grad/%s/G" % tag])).sum().backward()
+        checked = 0
+        for k, v in p.items():
+            key = "grad/%s/gnorm/%s" % (tag, k)
+            if key not in g:
+                assert v.grad is None or float(v.grad.abs().max()) == 0.0, (tag, k)   # (views_linears of the noview model is unused)
+                continue
+            ref_n = float(g[key])
+            assert abs(float(v.grad.double().norm()) - ref_n) <= 1e-4 * ref_n + 1e-12, (tag, k)
+            e = torch.from_numpy(g["grad/%s/ghead/%s" % (tag, k)])
+            assert float((v.grad.reshape(-1)[:512] - e).norm()) <= 1e-4 * float(e.norm()) + 1e-9, (tag, k)
+            checked += 1
+        assert checked >= 18
