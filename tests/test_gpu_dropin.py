@@ -125,3 +125,12 @@ def test_reference_pose_demo_loop_runs_unchanged():
     finally:
         torch.set_default_tensor_type("torch.FloatTensor")
         sys.path[:] = saved_path
+
+
+def test_reference_main_py_trains_the_wide_encoding_config(tmp_path):
+    """configs/stonehenge.txt's network (multires = 15, multires_views = 6: 93- / 39-wide encodings) through the unchanged
+    main.py: the models select the fp32 kernels (forward and backward) on their own."""
+    r, logdir = _run_main(tmp_path, extra_cfg="multires = 15\nmultires_views = 6\ni_print = 2\n", n_iters=6, images_hw=40)
+    text = r.stdout + r.stderr
+    losses = [float(l.split("Loss:")[1].split()[0]) for l in text.splitlines() if "[TRAIN] Iter:" in l]
+    assert len(losses) >= 3 and all(np.isfinite(losses)), (losses, text[-1500:])
