@@ -574,3 +574,46 @@ def test_lazily_captured_graphs_draw_fresh_random_numbers():
     same_g, same_e = run(True, True), run(False, True)
     assert max(abs(a - same_g[2]) for a in same_g[2:]) <= 1e-6, same_g          # same seed -> same draws, replay after replay
     assert abs(same_g[3] - same_e[3]) <= 1e-5 * abs(same_e[3]), (same_g, same_e)   # and the uncaptured path's draws
+
+
+def test_flat_adam_skips_frozen_parameters_and_honours_cleared_grads(golden):
+    """torch.optim.Adam semantics the flat optimizer has to keep: parameters with requires_grad=False are not updated
+    (neither the weights nor their moments move), and gradients cleared with set_to_none between steps do not make the
+    optimizer discard the next backward."""
+    from nerf_shared_b200 import render_utils, utils
+    H = W = 8
+    K = O.blender_intrinsics(H, W)
+    rb = cuda(golden["rr/ray_batch"])
+    rays = torch.stack([rb[:, 0:3], rb[:, 3:6]], 0).contiguous()
+    tgt = torch.rand(rays.shape[1], 3, generator=torch.Generator().manual_seed(2)).cuda()
+
+    class A:
+        lrate = 5e-4
+    mc, mf = make_model(13, scale=1.59), make_model(14, scale=1.59)
+    opt = utils.get_optimizer(mc, mf, A())
+    r = render_utils.Renderer(perturb=0.0, N_importance=128, N_samples=64, use_viewdirs=True, white_bkgd=True,
+                              raw_noise_std=0.0, near=2.0, far=6.0)
+    r.train()
+
+    def step(clear):
+        rgb, _, _, ex = r.render_from_rays(H, W, K, chunk=32768, rays=rays, coarse_model=mc, fine_model=mf, retraw=True)
+        if clear:
+            for m in (mc, mf):
+                m.zero_grad(set_to_none=True)
+        else:
+            opt.zero_grad()
+        (utils.img2mse(rgb, tgt) + utils.img2mse(ex["rgb0"], tgt)).backward()
+        opt.step()
+
+    step(False)
+    p1 = opt.flat_p.clone()
+    step(True)                                   # p.grad = None before backward: the step must still move the weights
+    assert float((opt.flat_p - p1).abs().max()) > 1e-5
+    assert all(p.grad is not None for p in mc.parameters())
+    for p in mc.parameters():                    # freeze the coarse network
+        p.requires_grad_(False)
+    n_c = sum(p.numel() for p in mc.parameters())
+    p2, m2 = opt.flat_p.clone(), opt.exp_avg.clone()
+    step(False)
+    assert torch.equal(opt.flat_p[:n_c], p2[:n_c]) and torch.equal(opt.exp_avg[:n_c], m2[:n_c])
+    assert float((opt.flat_p[n_c:] - p2[n_c:]).abs().max()) > 1e-5
