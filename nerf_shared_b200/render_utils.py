@@ -144,34 +144,31 @@ class Renderer(torch.nn.Module):
         if viewdirs is None:
             return self._render_no_viewdirs(H, W, K, coarse_model, fine_model, chunk, rays_o, rays_d, retraw, out_shape)
         needs_grad = torch.is_grad_enabled() and any(torch.is_tensor(t) and t.requires_grad for t in (rays_o, rays_d, viewdirs))
-        if needs_grad:   # pose estimation: every step of the row construction is differentiable
+        view_src = viewdirs.reshape(-1, 3)
+        if self.ndc:             # (an autograd op when the rays carry a gradient)
+            rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
+        rays_o = rays_o.reshape(-1, 3).float().contiguous()
+        rays_d = rays_d.reshape(-1, 3).float().contiguous()
+        if self._after_coarse is None and _fused.eligible(self, coarse_model, fine_model, rays_o, rays_d, rays_d.shape[0],
+                                                          max(int(chunk), MIN_CHUNK)):
+            # a training batch (rays without gradient) or a pose-estimation batch (rays with gradient): the whole coarse +
+            # fine render as ONE autograd node, replaying lazily captured CUDA graphs where it can (_fused.py)
+            out = _fused.FusedRender.apply(self, coarse_model, fine_model, rays_o, rays_d, view_src.float().contiguous(),
+                                           *_ops.mlp_params(coarse_model), *_ops.mlp_params(fine_model))
+            rgb, disp, acc, rgb0, disp0, acc0, z_std, raw = out
+            shp = lambda t: t.reshape(out_shape + list(t.shape[1:]))
+            extras = {"rgb0": shp(rgb0), "disp0": shp(disp0), "acc0": shp(acc0), "z_std": shp(z_std)}
+            if retraw:
+                extras["raw"] = shp(raw)
+            return [shp(rgb), shp(disp), shp(acc), extras]
+        if needs_grad:   # pose estimation outside the fused node's configurations: every step is a differentiable op
             viewdirs = _ops.Normalize.apply(viewdirs).reshape(-1, 3)
-            if self.ndc:
-                rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
-            rays_o = rays_o.reshape(-1, 3).float()
-            rays_d = rays_d.reshape(-1, 3).float()
             bounds = rays_d.new_empty((rays_d.shape[0], 2))
             bounds[:, 0] = float(self.near)
             bounds[:, 1] = float(self.far)
             ray_rows = torch.cat([rays_o, rays_d, bounds, viewdirs], -1)
             parts = None
         else:            # one kernel: normalise + near/far + concatenate
-            view_src = viewdirs.reshape(-1, 3)
-            if self.ndc:
-                rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
-            rays_o = rays_o.reshape(-1, 3).float().contiguous()
-            rays_d = rays_d.reshape(-1, 3).float().contiguous()
-            if self._after_coarse is None and _fused.eligible(self, coarse_model, fine_model, rays_o, rays_d, rays_d.shape[0],
-                                                              max(int(chunk), MIN_CHUNK)):
-                # training batch: the whole coarse + fine render as one autograd node (_fused.py)
-                out = _fused.FusedRender.apply(self, coarse_model, fine_model, rays_o, rays_d, view_src.float().contiguous(),
-                                               *_ops.mlp_params(coarse_model), *_ops.mlp_params(fine_model))
-                rgb, disp, acc, rgb0, disp0, acc0, z_std, raw = out
-                shp = lambda t: t.reshape(out_shape + list(t.shape[1:]))
-                extras = {"rgb0": shp(rgb0), "disp0": shp(disp0), "acc0": shp(acc0), "z_std": shp(z_std)}
-                if retraw:
-                    extras["raw"] = shp(raw)
-                return [shp(rgb), shp(disp), shp(acc), extras]
             ray_rows, viewdirs = _ops.ray_rows(rays_o, rays_d, view_src, self.near, self.far)
             parts = (rays_o, rays_d, viewdirs)
 

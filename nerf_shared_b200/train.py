@@ -323,21 +323,25 @@ class GraphedPoseStep:
         return loss.detach(), self.pose.grad
 
     def _capture(self):
-        from . import _lib
+        from . import _fused, _lib
         dev = self.pose.device
-        side = torch.cuda.Stream(device=dev)
-        side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):
-            for _ in range(self._warmup):
-                self._step()
-        torch.cuda.current_stream(dev).wait_stream(side)
-        torch.cuda.synchronize(dev)
-        g = torch.cuda.CUDAGraph()
-        l0 = _lib.launch_count()
-        with torch.cuda.graph(g):
-            self.loss, self.grad = self._step()
-        self.launches_per_replay = _lib.launch_count() - l0
-        self.graph = g
+        lazy, _fused.GRAPHS_ENABLED = _fused.GRAPHS_ENABLED, False      # no nested captures inside this one's warm-up
+        try:
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(self._warmup):
+                    self._step()
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            g = torch.cuda.CUDAGraph()
+            l0 = _lib.launch_count()
+            with torch.cuda.graph(g):
+                self.loss, self.grad = self._step()
+            self.launches_per_replay = _lib.launch_count() - l0
+            self.graph = g
+        finally:
+            _fused.GRAPHS_ENABLED = lazy
 
     def __call__(self, pose, pix, target):
         with torch.no_grad():

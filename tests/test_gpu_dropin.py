@@ -121,7 +121,7 @@ def test_reference_pose_demo_loop_runs_unchanged():
         l0 = _lib.launch_count()
         ns["estimate_relative_pose"](mc, mf, renderer, obs, start, K, args, extra, obs_img_pose=gt, obs_img=None)
         torch.cuda.synchronize()
-        assert _lib.launch_count() - l0 >= 300 * 15          # 300 iterations ran on the library's kernels
+        assert _lib.launch_count() - l0 >= 300 * 2           # 300 iterations ran on the library (the renders replay captured graphs)
     finally:
         torch.set_default_tensor_type("torch.FloatTensor")
         sys.path[:] = saved_path

@@ -210,3 +210,34 @@ def test_graphed_pose_step_equals_the_eager_step():
         assert float(pose.grad.abs().max()) > 1e-3
         assert float((pose.grad - grad_g).abs().max()) <= 1e-4 * float(pose.grad.abs().max()), (pose.grad, grad_g)
     assert step.launches_per_replay > 10
+
+
+def test_lazy_ray_grid_equals_the_full_grid():
+    """utils.get_rays with a pose that requires grad returns lazy [H, W, 3] grids: `rays[ys, xs]` (the demo's indexing,
+    demo_est_rel_pose.py:83-84) touches only the selected pixels; values, gradients and every other use equal the
+    materialised grid."""
+    from nerf_shared_b200 import utils
+    H, W = 37, 53
+    K = O.blender_intrinsics(H, W)
+    rng = np.random.default_rng(0)
+    ys, xs = rng.integers(0, H, 200), rng.integers(0, W, 200)
+    G = torch.randn(200, 3, generator=torch.Generator().manual_seed(1)).cuda()
+    res = {}
+    for lazy in ("1", "0"):
+        import os
+        os.environ["NB_LAZY_RAYS"] = lazy
+        try:
+            pose = cuda(O.pose_spherical(31.0, -30.0, 4.0)).clone().requires_grad_(True)
+            ro, rd = utils.get_rays(H, W, K, pose)
+            assert isinstance(ro, utils.LazyRayGrid) == (lazy == "1")
+            assert tuple(ro.shape) == (H, W, 3) and ro.requires_grad
+            so, sd = ro[ys, xs], rd[ys, xs]
+            assert type(so) is torch.Tensor and tuple(so.shape) == (200, 3)
+            ((so * G).sum() + (sd * G * 2).sum()).backward()
+            full = rd.reshape(-1, 3)                       # any other use materialises the grid
+            res[lazy] = (so.detach().clone(), sd.detach().clone(), pose.grad.clone(), full.detach().clone(), float(rd.sum()))
+        finally:
+            os.environ.pop("NB_LAZY_RAYS", None)
+    a, b = res["1"], res["0"]
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1]) and torch.equal(a[3], b[3]) and a[4] == b[4]
+    assert float((a[2] - b[2]).abs().max()) <= 1e-5 * float(b[2].abs().max())
