@@ -32,6 +32,16 @@ def _lib_for(t: torch.Tensor):
     return _lib.load()
 
 
+class _Fn(torch.autograd.Function):
+    """autograd.Function whose apply() materialises lazy ray grids first: Function.apply does not go through
+    __torch_function__, so a LazyRayGrid would enter forward() as an opaque leaf and its gradient would never reach
+    the pose."""
+
+    @classmethod
+    def apply(cls, *args):
+        return super().apply(*[a._full() if isinstance(a, LazyRayGrid) else a for a in args])
+
+
 # ----------------------------------------------------------------------------------------- rays
 class GetRays(torch.autograd.Function):
     """utils.get_rays (utils.py:33-42); differentiable wrt c2w (demo_est_rel_pose.py:80-82)."""
@@ -70,7 +80,76 @@ class GetRays(torch.autograd.Function):
         return g, None, None, None, None, None, None, None
 
 
-class Normalize(torch.autograd.Function):
+import numpy as np  # noqa: E402
+
+
+class LazyRayGrid(torch.Tensor):
+    """rays_o or rays_d of a pinhole camera as a [H, W, 3] tensor that is computed on demand (see get_rays)."""
+
+    @staticmethod
+    def make(geom, c2w, which, shared):
+        t = torch.Tensor._make_wrapper_subclass(LazyRayGrid, (geom[0], geom[1], 3), dtype=torch.float32, device=c2w.device,
+                                                requires_grad=True)
+        t._nb = (geom, c2w, which, shared)
+        return t
+
+    @classmethod
+    def __torch_dispatch__(cls, func, types, args=(), kwargs=None):
+        # only reached by calls that bypass the Python API (the autograd layer is already behind us here): values only
+        unwrap = lambda a: a._full().detach() if isinstance(a, LazyRayGrid) else a
+        return func(*torch.utils._pytree.tree_map(unwrap, args), **torch.utils._pytree.tree_map(unwrap, kwargs or {}))
+
+    def _full(self):
+        geom, c2w, which, shared = self._nb
+        if "full" not in shared:
+            shared["full"] = GetRays.apply(c2w, *geom, None)
+        return shared["full"][which]
+
+    def _select(self, ys, xs):
+        geom, c2w, which, shared = self._nb
+        key = (id(ys), id(xs))
+        if shared.get("sel_key") != key:          # rays_o[ys, xs] and rays_d[ys, xs] share one launch
+            if torch.is_tensor(ys):
+                pix = (ys.to(device=c2w.device, dtype=torch.int64) * geom[1] + xs.to(device=c2w.device, dtype=torch.int64))
+            else:                              # NumPy pixel coordinates (the demo): one small host array, one copy
+                pix = torch.from_numpy(ys.astype(np.int64) * geom[1] + xs.astype(np.int64)).to(c2w.device, non_blocking=True)
+            shared["sel"] = GetRays.apply(c2w, *geom, pix.reshape(-1).contiguous())
+            shared["sel_key"], shared["sel_keep"] = key, (ys, xs)
+        return shared["sel"][which]
+
+    def __getitem__(self, idx):
+        # a Python-level slot: the [ys, xs] selection never enters torch's generic indexing path (which costs ~0.4 ms per
+        # call on a wrapper subclass with NumPy index arrays)
+        if isinstance(idx, tuple) and len(idx) == 2 and _is_int_index(idx[0]) and _is_int_index(idx[1]) \
+                and len(idx[0]) == len(idx[1]):
+            return self._select(idx[0], idx[1])
+        return self._full()[idx]
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        kwargs = kwargs or {}
+        if getattr(func, "__name__", "") == "__get__" or func in (torch.Tensor.size, torch.Tensor.dim, torch.Tensor.numel):
+            with torch._C.DisableTorchFunctionSubclass():       # metadata (shape, dtype, device, ...) lives on the wrapper
+                return func(*args, **kwargs)
+        if func is torch.Tensor.__getitem__ and isinstance(args[0], LazyRayGrid) and isinstance(args[1], tuple) \
+                and len(args[1]) == 2 and all(_is_int_index(a) for a in args[1]):
+            ys, xs = args[1]
+            if np.shape(ys) == np.shape(xs) and np.ndim(ys) == 1:
+                return args[0]._select(ys, xs)
+        with torch._C.DisableTorchFunctionSubclass():
+            unwrap = lambda a: a._full() if isinstance(a, LazyRayGrid) else a
+            args = torch.utils._pytree.tree_map(unwrap, args)
+            kwargs = torch.utils._pytree.tree_map(unwrap, kwargs)
+            return func(*args, **kwargs)
+
+
+def _is_int_index(a):
+    if torch.is_tensor(a):
+        return a.dtype in (torch.int64, torch.int32) and a.dim() == 1
+    return isinstance(a, np.ndarray) and a.dtype.kind in "iu" and a.ndim == 1
+
+
+class Normalize(_Fn):
     """v / |v| over the last dim (render_utils.py:211)."""
 
     @staticmethod
@@ -95,7 +174,7 @@ class Normalize(torch.autograd.Function):
         return dv.view(ctx.shape)
 
 
-class NdcRays(torch.autograd.Function):
+class NdcRays(_Fn):
     """utils.ndc_rays (utils.py:54-71)."""
 
     @staticmethod
@@ -144,7 +223,7 @@ def sample_coarse(ray_batch: torch.Tensor, n_samples: int, t_rand, lindisp: bool
     return (z, pts) if want_pts else z
 
 
-class RayPoints(torch.autograd.Function):
+class RayPoints(_Fn):
     """pts = o + d * z (render_utils.py:131,148)."""
 
     @staticmethod
@@ -214,7 +293,7 @@ def ray_rows(rays_o, rays_d, view_src, near, far):
     return rows, vd
 
 
-class MsePair(torch.autograd.Function):
+class MsePair(_Fn):
     """(loss, img_loss, img_loss0, psnr) of the training step: img2mse on the fine and coarse maps, their sum and
     mse2psnr of the fine term (main.py:87-99, utils.py:24,27) in one launch; one launch backward."""
 
@@ -248,7 +327,7 @@ class MsePair(torch.autograd.Function):
 
 
 # ----------------------------------------------------------------------------------- compositing
-class Composite(torch.autograd.Function):
+class Composite(_Fn):
     """Renderer.raw2outputs (render_utils.py:241-290)."""
 
     @staticmethod
@@ -404,7 +483,7 @@ def mlp_forward_tc(model, pts, viewdirs, S, save_acts=False):
     return raw, acts
 
 
-class NerfMLP(torch.autograd.Function):
+class NerfMLP(_Fn):
     """NeRF.forward (nerf.py:96-134): pts [M,3], viewdirs [M/S,3] -> raw [M,4]."""
 
     @staticmethod
@@ -492,7 +571,7 @@ def _f32_params(model):
     return [l.weight for l in pl] + [l.bias for l in pl] + [model.output_linear.weight, model.output_linear.bias], model.output_linear
 
 
-class NerfMLPf32(torch.autograd.Function):
+class NerfMLPf32(_Fn):
     """NeRF.forward with exact fp32 operands and a backward (layer-by-layer CUDA-core GEMMs, saved fp32 activations):
     encodings up to multires 15 / 6 and use_viewdirs=False models; parameter gradients only."""
 

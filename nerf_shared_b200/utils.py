@@ -81,70 +81,8 @@ def get_rays(H, W, K, c2w):
     return _ops.GetRays.apply(c2w, int(H), int(W), fx, fy, cx, cy, None)
 
 
-class LazyRayGrid(torch.Tensor):
-    """rays_o or rays_d of a pinhole camera as a [H, W, 3] tensor that is computed on demand (see get_rays)."""
+LazyRayGrid = _ops.LazyRayGrid
 
-    @staticmethod
-    def make(geom, c2w, which, shared):
-        t = torch.Tensor._make_wrapper_subclass(LazyRayGrid, (geom[0], geom[1], 3), dtype=torch.float32, device=c2w.device,
-                                                requires_grad=True)
-        t._nb = (geom, c2w, which, shared)
-        return t
-
-    @classmethod
-    def __torch_dispatch__(cls, func, types, args=(), kwargs=None):
-        # only reached by calls that bypass the Python API (the autograd layer is already behind us here): values only
-        unwrap = lambda a: a._full().detach() if isinstance(a, LazyRayGrid) else a
-        return func(*torch.utils._pytree.tree_map(unwrap, args), **torch.utils._pytree.tree_map(unwrap, kwargs or {}))
-
-    def _full(self):
-        geom, c2w, which, shared = self._nb
-        if "full" not in shared:
-            shared["full"] = _ops.GetRays.apply(c2w, *geom, None)
-        return shared["full"][which]
-
-    def _select(self, ys, xs):
-        geom, c2w, which, shared = self._nb
-        key = (id(ys), id(xs))
-        if shared.get("sel_key") != key:          # rays_o[ys, xs] and rays_d[ys, xs] share one launch
-            if torch.is_tensor(ys):
-                pix = (ys.to(device=c2w.device, dtype=torch.int64) * geom[1] + xs.to(device=c2w.device, dtype=torch.int64))
-            else:                              # NumPy pixel coordinates (the demo): one small host array, one copy
-                pix = torch.from_numpy(ys.astype(np.int64) * geom[1] + xs.astype(np.int64)).to(c2w.device, non_blocking=True)
-            shared["sel"] = _ops.GetRays.apply(c2w, *geom, pix.reshape(-1).contiguous())
-            shared["sel_key"], shared["sel_keep"] = key, (ys, xs)
-        return shared["sel"][which]
-
-    def __getitem__(self, idx):
-        # a Python-level slot: the [ys, xs] selection never enters torch's generic indexing path (which costs ~0.4 ms per
-        # call on a wrapper subclass with NumPy index arrays)
-        if isinstance(idx, tuple) and len(idx) == 2 and _is_int_index(idx[0]) and _is_int_index(idx[1]) \
-                and len(idx[0]) == len(idx[1]):
-            return self._select(idx[0], idx[1])
-        return self._full()[idx]
-
-    @classmethod
-    def __torch_function__(cls, func, types, args=(), kwargs=None):
-        kwargs = kwargs or {}
-        if getattr(func, "__name__", "") == "__get__" or func in (torch.Tensor.size, torch.Tensor.dim, torch.Tensor.numel):
-            with torch._C.DisableTorchFunctionSubclass():       # metadata (shape, dtype, device, ...) lives on the wrapper
-                return func(*args, **kwargs)
-        if func is torch.Tensor.__getitem__ and isinstance(args[0], LazyRayGrid) and isinstance(args[1], tuple) \
-                and len(args[1]) == 2 and all(_is_int_index(a) for a in args[1]):
-            ys, xs = args[1]
-            if np.shape(ys) == np.shape(xs) and np.ndim(ys) == 1:
-                return args[0]._select(ys, xs)
-        with torch._C.DisableTorchFunctionSubclass():
-            unwrap = lambda a: a._full() if isinstance(a, LazyRayGrid) else a
-            args = torch.utils._pytree.tree_map(unwrap, args)
-            kwargs = torch.utils._pytree.tree_map(unwrap, kwargs)
-            return func(*args, **kwargs)
-
-
-def _is_int_index(a):
-    if torch.is_tensor(a):
-        return a.dtype in (torch.int64, torch.int32) and a.dim() == 1
-    return isinstance(a, np.ndarray) and a.dtype.kind in "iu" and a.ndim == 1
 
 
 def get_rays_at(H, W, K, c2w, pix):
