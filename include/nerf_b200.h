@@ -145,6 +145,23 @@ NB_API int nb_composite_train(const float* raw, const float* z, const float* ray
  * to zero for the next step.  replaces: main.py:87-99 (loss sum, mse2psnr utils.py:27). */
 NB_API int nb_loss_finalize(float* acc_fine, float* acc_coarse, float* out4, void* stream);
 
+/* ---- the inference path as one call ---------------------------------------------------------------------------- */
+/* replaces: Renderer.render_rays render_utils.py:67-174 under torch.no_grad() (ray rows, stratified depths, coarse MLP,
+ * compositing, inverse-CDF resampling + merge, fine points, fine MLP, compositing) for one chunk of rays: the kernels of
+ * the per-stage entry points, issued back to back on `stream` on a caller-provided workspace
+ * (nb_render_rays_workspace_bytes, 256-byte aligned); results are bit-identical to the per-stage sequence.
+ * packed_*: nb_mlp_pack blobs (packed_fine NULL: the coarse network is reused, render_utils.py:156); t_vals / u_det:
+ * linspace(0,1,S) / linspace(0,1,I); t_rand [n,S], u [n,I], noise_c [n,S], noise_f [n,S+I]: the caller's random draws
+ * (noise already scaled by raw_noise_std) or NULL.  Outputs may be NULL; raw_out [n,S+I,4] NULL keeps raw in the workspace.
+ * I = 0: coarse pass only, its maps in rgb / disp / acc. */
+NB_API int64_t nb_render_rays_workspace_bytes(int64_t n, int S, int I);
+NB_API int nb_render_rays_fwd(const void* packed_coarse, const void* packed_fine, int L_pts, int L_dirs, const float* rays_o,
+                              const float* rays_d, const float* view_src, float near_, float far_, int64_t n, int S, int I,
+                              const float* t_vals, const float* t_rand, const float* u_det, const float* u,
+                              const float* noise_c, const float* noise_f, int lindisp, int white_bkgd, void* workspace,
+                              int64_t workspace_bytes, float* rgb, float* disp, float* acc, float* rgb0, float* disp0,
+                              float* acc0, float* z_std, float* raw_out, void* stream);
+
 /* ---- frame output ------------------------------------------------------------------------ */
 /* out[i] = (uint8)(255 * clip(x[i], 0, 1)), NumPy's truncating cast.  replaces: utils.to8b utils.py:30 (host NumPy) in
  * render_path / render_from_batch_poses (utils.py:330-357, render_utils.py:293-319). */

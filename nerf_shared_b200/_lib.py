@@ -47,6 +47,9 @@ SIGNATURES = {
     "nb_normalize_fwd": (i32, [vp, i64, vp, vp]),
     "nb_ray_rows": (i32, [vp, vp, vp, f32, f32, i64, vp, vp, vp]),
     "nb_to8b": (i32, [vp, i64, vp, vp]),
+    "nb_render_rays_workspace_bytes": (i64, [i64, i32, i32]),
+    "nb_render_rays_fwd": (i32, [vp, vp, i32, i32, vp, vp, vp, f32, f32, i64, i32, i32, vp, vp, vp, vp, vp, vp, i32, i32, vp, i64,
+                                 vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "nb_composite_train": (i32, [vp, vp, vp, vp, vp, i64, i32, i32, f32, vp, vp, vp, vp, vp, vp, vp]),
     "nb_loss_finalize": (i32, [vp, vp, vp, vp]),
     "nb_mse_pair_fwd": (i32, [vp, vp, vp, i64, vp, vp]),

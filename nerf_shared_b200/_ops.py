@@ -638,3 +638,47 @@ def mlp_f32_trainable(model, pts, viewdirs, S):
                                   "(pose / input gradients: use the tensor-core path, precision='bf16')")
     ps, _ = _f32_params(model)
     return NerfMLPf32.apply(pts, viewdirs, S, model, *ps)
+
+
+# ------------------------------------------------------------------------ inference: Renderer.render_rays as one C-ABI call
+def tc_model_ok(m):
+    """The tensor-core kernels' configuration (every shipped config but stonehenge's 15 / 6 encodings)."""
+    return (getattr(m, "use_viewdirs", False) and m.precision == "bf16" and m.D == 8 and m.W == 256 and list(m.skips) == [4]
+            and m.i_embed == 0 and m.multires <= 10 and m.multires_views <= 4)
+
+
+def render_rays_inference(r, coarse, fine, rays_o, rays_d, view_src, step, retraw):
+    """All rays of a render() call through nb_render_rays_fwd, `step` rays per call, outputs written straight into the
+    full-size result tensors (no per-chunk concatenation).  Random draws come from the renderer's hooks in the reference's
+    order per chunk: t_rand, coarse noise, u, fine noise."""
+    lib = _lib_for(rays_o)
+    o, d, v = f32c(rays_o), f32c(rays_d), f32c(view_src)
+    n, dev = o.shape[0], o.device
+    S, I = int(r.N_samples), int(r.N_importance)
+    F = S + I
+    f = lambda *shape: torch.empty(shape, device=dev, dtype=torch.float32)
+    rgb, disp, acc = f(n, 3), f(n), f(n)
+    rgb0, disp0, acc0, z_std = (f(n, 3), f(n), f(n), f(n)) if I > 0 else (None, None, None, None)
+    raw = f(n, F, 4) if retraw else None
+    pc = packed_weights(coarse)
+    pf = packed_weights(fine) if (fine is not None and I > 0) else None
+    L, Lv = int(coarse.multires), int(coarse.multires_views)
+    step = max(1, min(int(step), n))
+    ws_bytes = int(lib.nb_render_rays_workspace_bytes(step, S, I))
+    ws = torch.empty((ws_bytes,), device=dev, dtype=torch.uint8)
+    sl = lambda t, b, e: None if t is None else t[b:e]
+    with torch.cuda.device(dev):
+        for b in range(0, n, step):
+            e = min(b + step, n)
+            m = e - b
+            t_rand = f32c(r._uniform((m, S), dev, "t_rand")) if r.perturb > 0.0 else None
+            noise_c = f32c(r._normal((m, S), dev, "noise_c") * r.raw_noise_std) if r.raw_noise_std > 0.0 else None
+            u = f32c(r._uniform((m, I), dev, "u")) if (I > 0 and r.perturb != 0.0) else None
+            noise_f = f32c(r._normal((m, F), dev, "noise_f") * r.raw_noise_std) if (I > 0 and r.raw_noise_std > 0.0) else None
+            check(lib.nb_render_rays_fwd(ptr(pc), ptr(pf), L, Lv, ptr(o[b:e]), ptr(d[b:e]), ptr(v[b:e]), float(r.near), float(r.far),
+                                         m, S, I, ptr(linspace01(S, dev)), ptr(t_rand), ptr(linspace01(I, dev)) if I > 0 else None,
+                                         ptr(u), ptr(noise_c), ptr(noise_f), int(bool(r.lindisp)), int(bool(r.white_bkgd)), ptr(ws),
+                                         ws_bytes, ptr(sl(rgb, b, e)), ptr(sl(disp, b, e)), ptr(sl(acc, b, e)), ptr(sl(rgb0, b, e)),
+                                         ptr(sl(disp0, b, e)), ptr(sl(acc0, b, e)), ptr(sl(z_std, b, e)), ptr(sl(raw, b, e)),
+                                         stream_ptr()), "nb_render_rays_fwd")
+    return rgb, disp, acc, rgb0, disp0, acc0, z_std, raw

@@ -149,6 +149,20 @@ class Renderer(torch.nn.Module):
             rays_o, rays_d = utils.ndc_rays(H, W, K[0][0], 1.0, rays_o, rays_d)
         rays_o = rays_o.reshape(-1, 3).float().contiguous()
         rays_d = rays_d.reshape(-1, 3).float().contiguous()
+        no_grads = not (torch.is_grad_enabled() and (needs_grad or any(p.requires_grad for p in coarse_model.parameters())
+                                                     or (fine_model is not None and any(p.requires_grad for p in fine_model.parameters()))))
+        if (no_grads and self._after_coarse is None and _ops.tc_model_ok(coarse_model) and rays_d.shape[0] > 0
+                and (fine_model is None or _ops.tc_model_ok(fine_model)) and (self.N_importance > 0 or not retraw) and os.environ.get("NB_FUSED_INFERENCE", "1") != "0"):
+            # inference: every chunk of rays is ONE C-ABI call (nb_render_rays_fwd), results land in the full-size outputs
+            rgb, disp, acc, rgb0, disp0, acc0, z_std, raw = _ops.render_rays_inference(
+                self, coarse_model, fine_model, rays_o, rays_d, view_src.float().contiguous(), max(int(chunk), MIN_CHUNK), retraw)
+            shp = lambda t: t.reshape(out_shape + list(t.shape[1:]))
+            extras = {}
+            if rgb0 is not None:
+                extras = {"rgb0": shp(rgb0), "disp0": shp(disp0), "acc0": shp(acc0), "z_std": shp(z_std)}
+            if retraw:
+                extras["raw"] = shp(raw)
+            return [shp(rgb), shp(disp), shp(acc), extras]
         if self._after_coarse is None and _fused.eligible(self, coarse_model, fine_model, rays_o, rays_d, rays_d.shape[0],
                                                           max(int(chunk), MIN_CHUNK)):
             # a training batch (rays without gradient) or a pose-estimation batch (rays with gradient): the whole coarse +

@@ -217,3 +217,31 @@ def test_full_size_llff_ndc_render_sampled_against_oracle():
     assert maxabs(extras["rgb0"].reshape(-1, 3)[sel].cpu(), ref["rgb0"]) <= 2e-3
     assert maxabs(rgb.reshape(-1, 3)[sel].cpu(), ref["rgb_map"]) <= 2e-3
     assert maxabs(acc.reshape(-1)[sel].cpu(), ref["acc_map"]) <= 2e-3
+
+
+@pytest.mark.parametrize("kw", [dict(perturb=0.0, raw_noise_std=0.0), dict(perturb=1.0, raw_noise_std=1.0, white_bkgd=False, lindisp=True)])
+def test_fused_inference_entry_equals_per_stage_path(kw):
+    """nb_render_rays_fwd (Renderer.render under no_grad: one C-ABI call per chunk of rays, outputs written into the
+    full-size maps) against the per-stage entry points (NB_FUSED_INFERENCE=0) on a 640 x 600 frame = two chunks: the same
+    bits, with the same random draws when sampling is random."""
+    import os
+    mc, mf = make_model(13, scale=1.59), make_model(14, scale=1.59)
+    H, W = 600, 640
+    K = O.blender_intrinsics(H, W)
+    c2w = cuda(O.pose_spherical(33.0, -30.0, 4.0))[:3, :4]
+    out = {}
+    for fused in ("1", "0"):
+        os.environ["NB_FUSED_INFERENCE"] = fused
+        try:
+            r = _renderer(**kw)
+            torch.manual_seed(5)
+            torch.cuda.manual_seed(5)
+            with torch.no_grad():
+                rgb, disp, acc, extras = r.render(H, W, K, mc, mf, chunk=32768, c2w=c2w, retraw=True)
+            out[fused] = (rgb, disp, acc, extras["rgb0"], extras["acc0"], extras["z_std"], extras["raw"])
+        finally:
+            os.environ.pop("NB_FUSED_INFERENCE", None)
+    assert out["1"][0].shape == (H, W, 3) and out["1"][6].shape == (H, W, 192, 4)
+    for a, b in zip(out["1"], out["0"]):
+        assert torch.equal(a.nan_to_num(), b.nan_to_num())
+    assert float(out["1"][2].max()) > 0.5          # the fixture is not a blank frame
