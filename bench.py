@@ -815,8 +815,13 @@ def run_reference(a):
 
 if __name__ == "__main__":
     a = parse()
-    _real_stdout = sys.stdout
-    sys.stdout = sys.stderr          # the library prints its configuration; stdout carries ONE JSON line
+    # stdout carries ONE JSON line: Python-level prints (the library prints its configuration) AND C-level writes to fd 1
+    # (NCCL prints its version banner there at N > 1) go to stderr; the JSON line goes to the original stdout
+    sys.stdout.flush()
+    _json_fd = os.dup(1)
+    os.dup2(2, 1)
+    _real_stdout = os.fdopen(_json_fd, "w")
+    sys.stdout = sys.stderr
     if a.impl == "reference":
         run_reference(a)
     else:
