@@ -236,6 +236,14 @@ NB_API int nb_mlp_bwd_tc(const void* packed_bwd, int L_pts, int L_dirs, const vo
  * gradients from acts / dA / d_raw), so that a caller can put other work between them or on another stream. */
 NB_API int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
                         void* dA, const int64_t* grad_off_host24, float* grads, int parts, void* stream);
+/* Streamed backward: the dgrad chain on `dgrad_clusters` CTA pairs and, beside it on a library-owned auxiliary stream,
+ * the weight-gradient kernel on `wgrad_ctas` CTAs consuming every tile's activation gradients as soon as the chain has
+ * written them (per-tile arrival counters in `ready`: [ceil(M/128)] ints, zeroed by the call) -- from L2 instead of HBM.
+ * 0 for either count = the default split (37 pairs / 74 CTAs).  Same results as nb_mlp_bwd_tc up to the order of the
+ * gradient atomics; the call returns with `stream` waiting for both kernels. */
+NB_API int nb_mlp_bwd_tc_streamed(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
+                           void* dA, const int64_t* grad_off_host24, float* grads, int* ready, int dgrad_clusters,
+                           int wgrad_ctas, void* stream);
 
 /* Gradient wrt the MLP's INPUTS from the dA tiles nb_mlp_bwd_tc left behind (pose estimation:
  * demo_est_rel_pose.py:87-97 backpropagates through frozen weights to the sample positions and view

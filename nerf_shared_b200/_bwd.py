@@ -91,8 +91,16 @@ def mlp_backward(model, pts, viewdirs, acts, S, g_raw, need_in, need_param, pack
     d_pts = d_vd = None
     with torch.cuda.device(dev):
         # frozen weights (grads == NULL): only the dgrad chain runs (pose estimation, demo_est_rel_pose.py:375)
-        check(lib.nb_mlp_bwd_tc(ptr(packed_bwd), L, Lv, ptr(acts), ptr(g), M, ptr(dA), off_arr, ptr(grads), stream_ptr()),
-              "nb_mlp_bwd_tc")
+        import os
+        stream_min = int(os.environ.get("NB_STREAM_BWD", "0"))       # samples from which dgrad and wgrad run side by side
+        if stream_min > 0 and grads is not None and M >= stream_min:
+            ready = torch.empty(((M + 127) // 128,), device=dev, dtype=torch.int32)
+            check(lib.nb_mlp_bwd_tc_streamed(ptr(packed_bwd), L, Lv, ptr(acts), ptr(g), M, ptr(dA), off_arr, ptr(grads), ptr(ready),
+                                             int(os.environ.get("NB_STREAM_DGRAD", "0")), int(os.environ.get("NB_STREAM_WGRAD", "0")),
+                                             stream_ptr()), "nb_mlp_bwd_tc_streamed")
+        else:
+            check(lib.nb_mlp_bwd_tc(ptr(packed_bwd), L, Lv, ptr(acts), ptr(g), M, ptr(dA), off_arr, ptr(grads), stream_ptr()),
+                  "nb_mlp_bwd_tc")
         if need_in:
             d_pts = torch.empty((M, 3), device=dev, dtype=torch.float32)
             d_vd = torch.zeros((M // S, 3), device=dev, dtype=torch.float32)

@@ -79,6 +79,7 @@ SIGNATURES = {
     "nb_mlp_da_bytes": (i64, [i64]),
     "nb_mlp_bwd_tc": (i32, [vp, i32, i32, vp, vp, i64, vp, C.POINTER(i64), vp, vp]),
     "nb_mlp_bwd_tc_parts": (i32, [vp, i32, i32, vp, vp, i64, vp, C.POINTER(i64), vp, i32, vp]),
+    "nb_mlp_bwd_tc_streamed": (i32, [vp, i32, i32, vp, vp, i64, vp, C.POINTER(i64), vp, vp, i32, i32, vp]),
     "nb_mlp_ingrad_packed_bytes": (i64, [i32, i32]),
     "nb_mlp_pack_ingrad": (i32, [C.POINTER(NbMlpWeights), vp, vp]),
     "nb_mlp_bwd_inputs": (i32, [vp, i32, i32, vp, vp, vp, i64, i32, vp, vp, vp]),

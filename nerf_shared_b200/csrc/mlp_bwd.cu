@@ -132,7 +132,7 @@ constexpr int kBwdThreads = 640;  // 4 control warps + 16 epilogue warps (see ml
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
     mlp_dgrad_kernel(const __grid_constant__ CUtensorMap wmap, const uint8_t* __restrict__ blob,
                      const uint8_t* __restrict__ acts, const float* __restrict__ d_raw, int64_t M,
-                     uint8_t* __restrict__ dA, int num_quads) {
+                     uint8_t* __restrict__ dA, int num_quads, int* __restrict__ ready) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
@@ -318,6 +318,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
         if (step < 8 && lane == 0) mbar_arrive_remote(act_leader);
         flush(2 * h, dst_slab + 2 * h, 2);
       }
+      // streamed backward: this warp's share of the tile's dA has landed in global memory -> one of the tile's eight
+      // arrivals; the weight-gradient kernel running beside this one picks the tile up while it is still in L2
+      if (ready != nullptr && dt != nullptr && lane == 0) {
+        bulk_wait_all();
+        __threadfence();
+        atomicAdd(ready + tile, 1);
+      }
     }
     if (lane == 0) bulk_wait_all();
   }
@@ -386,9 +393,33 @@ __device__ __forceinline__ void red_add_v4(float* p, uint32_t a, uint32_t b, uin
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 
-__global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit split, const uint8_t* __restrict__ acts,
+// Streamed form (STREAM = true): the kernel runs BESIDE the dgrad chain on its own SMs and consumes dA tiles in the
+// order the chain produces them, while they are still in L2.  Every CTA owns ONE job (layer block) and every
+// parts[job]-th tile of it (CTAs per job in proportion to the blocks the job streams), so each job's accumulator is
+// still flushed once per CTA; the producer warp waits for a tile's eight arrivals in `ready` before it issues the loads.
+struct WStream {
+  unsigned char job[kNumSMs];    // job of CTA b
+  unsigned char part[kNumSMs];   // its first tile
+  unsigned char parts[kNumWJobs];  // CTAs working on the job = tile stride
+};
+template <bool STREAM>
+__device__ __forceinline__ void wgrad_range(const WSplit& sp, const WStream& ws, const WJob& j, int ji, int num_tiles, int& tb,
+                                            int& te, int& ts) {
+  if (STREAM) {
+    const bool mine = ws.job[blockIdx.x] == ji;
+    tb = mine ? (int)ws.part[blockIdx.x] : 0;
+    te = mine ? num_tiles : 0;
+    ts = mine ? (int)ws.parts[ji] : 1;
+  } else {
+    wgrad_unit(sp, j, ji, num_tiles, tb, te);
+    ts = 1;
+  }
+}
+
+template <bool STREAM>
+__global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit split, WStream ws, const uint8_t* __restrict__ acts,
                                                            const uint8_t* __restrict__ dA, int num_tiles,
-                                                           float* __restrict__ grads) {
+                                                           float* __restrict__ grads, const int* __restrict__ ready) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
@@ -418,10 +449,22 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
     uint32_t stage = 0, phase = 0;
     for (int ji = 0; ji < kNumWJobs; ++ji) {
       const WJob& j = jobs.job[ji];
-      int t0, t1;
-      wgrad_unit(split, j, ji, num_tiles, t0, t1);
+      int t0, t1, ts;
+      wgrad_range<STREAM>(split, ws, j, ji, num_tiles, t0, t1, ts);
       const int na = j.m_blocks * 2, nb_ = j.n_cols / 64;
-      for (int t = t0; t < t1; ++t) {
+      for (int t = t0; t < t1; t += ts) {
+        if (STREAM) {   // the dgrad chain has written this tile (8 epilogue warps): acquire, then order the async-proxy loads
+          long long spins = 0;
+          int seen;
+          do {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(ready + t) : "memory");
+            if (seen < 8) {
+              if (++spins > (1ll << 24)) __trap();   // seconds: the producer kernel is gone
+              __nanosleep(200);
+            }
+          } while (seen < 8);
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         const uint8_t* da_t = dA + (size_t)t * kDaSlabs * kSlabBytes + (size_t)j.a_slab * kSlabBytes;
         const uint8_t* ac_t = acts + (size_t)t * kActSlabs * kSlabBytes + (size_t)j.b_slab * kSlabBytes;
         for (int half = 0; half < 2; ++half) {
@@ -445,8 +488,8 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
     const uint64_t desc0 = make_desc_mnmajor_sw128(0, 8192);
     for (int ji = 0; ji < kNumWJobs; ++ji) {
       const WJob& j = jobs.job[ji];
-      int t0, t1;
-      wgrad_unit(split, j, ji, num_tiles, t0, t1);
+      int t0, t1, ts;
+      wgrad_range<STREAM>(split, ws, j, ji, num_tiles, t0, t1, ts);
       if (t0 >= t1) continue;
       const int na = j.m_blocks * 2;
       const uint32_t idesc = make_idesc_bf16_mn(128, j.n_cols);
@@ -457,7 +500,7 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
       }
       first_unit = false;
       uint32_t acc = 0;
-      for (int t = t0; t < t1; ++t) {
+      for (int t = t0; t < t1; t += ts) {
         for (int half = 0; half < 2; ++half) {
           mbar_wait(bar_full + 8 * stage, phase);
           tc_fence_after();
@@ -473,7 +516,7 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
               umma_bf16(d, ad + 3 * (2048 >> 4), bd0 + 3 * (2048 >> 4), idesc, 1);
             }
             umma_commit(bar_empty + 8 * stage);
-            if (t == t1 - 1 && half == 1) umma_commit(bar_acc);
+            if (t + ts >= t1 && half == 1) umma_commit(bar_acc);
           }
           __syncwarp();
           acc = 1;
@@ -487,8 +530,8 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
     uint32_t par_acc = 0;
     for (int ji = 0; ji < kNumWJobs; ++ji) {
       const WJob j = jobs.job[ji];
-      int t0, t1;
-      wgrad_unit(split, j, ji, num_tiles, t0, t1);
+      int t0, t1, ts;
+      wgrad_range<STREAM>(split, ws, j, ji, num_tiles, t0, t1, ts);
       if (t0 >= t1) continue;
       mbar_wait(bar_acc, par_acc);
       par_acc ^= 1;
@@ -523,12 +566,12 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
     uint32_t stage = 0, phase = 0;
     for (int ji = 0; ji < kNumWJobs; ++ji) {
       const WJob j = jobs.job[ji];
-      int t0, t1;
-      wgrad_unit(split, j, ji, num_tiles, t0, t1);
+      int t0, t1, ts;
+      wgrad_range<STREAM>(split, ws, j, ji, num_tiles, t0, t1, ts);
       if (t0 >= t1) continue;
       const bool mine = j.bias_off >= 0 && c < j.m_blocks * 16;
       float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int st = 2 * (t1 - t0); st > 0; --st) {
+      for (int st = 2 * ((t1 - t0 + ts - 1) / ts); st > 0; --st) {
         mbar_wait(bar_full + 8 * stage, phase);
         if (mine) {
           const uint32_t blk = base + stage * kWStageBytes + (c >> 3) * 8192;
@@ -786,7 +829,9 @@ __global__ void __launch_bounds__(128, 1) umma_mn_selftest_kernel(const float* _
 int init_mlp_bwd(int) {
   cudaError_t e = cudaFuncSetAttribute(mlp_dgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBSmemBytes);
   if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemBytes);
+    e = cudaFuncSetAttribute(mlp_wgrad_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemBytes);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(mlp_wgrad_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemBytes);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(mlp_small_grads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kHgSmemBytes);
   if (e == cudaSuccess)
@@ -821,6 +866,57 @@ static int build_pack_args_t(const NbMlpWeights* w, PackArgsT& a) {
       for (int nh = 0; nh < 2; ++nh) a.slab[s++] = SlabSrcT{mat, ld, in_base + nh * 128, ks * 64, kout - ks * 64 < 64 ? kout - ks * 64 : 64};
   }
   return s == kBwdSlabs ? 0 : NB_E_ARG;
+}
+
+// the twelve weight-gradient jobs (layer blocks) and the cost axis of the static split
+static int build_wjobs(const int64_t* off, int in_ch, int in_views, WJobs& jobs, WSplit& split) {
+  int n = 0;
+  jobs.job[n++] = WJob{0, 2, kActSlabEncP, 64, in_ch, in_ch, off[0], off[8]};                // pts_linears[0] (+ its bias)
+  for (int l = 1; l < 8; ++l) {
+    if (l == 5) {
+      jobs.job[n++] = WJob{20, 2, 16, 256, 256, 256 + in_ch, off[5] + in_ch, off[13]};         // W5[:, in_ch:]  (h4)
+      jobs.job[n++] = WJob{20, 2, kActSlabEncP, 64, in_ch, 256 + in_ch, off[5], -1};           // W5[:, :in_ch]  (enc)
+    } else {
+      jobs.job[n++] = WJob{4 * l, 2, 4 * (l - 1), 256, 256, 256, off[l], off[8 + l]};
+    }
+  }
+  jobs.job[n++] = WJob{kDaSlabFeat, 2, 28, 256, 256, 256, off[16], off[17]};                   // feature_linear (h7)
+  jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabFeat, 256, 256, 256 + in_views, off[20], off[21]};  // views[:, :256] (feature)
+  jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabEncD, 64, in_views, 256 + in_views, off[20] + 256, -1};  // views[:, 256:]
+  if (n != kNumWJobs) return -1;
+  split.cum[0] = 0;
+  for (int i = 0; i < kNumWJobs; ++i) split.cum[i + 1] = split.cum[i] + jobs.job[i].m_blocks * 2 + jobs.job[i].n_cols / 64;
+  return 0;
+}
+
+static int launch_small_grads(const int64_t* off, const void* acts, const float* d_raw, int64_t M, int64_t tiles, float* grads,
+                              cudaStream_t st) {
+  SmallOffsets o;
+  for (int l = 0; l < 8; ++l) o.pts_b[l] = off[8 + l];
+  o.feature_b = off[17]; o.views_b = off[21]; o.alpha_w = off[18]; o.alpha_b = off[19];
+  o.rgb_w = off[22]; o.rgb_b = off[23];
+  NB_REQUIRE(((uintptr_t)d_raw & 15) == 0, "nb_mlp_bwd_tc: d_raw must be 16-byte aligned");
+  const int grid = (int)(tiles < kNumSMs ? tiles : kNumSMs);
+  mlp_small_grads_kernel<<<grid, 288, kHgSmemBytes, st>>>((const uint8_t*)acts, d_raw, M, (int)tiles, o, grads);
+  return check_launch("mlp_small_grads_kernel");
+}
+
+// per-device auxiliary stream + events of the streamed backward (library-owned state, created lazily)
+struct AuxStream {
+  cudaStream_t s = nullptr;
+  cudaEvent_t fork = nullptr, join = nullptr;
+};
+static AuxStream* aux_for_device() {
+  static AuxStream aux[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  AuxStream& a = aux[dev];
+  if (!a.s) {
+    if (cudaStreamCreateWithFlags(&a.s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&a.fork, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&a.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+  }
+  return &a;
 }
 
 }  // namespace nb
@@ -873,7 +969,7 @@ int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const voi
     int clusters = (int)(quads < kNumSMs / 2 ? quads : kNumSMs / 2);
     if (limit_mlp_clusters() > 0 && clusters > limit_mlp_clusters()) clusters = limit_mlp_clusters();
     mlp_dgrad_kernel<<<2 * clusters, kBwdThreads, kBSmemBytes, st>>>(wmap, (const uint8_t*)packed_bwd, (const uint8_t*)acts, d_raw,
-                                                             M, (uint8_t*)dA, (int)quads);
+                                                             M, (uint8_t*)dA, (int)quads, nullptr);
     rc = check_launch("mlp_dgrad_kernel");
     if (rc) return rc;
   }
@@ -883,23 +979,8 @@ int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const voi
                                          // 20 views_w, 21 views_b, 22 rgb_w, 23 rgb_b
   {
     WJobs jobs;
-    int n = 0;
-    jobs.job[n++] = WJob{0, 2, kActSlabEncP, 64, in_ch, in_ch, off[0], off[8]};                // pts_linears[0] (+ its bias)
-    for (int l = 1; l < 8; ++l) {
-      if (l == 5) {
-        jobs.job[n++] = WJob{20, 2, 16, 256, 256, 256 + in_ch, off[5] + in_ch, off[13]};         // W5[:, in_ch:]  (h4)
-        jobs.job[n++] = WJob{20, 2, kActSlabEncP, 64, in_ch, 256 + in_ch, off[5], -1};           // W5[:, :in_ch]  (enc)
-      } else {
-        jobs.job[n++] = WJob{4 * l, 2, 4 * (l - 1), 256, 256, 256, off[l], off[8 + l]};
-      }
-    }
-    jobs.job[n++] = WJob{kDaSlabFeat, 2, 28, 256, 256, 256, off[16], off[17]};                   // feature_linear (h7)
-    jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabFeat, 256, 256, 256 + in_views, off[20], off[21]};  // views[:, :256] (feature)
-    jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabEncD, 64, in_views, 256 + in_views, off[20] + 256, -1};  // views[:, 256:]
-    NB_REQUIRE(n == kNumWJobs, "internal: wgrad job table");
     WSplit split;
-    split.cum[0] = 0;
-    for (int i = 0; i < kNumWJobs; ++i) split.cum[i + 1] = split.cum[i] + jobs.job[i].m_blocks * 2 + jobs.job[i].n_cols / 64;
+    NB_REQUIRE(build_wjobs(off, in_ch, in_views, jobs, split) == 0, "internal: wgrad job table");
     // at least ~4 tiles of the average job per CTA, else fewer CTAs (the flush is a fixed cost per range)
     int64_t grid = split.cum[kNumWJobs] * tiles / (4 * (split.cum[kNumWJobs] / kNumWJobs));
     if (grid > kNumSMs) grid = kNumSMs;
@@ -923,10 +1004,11 @@ int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const voi
       at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
       cfg.attrs = at;
       cfg.numAttrs = 1;
-      cudaLaunchKernelEx(&cfg, mlp_wgrad_kernel, jobs, split, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, grads);
+      cudaLaunchKernelEx(&cfg, mlp_wgrad_kernel<false>, jobs, split, WStream{}, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, grads,
+                         (const int*)nullptr);
     } else {
-      mlp_wgrad_kernel<<<(int)grid, 384, kWSmemBytes, st>>>(jobs, split, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles,
-                                                            grads);
+      mlp_wgrad_kernel<false><<<(int)grid, 384, kWSmemBytes, st>>>(jobs, split, WStream{}, (const uint8_t*)acts, (const uint8_t*)dA,
+                                                                   (int)tiles, grads, nullptr);
     }
     int rc = check_launch("mlp_wgrad_kernel");
     if (rc) return rc;
@@ -942,6 +1024,99 @@ int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const voi
     int rc = check_launch("mlp_small_grads_kernel");
     if (rc) return rc;
   }
+  return 0;
+}
+
+// Streamed backward: the dgrad chain on `dgrad_clusters` CTA pairs and, BESIDE it on an auxiliary stream, the
+// weight-gradient kernel on `wgrad_ctas` CTAs (placed as pairs on the other TPCs) consuming each tile's activation
+// gradients as soon as the chain has written them (per-tile arrival counters in `ready`, [tiles] ints, zeroed here),
+// i.e. while they are still in L2: the weight-gradient pass reads dA from L2 instead of HBM and its bandwidth-bound time
+// overlaps the shared-memory-bound chain.  Same results as nb_mlp_bwd_tc (the accumulation order of the atomics differs).
+int nb_mlp_bwd_tc_streamed(const void* packed_bwd, int L_pts, int L_dirs, const void* acts, const float* d_raw, int64_t M,
+                           void* dA, const int64_t* grad_off_host24, float* grads, int* ready, int dgrad_clusters,
+                           int wgrad_ctas, void* stream) {
+  if (M == 0) return 0;
+  NB_REQUIRE(packed_bwd && acts && d_raw && dA && grad_off_host24 && grads && ready, "nb_mlp_bwd_tc_streamed: null pointer");
+  if (L_pts != 10 || L_dirs != 4) {
+    set_error("nb_mlp_bwd_tc_streamed: only multires=10 / multires_views=4 is instantiated (got %d, %d)", L_pts, L_dirs);
+    return NB_E_UNSUPPORTED;
+  }
+  const int in_ch = 3 + 6 * L_pts, in_views = 3 + 6 * L_dirs;
+  cudaStream_t st = as_stream(stream);
+  const int64_t tiles = (M + kTileM - 1) / kTileM;
+  const int64_t quads = (tiles + 3) / 4;
+  NB_REQUIRE(quads < (1ll << 30), "nb_mlp_bwd_tc_streamed: M too large for one launch");
+  if (dgrad_clusters <= 0) dgrad_clusters = kNumSMs / 4;          // 37 pairs
+  if (wgrad_ctas <= 0) wgrad_ctas = kNumSMs / 2;                  // 74 CTAs
+  wgrad_ctas &= ~1;
+  NB_REQUIRE(dgrad_clusters >= 1 && wgrad_ctas >= 24 && 2 * dgrad_clusters + wgrad_ctas <= kNumSMs,
+             "nb_mlp_bwd_tc_streamed: the two kernels must fit the GPU side by side (%d pairs + %d CTAs)", dgrad_clusters, wgrad_ctas);
+  AuxStream* aux = aux_for_device();
+  NB_REQUIRE(aux != nullptr, "nb_mlp_bwd_tc_streamed: could not create the auxiliary stream");
+  WJobs jobs;
+  WSplit split;
+  NB_REQUIRE(build_wjobs(grad_off_host24, in_ch, in_views, jobs, split) == 0, "internal: wgrad job table");
+  // CTAs per job in proportion to the blocks a job streams per tile (largest remainder), at least one each
+  WStream ws;
+  {
+    const int64_t total = split.cum[kNumWJobs];
+    int given = 0, cnt[kNumWJobs];
+    double rem[kNumWJobs];
+    for (int j = 0; j < kNumWJobs; ++j) {
+      const double share = (double)(split.cum[j + 1] - split.cum[j]) * wgrad_ctas / (double)total;
+      cnt[j] = (int)share < 1 ? 1 : (int)share;
+      rem[j] = share - cnt[j];
+      given += cnt[j];
+    }
+    while (given < wgrad_ctas) {
+      int best = 0;
+      for (int j = 1; j < kNumWJobs; ++j) if (rem[j] > rem[best]) best = j;
+      ++cnt[best]; rem[best] -= 1.0; ++given;
+    }
+    while (given > wgrad_ctas) {
+      int best = -1;
+      for (int j = 0; j < kNumWJobs; ++j) if (cnt[j] > 1 && (best < 0 || rem[j] < rem[best])) best = j;
+      --cnt[best]; rem[best] += 1.0; --given;
+    }
+    int b = 0;
+    for (int j = 0; j < kNumWJobs; ++j) {
+      ws.parts[j] = (unsigned char)cnt[j];
+      for (int p = 0; p < cnt[j]; ++p, ++b) { ws.job[b] = (unsigned char)j; ws.part[b] = (unsigned char)p; }
+    }
+  }
+  cudaMemsetAsync(ready, 0, sizeof(int) * (size_t)tiles, st);
+  cudaEventRecord(aux->fork, st);
+  cudaStreamWaitEvent(aux->s, aux->fork, 0);
+  {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)wgrad_ctas);
+    cfg.blockDim = dim3(384);
+    cfg.dynamicSmemBytes = kWSmemBytes;
+    cfg.stream = aux->s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, mlp_wgrad_kernel<true>, jobs, split, ws, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, grads,
+                       (const int*)ready);
+    int rc = check_launch("mlp_wgrad_kernel<stream>");
+    if (rc) return rc;
+  }
+  {
+    CUtensorMap wmap;
+    int rc = make_slab_tmap(&wmap, packed_bwd, kBwdSlabs);
+    if (rc) return rc;
+    int clusters = (int)(quads < dgrad_clusters ? quads : dgrad_clusters);
+    mlp_dgrad_kernel<<<2 * clusters, kBwdThreads, kBSmemBytes, st>>>(wmap, (const uint8_t*)packed_bwd, (const uint8_t*)acts, d_raw,
+                                                             M, (uint8_t*)dA, (int)quads, ready);
+    rc = check_launch("mlp_dgrad_kernel");
+    if (rc) return rc;
+  }
+  int rc = launch_small_grads(grad_off_host24, acts, d_raw, M, tiles, grads, aux->s);
+  if (rc) return rc;
+  cudaEventRecord(aux->join, aux->s);
+  cudaStreamWaitEvent(st, aux->join, 0);
   return 0;
 }
 

@@ -103,6 +103,23 @@ def test_wgrad_from_saved_tensors():
         assert err < 2e-3, (k, err, report)
 
 
+@pytest.mark.parametrize("n_rays,S", [(1, 64), (5, 192), (1024, 192), (1031, 64)])
+def test_streamed_backward_equals_the_two_pass_backward(n_rays, S, monkeypatch):
+    """nb_mlp_bwd_tc_streamed (dgrad chain and wgrad side by side, dA through per-tile arrival counters) against
+    nb_mlp_bwd_tc on the same saved activations: same gradients up to the order of the fp32 atomics"""
+    monkeypatch.delenv("NB_STREAM_BWD", raising=False)
+    m0, pts, vd, d_raw, _ = _run_fwd_bwd(n_rays, S, 21, keep=False)
+    base = {k: v.grad.clone() for k, v in m0.named_parameters()}
+    for rep in range(3):                                   # repeated: a missed arrival would show as a changing result
+        monkeypatch.setenv("NB_STREAM_BWD", "1")
+        m0.zero_grad(set_to_none=False)
+        m0(pts, vd).backward(d_raw)
+        torch.cuda.synchronize()
+        for k, v in m0.named_parameters():
+            e = base[k]
+            assert float((v.grad - e).norm()) <= 1e-4 * float(e.norm()) + 1e-12, (k, rep, n_rays, S)
+
+
 @pytest.mark.parametrize("n_rays,S", [(1, 64), (3, 192), (64, 64), (256, 192)])
 def test_mlp_grads_vs_fp32_autograd(n_rays, S):
     """parameter gradients of the bf16 kernels against fp32 autograd of the oracle MLP"""
