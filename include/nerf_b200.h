@@ -297,6 +297,9 @@ NB_API int nb_debug_umma(const float* A, const float* B, int K, float* D, void* 
 /* D[128,128] = A[K,128]^T * B[K,128] with both operands MN-major (the wgrad operand mode); K in {64,128}. */
 NB_API int nb_debug_umma_mn(const float* A, const float* B, int K, float* D, void* stream);
 
+/* start / end timestamps (globaltimer, ns: [2 * cta], [2 * cta + 1]) of the CTAs of the last weight-gradient launch on the
+ * current device, copied to host memory (synchronises the device); n <= 296 values.  tools/wgrad_skew.py */
+NB_API int nb_debug_wgrad_trace(unsigned long long* host_out, int n);
 /* (The tensor-pipe micro-benchmark nb_debug_umma_rate lives in csrc/umma_rate.cu and is NOT part of the default build:
  * `make EXTRA_SRCS=umma_rate.cu`; tools/umma_rate.py declares its prototype itself.) */
 

@@ -89,6 +89,7 @@ SIGNATURES = {
     "nb_train_step_prologue": (i32, [vp, f32, f32, f32, f32, i32, f32, i32, vp, vp, i64, vp, vp, i64, vp]),
     "nb_adam_step_dev": (i32, [vp, vp, vp, vp, i64, vp, vp]),
     "nb_adam_allreduce_p2p": (i32, [vp, vp, vp, i64, vp, C.POINTER(vp), C.POINTER(vp), vp, i32, i32, vp, vp]),
+    "nb_debug_wgrad_trace": (i32, [C.POINTER(C.c_uint64), i32]),
     "nb_debug_umma": (i32, [vp, vp, i32, vp, vp]),
 }
 

@@ -16,6 +16,7 @@
 //   3. small grads  (mlp_small_grads_kernel): the two CUDA-core heads (alpha_linear, rgb_linear)
 //      and their biases; one CTA per SM, whole tiles of h7 / hv / d_raw staged by bulk copies.
 #include <cuda_bf16.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -336,23 +337,38 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
 // ------------------------------------------------------------------------------------------
 // wgrad: dW[out, in] += sum_samples dA[s, out] * X[s, in]
 // ------------------------------------------------------------------------------------------
-struct WJob {
-  int a_slab;     // first dA slab (out features), m_blocks*2 consecutive slabs
-  int m_blocks;   // out features / 128
-  int b_slab;     // first activation slab (in features)
-  int n_cols;     // in features rounded up to 64 (64 or 256)
-  int n_valid;    // in features actually present
-  int ld;         // row stride of the fp32 weight gradient
-  int64_t off;    // float offset of dW[0][first in-feature] in the flat gradient buffer
-  int64_t bias_off;  // float offset of the bias gradient (column sums of this job's dA block), or -1
+// A job streams, per 64-sample stage, an A region (dA blocks: out features) and a B region (activation blocks: in
+// features), 8 KB per 64-feature block, and accumulates up to four cells: one 128-row dA block against one activation
+// segment each.  Jobs are shaped so that every stage carries 7..9 blocks -- the narrow products share a stage with a
+// wide operand instead of running as 3- and 5-block jobs that cannot keep the ring full (they ran 1.15-1.4x slower per
+// byte and held the kernel's tail: tools/wgrad_skew.py):
+//   enc job   A = dA_0 | dA_5 (8 blocks), B = encoded points (1):   dW_0 and dW_5[:, :in_ch], four 128 x 64 cells
+//   layer l   A = dA_l (4), B = h_(l-1) (4):                        two 128 x 256 cells  (l = 1..7, feature_linear)
+//   views     A = d hv (2), B = feature | encoded dirs (5):         128 x 256 and 128 x 64
+struct WCell {
+  int a_blk;     // first block of this cell's 128-row dA block inside the A region
+  int b_blk;     // first block of this cell's activation segment inside the B region
+  int n_cols;    // in features of the segment rounded up to 64 (64 or 256) = TMEM columns
+  int n_valid;   // in features actually present
+  int tcol;      // first TMEM column of the accumulator
+  int ld;        // row stride of the fp32 weight gradient
+  int64_t off;   // float offset of dW[first out feature of the block][first in feature of the segment]
 };
-constexpr int kNumWJobs = 12;
+struct WJob {
+  int a_slab[2], a_n[2];   // dA slab ranges of the A region
+  int b_slab[2], b_n[2];   // activation slab ranges of the B region
+  int n_cells;
+  int bias_blocks;         // leading A blocks whose column sums are a bias gradient (<= 4)
+  int64_t bias_off;        // float offset of that bias gradient, or -1
+  WCell cell[4];
+};
+constexpr int kNumWJobs = 10;
 struct WJobs {
   WJob job[kNumWJobs];
 };
 
 constexpr int kWStages = 3;
-constexpr uint32_t kWStageBytes = 65536;  // 64 samples x (256 + 256) features
+constexpr uint32_t kWStageBytes = 9 * 8192;  // 64 samples x up to nine 64-feature blocks
 constexpr uint32_t kWSmRed = kWStages * kWStageBytes;       // [4 sample groups][256 features] fp32 bias partials
 constexpr uint32_t kWSmBar = kWSmRed + 4096;
 constexpr uint32_t kWSmTmemPtr = kWSmBar + 120;
@@ -416,6 +432,14 @@ __device__ __forceinline__ void wgrad_range(const WSplit& sp, const WStream& ws,
   }
 }
 
+// start / end (globaltimer, ns) of every CTA of the last weight-gradient launch: nb_debug_wgrad_trace
+__device__ unsigned long long g_wgrad_trace[2 * kNumSMs];
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 template <bool STREAM>
 __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit split, WStream ws, const uint8_t* __restrict__ acts,
                                                            const uint8_t* __restrict__ dA, int num_tiles,
@@ -439,6 +463,7 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
     tmem_alloc(base + kWSmTmemPtr, 512);
     tmem_relinquish();
   }
+  if (threadIdx.x == 0 && blockIdx.x < kNumSMs) g_wgrad_trace[2 * blockIdx.x] = globaltimer_ns();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -451,7 +476,7 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
       const WJob& j = jobs.job[ji];
       int t0, t1, ts;
       wgrad_range<STREAM>(split, ws, j, ji, num_tiles, t0, t1, ts);
-      const int na = j.m_blocks * 2, nb_ = j.n_cols / 64;
+      const int na = j.a_n[0] + j.a_n[1], nb_ = j.b_n[0] + j.b_n[1];
       for (int t = t0; t < t1; t += ts) {
         if (STREAM) {   // the dgrad chain has written this tile (8 epilogue warps): acquire, then order the async-proxy loads
           long long spins = 0;
@@ -465,17 +490,19 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
           } while (seen < 8);
           asm volatile("fence.proxy.async;" ::: "memory");
         }
-        const uint8_t* da_t = dA + (size_t)t * kDaSlabs * kSlabBytes + (size_t)j.a_slab * kSlabBytes;
-        const uint8_t* ac_t = acts + (size_t)t * kActSlabs * kSlabBytes + (size_t)j.b_slab * kSlabBytes;
+        const uint8_t* da_t = dA + (size_t)t * kDaSlabs * kSlabBytes;
+        const uint8_t* ac_t = acts + (size_t)t * kActSlabs * kSlabBytes;
         for (int half = 0; half < 2; ++half) {
           mbar_wait(bar_empty + 8 * stage, phase ^ 1);
           if (elect_one()) {
             mbar_expect_tx(bar_full + 8 * stage, (na + nb_) * 8192);
-            const uint32_t dst = base + stage * kWStageBytes;
-            for (int s = 0; s < na; ++s)
-              bulk_g2s(dst + s * 8192, da_t + (size_t)s * kSlabBytes + half * 8192, 8192, bar_full + 8 * stage);
-            for (int s = 0; s < nb_; ++s)
-              bulk_g2s(dst + (na + s) * 8192, ac_t + (size_t)s * kSlabBytes + half * 8192, 8192, bar_full + 8 * stage);
+            uint32_t dst = base + stage * kWStageBytes;
+            for (int r = 0; r < 2; ++r)
+              for (int s = 0; s < j.a_n[r]; ++s, dst += 8192)
+                bulk_g2s(dst, da_t + (size_t)(j.a_slab[r] + s) * kSlabBytes + half * 8192, 8192, bar_full + 8 * stage);
+            for (int r = 0; r < 2; ++r)
+              for (int s = 0; s < j.b_n[r]; ++s, dst += 8192)
+                bulk_g2s(dst, ac_t + (size_t)(j.b_slab[r] + s) * kSlabBytes + half * 8192, 8192, bar_full + 8 * stage);
           }
           __syncwarp();
           if (++stage == kWStages) { stage = 0; phase ^= 1; }
@@ -491,8 +518,7 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
       int t0, t1, ts;
       wgrad_range<STREAM>(split, ws, j, ji, num_tiles, t0, t1, ts);
       if (t0 >= t1) continue;
-      const int na = j.m_blocks * 2;
-      const uint32_t idesc = make_idesc_bf16_mn(128, j.n_cols);
+      const int na = j.a_n[0] + j.a_n[1];
       if (!first_unit) {  // the previous unit's accumulators must be drained before they are overwritten
         mbar_wait(bar_flush, par_flush);
         par_flush ^= 1;
@@ -505,15 +531,17 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
           mbar_wait(bar_full + 8 * stage, phase);
           tc_fence_after();
           const uint32_t sa = base + stage * kWStageBytes, sb = sa + na * 8192;
-          const uint64_t ad0 = desc0 | (uint64_t)((sa & 0x3FFFFu) >> 4), bd0 = desc0 | (uint64_t)((sb & 0x3FFFFu) >> 4);
           if (elect_one()) {
-            for (int mb = 0; mb < j.m_blocks; ++mb) {
-              const uint32_t d = tmem + mb * j.n_cols;
-              const uint64_t ad = ad0 + (uint64_t)(mb * (2 * 8192 >> 4));
-              umma_bf16(d, ad, bd0, idesc, acc);
-              umma_bf16(d, ad + (2048 >> 4), bd0 + (2048 >> 4), idesc, 1);
-              umma_bf16(d, ad + 2 * (2048 >> 4), bd0 + 2 * (2048 >> 4), idesc, 1);
-              umma_bf16(d, ad + 3 * (2048 >> 4), bd0 + 3 * (2048 >> 4), idesc, 1);
+            for (int ci = 0; ci < j.n_cells; ++ci) {
+              const WCell& cl = j.cell[ci];
+              const uint32_t d = tmem + cl.tcol;
+              const uint32_t idesc = make_idesc_bf16_mn(128, cl.n_cols);
+              const uint64_t ad = desc0 | (uint64_t)(((sa + cl.a_blk * 8192) & 0x3FFFFu) >> 4);
+              const uint64_t bd = desc0 | (uint64_t)(((sb + cl.b_blk * 8192) & 0x3FFFFu) >> 4);
+              umma_bf16(d, ad, bd, idesc, acc);
+              umma_bf16(d, ad + (2048 >> 4), bd + (2048 >> 4), idesc, 1);
+              umma_bf16(d, ad + 2 * (2048 >> 4), bd + 2 * (2048 >> 4), idesc, 1);
+              umma_bf16(d, ad + 3 * (2048 >> 4), bd + 3 * (2048 >> 4), idesc, 1);
             }
             umma_commit(bar_empty + 8 * stage);
             if (t + ts >= t1 && half == 1) umma_commit(bar_acc);
@@ -536,13 +564,14 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
       mbar_wait(bar_acc, par_acc);
       par_acc ^= 1;
       tc_fence_after();
-      // 16-byte reductions where every row of this job's block starts on a 16-byte boundary
-      const bool vec = j.n_valid == j.n_cols && (j.ld & 3) == 0 && (((uintptr_t)(grads + j.off)) & 15) == 0;
-      for (int mb = 0; mb < j.m_blocks; ++mb) {
-        float* grow = grads + j.off + (size_t)(mb * 128 + row) * j.ld;
-        for (int c = 0; c < j.n_cols; c += 32) {
+      for (int ci = 0; ci < j.n_cells; ++ci) {
+        const WCell cl = j.cell[ci];
+        // 16-byte reductions where every row of this cell starts on a 16-byte boundary
+        const bool vec = cl.n_valid == cl.n_cols && (cl.ld & 3) == 0 && (((uintptr_t)(grads + cl.off)) & 15) == 0;
+        float* grow = grads + cl.off + (size_t)row * cl.ld;
+        for (int c = 0; c < cl.n_cols; c += 32) {
           uint32_t v[32];
-          tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + mb * j.n_cols + c, v);
+          tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + cl.tcol + c, v);
           tmem_ld_wait();
           if (vec) {
 #pragma unroll
@@ -550,7 +579,7 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
           } else {
 #pragma unroll
             for (int q = 0; q < 32; ++q)
-              if (c + q < j.n_valid) atomicAdd(grow + c + q, __uint_as_float(v[q]));
+              if (c + q < cl.n_valid) atomicAdd(grow + c + q, __uint_as_float(v[q]));
           }
         }
       }
@@ -569,7 +598,7 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
       int t0, t1, ts;
       wgrad_range<STREAM>(split, ws, j, ji, num_tiles, t0, t1, ts);
       if (t0 >= t1) continue;
-      const bool mine = j.bias_off >= 0 && c < j.m_blocks * 16;
+      const bool mine = j.bias_off >= 0 && c < j.bias_blocks * 8;
       float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
       for (int st = 2 * ((t1 - t0 + ts - 1) / ts); st > 0; --st) {
         mbar_wait(bar_full + 8 * stage, phase);
@@ -600,13 +629,14 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
           for (int k = 0; k < 8; ++k) red[q * 256 + c * 8 + k] = acc[k];
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        for (int f = t; f < j.m_blocks * 128; f += 128)
+        for (int f = t; f < j.bias_blocks * 64; f += 128)
           atomicAdd(grads + j.bias_off + f, red[f] + red[256 + f] + red[512 + f] + red[768 + f]);
         asm volatile("bar.sync 1, 128;" ::: "memory");
       }
     }
   }
   __syncthreads();
+  if (threadIdx.x == 0 && blockIdx.x < kNumSMs) g_wgrad_trace[2 * blockIdx.x + 1] = globaltimer_ns();
   if (warp == 2) tmem_dealloc(tmem, 512);
 }
 
@@ -868,24 +898,66 @@ static int build_pack_args_t(const NbMlpWeights* w, PackArgsT& a) {
   return s == kBwdSlabs ? 0 : NB_E_ARG;
 }
 
-// the twelve weight-gradient jobs (layer blocks) and the cost axis of the static split
+// the ten weight-gradient jobs and the cost axis of the static split
+static WJob square_job(int a_slab, int b_slab, int64_t off, int ld, int64_t bias_off) {
+  WJob j = {};
+  j.a_slab[0] = a_slab; j.a_n[0] = 4;
+  j.b_slab[0] = b_slab; j.b_n[0] = 4;
+  j.n_cells = 2;
+  j.bias_blocks = 4;
+  j.bias_off = bias_off;
+  for (int mb = 0; mb < 2; ++mb) j.cell[mb] = WCell{2 * mb, 0, 256, 256, 256 * mb, ld, off + (int64_t)mb * 128 * ld};
+  return j;
+}
 static int build_wjobs(const int64_t* off, int in_ch, int in_views, WJobs& jobs, WSplit& split) {
   int n = 0;
-  jobs.job[n++] = WJob{0, 2, kActSlabEncP, 64, in_ch, in_ch, off[0], off[8]};                // pts_linears[0] (+ its bias)
-  for (int l = 1; l < 8; ++l) {
-    if (l == 5) {
-      jobs.job[n++] = WJob{20, 2, 16, 256, 256, 256 + in_ch, off[5] + in_ch, off[13]};         // W5[:, in_ch:]  (h4)
-      jobs.job[n++] = WJob{20, 2, kActSlabEncP, 64, in_ch, 256 + in_ch, off[5], -1};           // W5[:, :in_ch]  (enc)
-    } else {
-      jobs.job[n++] = WJob{4 * l, 2, 4 * (l - 1), 256, 256, 256, off[l], off[8 + l]};
+  {  // pts_linears[0] (+ its bias) and the skip layer's encoded-points columns W5[:, :in_ch]: both multiply the encoding
+    WJob j = {};
+    j.a_slab[0] = 0; j.a_n[0] = 4;
+    j.a_slab[1] = 20; j.a_n[1] = 4;
+    j.b_slab[0] = kActSlabEncP; j.b_n[0] = 1;
+    j.n_cells = 4;
+    j.bias_blocks = 4;
+    j.bias_off = off[8];
+    for (int mb = 0; mb < 2; ++mb) {
+      j.cell[mb] = WCell{2 * mb, 0, 64, in_ch, 64 * mb, in_ch, off[0] + (int64_t)mb * 128 * in_ch};
+      j.cell[2 + mb] = WCell{4 + 2 * mb, 0, 64, in_ch, 128 + 64 * mb, 256 + in_ch, off[5] + (int64_t)mb * 128 * (256 + in_ch)};
     }
+    jobs.job[n++] = j;
   }
-  jobs.job[n++] = WJob{kDaSlabFeat, 2, 28, 256, 256, 256, off[16], off[17]};                   // feature_linear (h7)
-  jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabFeat, 256, 256, 256 + in_views, off[20], off[21]};  // views[:, :256] (feature)
-  jobs.job[n++] = WJob{kDaSlabHv, 1, kActSlabEncD, 64, in_views, 256 + in_views, off[20] + 256, -1};  // views[:, 256:]
+  for (int l = 1; l < 8; ++l) {
+    if (l == 5) jobs.job[n++] = square_job(20, 16, off[5] + in_ch, 256 + in_ch, off[13]);   // W5[:, in_ch:]  (h4)
+    else jobs.job[n++] = square_job(4 * l, 4 * (l - 1), off[l], 256, off[8 + l]);
+  }
+  jobs.job[n++] = square_job(kDaSlabFeat, 28, off[16], 256, off[17]);                       // feature_linear (h7)
+  {  // views_linears[0]: [feature | encoded dirs] against d hv
+    WJob j = {};
+    j.a_slab[0] = kDaSlabHv; j.a_n[0] = 2;
+    j.b_slab[0] = kActSlabFeat; j.b_n[0] = 4;
+    j.b_slab[1] = kActSlabEncD; j.b_n[1] = 1;
+    j.n_cells = 2;
+    j.bias_blocks = 2;
+    j.bias_off = off[21];
+    j.cell[0] = WCell{0, 0, 256, 256, 0, 256 + in_views, off[20]};
+    j.cell[1] = WCell{0, 4, 64, in_views, 256, 256 + in_views, off[20] + 256};
+    jobs.job[n++] = j;
+  }
   if (n != kNumWJobs) return -1;
+  // Cost of a job per tile = the 8 KB operand blocks it streams, times a weight in 1/64 for how fast its stages stream
+  // (7 / 8 / 9 blocks in flight per stage); NB_WGRAD_W="w7,w9" (floats) overrides the weights of the two odd shapes.
+  static int w64[10] = {0};
+  if (w64[8] == 0) {
+    double w7 = 1.0, w9 = 1.0;
+    if (const char* e = getenv("NB_WGRAD_W")) sscanf(e, "%lf,%lf", &w7, &w9);
+    for (int b = 0; b < 10; ++b) w64[b] = 64;
+    w64[7] = (int)(64 * w7 + 0.5); w64[9] = (int)(64 * w9 + 0.5);
+  }
   split.cum[0] = 0;
-  for (int i = 0; i < kNumWJobs; ++i) split.cum[i + 1] = split.cum[i] + jobs.job[i].m_blocks * 2 + jobs.job[i].n_cols / 64;
+  for (int i = 0; i < kNumWJobs; ++i) {
+    const WJob& j = jobs.job[i];
+    const int blocks = j.a_n[0] + j.a_n[1] + j.b_n[0] + j.b_n[1];
+    split.cum[i + 1] = split.cum[i] + (int64_t)blocks * w64[blocks < 10 ? blocks : 8];
+  }
   return 0;
 }
 
@@ -1117,6 +1189,16 @@ int nb_mlp_bwd_tc_streamed(const void* packed_bwd, int L_pts, int L_dirs, const 
   if (rc) return rc;
   cudaEventRecord(aux->join, aux->s);
   cudaStreamWaitEvent(st, aux->join, 0);
+  return 0;
+}
+
+int nb_debug_wgrad_trace(unsigned long long* host_out, int n) {
+  NB_REQUIRE(host_out && n >= 1 && n <= 2 * kNumSMs, "nb_debug_wgrad_trace: bad arguments");
+  cudaError_t e = cudaMemcpyFromSymbol(host_out, g_wgrad_trace, sizeof(unsigned long long) * (size_t)n);
+  if (e != cudaSuccess) {
+    set_error("nb_debug_wgrad_trace: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
   return 0;
 }
 
