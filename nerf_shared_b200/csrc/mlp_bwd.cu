@@ -352,6 +352,8 @@ struct WCell {
   int n_valid;   // in features actually present
   int tcol;      // first TMEM column of the accumulator
   int ld;        // row stride of the fp32 weight gradient
+  int scratch;   // 1: `off` is an offset into the launch's padded scratch block (rows of the real matrix are not 16-byte
+                 // aligned: the cell is reduced there with vector atomics and added to the gradient by wgrad_unpad_kernel)
   int64_t off;   // float offset of dW[first out feature of the block][first in feature of the segment]
 };
 struct WJob {
@@ -432,6 +434,36 @@ __device__ __forceinline__ void wgrad_range(const WSplit& sp, const WStream& ws,
   }
 }
 
+// Padded scratch of a launch.  Three weight matrices have rows that are not 16-byte aligned (row strides in_ch,
+// 256 + in_ch and 256 + in_views floats); scalar atomics from the ~16 CTAs of such a job, all flushing the same elements
+// at the same moment, took 40-70 us (tools/wgrad_skew.py).  Their cells are reduced into padded blocks here with vector
+// atomics, and wgrad_unpad_kernel adds the blocks to the real rows and zeroes them again.  One slot per launch, taken
+// round-robin by the host (the coarse and the fine launch of a step may overlap: consecutive launches never share a slot).
+//   [256][256] dW_5[:, in_ch:] | [256][64] dW_0 | [256][64] dW_5[:, :in_ch] | [128][256] dW_v[:, :256] | [128][64] dW_v[:, 256:]
+constexpr int kWScr5 = 0, kWScr0 = kWScr5 + 256 * 256, kWScr5e = kWScr0 + 256 * 64, kWScrV = kWScr5e + 256 * 64,
+              kWScrVd = kWScrV + 128 * 256, kWScratchFloats = kWScrVd + 128 * 64;
+constexpr int kWScratchSlots = 8;
+__device__ __align__(256) float g_wgrad_scratch[kWScratchSlots][kWScratchFloats];
+struct WUnpad {
+  int start[6];      // first scratch float of region k (start[5] = end)
+  int cols_log2[5];  // padded row length
+  int valid[5];      // real row length
+  int ld[5];         // row stride of the destination
+  int64_t off[5];    // destination of element (0, 0)
+};
+
+// adds the padded scratch cells to the real gradient rows and leaves the scratch zeroed
+__global__ void __launch_bounds__(256) wgrad_unpad_kernel(float* __restrict__ scratch, float* __restrict__ grads, WUnpad u) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= kWScratchFloats) return;
+  const float v = scratch[i];
+  scratch[i] = 0.f;
+  int k = 0;
+  while (i >= u.start[k + 1]) ++k;
+  const int e = i - u.start[k], r = e >> u.cols_log2[k], c = e & ((1 << u.cols_log2[k]) - 1);
+  if (c < u.valid[k]) atomicAdd(grads + u.off[k] + (int64_t)r * u.ld[k] + c, v);
+}
+
 // start / end (globaltimer, ns) of every CTA of the last weight-gradient launch: nb_debug_wgrad_trace
 __device__ unsigned long long g_wgrad_trace[2 * kNumSMs];
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
@@ -443,7 +475,8 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 template <bool STREAM>
 __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit split, WStream ws, const uint8_t* __restrict__ acts,
                                                            const uint8_t* __restrict__ dA, int num_tiles,
-                                                           float* __restrict__ grads, const int* __restrict__ ready) {
+                                                           float* __restrict__ grads, const int* __restrict__ ready,
+                                                           float* __restrict__ scratch) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* gbase = smem_raw + (base - smem_u32(smem_raw));
@@ -567,9 +600,13 @@ __global__ void __launch_bounds__(384, 1) mlp_wgrad_kernel(WJobs jobs, WSplit sp
       for (int ci = 0; ci < j.n_cells; ++ci) {
         const WCell cl = j.cell[ci];
         // 16-byte reductions where every row of this cell starts on a 16-byte boundary
-        const bool vec = cl.n_valid == cl.n_cols && (cl.ld & 3) == 0 && (((uintptr_t)(grads + cl.off)) & 15) == 0;
-        float* grow = grads + cl.off + (size_t)row * cl.ld;
-        for (int c = 0; c < cl.n_cols; c += 32) {
+        float* cbase = (cl.scratch ? scratch : grads) + cl.off;
+        const bool vec = (cl.scratch || cl.n_valid == cl.n_cols) && (cl.ld & 3) == 0 && (((uintptr_t)cbase) & 15) == 0;
+        float* grow = cbase + (size_t)row * cl.ld;
+        // the CTAs of a job flush the same elements at about the same time: each starts at another column chunk
+        const int nch = cl.n_cols >> 5, rot = (int)blockIdx.x;
+        for (int cc = 0; cc < nch; ++cc) {
+          const int c = ((cc + rot) & (nch - 1)) << 5;
           uint32_t v[32];
           tmem_ld32(tmem + ((uint32_t)((warp & 3) * 32) << 16) + cl.tcol + c, v);
           tmem_ld_wait();
@@ -906,7 +943,7 @@ static WJob square_job(int a_slab, int b_slab, int64_t off, int ld, int64_t bias
   j.n_cells = 2;
   j.bias_blocks = 4;
   j.bias_off = bias_off;
-  for (int mb = 0; mb < 2; ++mb) j.cell[mb] = WCell{2 * mb, 0, 256, 256, 256 * mb, ld, off + (int64_t)mb * 128 * ld};
+  for (int mb = 0; mb < 2; ++mb) j.cell[mb] = WCell{2 * mb, 0, 256, 256, 256 * mb, ld, 0, off + (int64_t)mb * 128 * ld};
   return j;
 }
 static int build_wjobs(const int64_t* off, int in_ch, int in_views, WJobs& jobs, WSplit& split) {
@@ -920,14 +957,18 @@ static int build_wjobs(const int64_t* off, int in_ch, int in_views, WJobs& jobs,
     j.bias_blocks = 4;
     j.bias_off = off[8];
     for (int mb = 0; mb < 2; ++mb) {
-      j.cell[mb] = WCell{2 * mb, 0, 64, in_ch, 64 * mb, in_ch, off[0] + (int64_t)mb * 128 * in_ch};
-      j.cell[2 + mb] = WCell{4 + 2 * mb, 0, 64, in_ch, 128 + 64 * mb, 256 + in_ch, off[5] + (int64_t)mb * 128 * (256 + in_ch)};
+      j.cell[mb] = WCell{2 * mb, 0, 64, in_ch, 64 * mb, 64, 1, kWScr0 + mb * 128 * 64};
+      j.cell[2 + mb] = WCell{4 + 2 * mb, 0, 64, in_ch, 128 + 64 * mb, 64, 1, kWScr5e + mb * 128 * 64};
     }
     jobs.job[n++] = j;
   }
   for (int l = 1; l < 8; ++l) {
-    if (l == 5) jobs.job[n++] = square_job(20, 16, off[5] + in_ch, 256 + in_ch, off[13]);   // W5[:, in_ch:]  (h4)
-    else jobs.job[n++] = square_job(4 * l, 4 * (l - 1), off[l], 256, off[8 + l]);
+    if (l == 5) {
+      jobs.job[n++] = square_job(20, 16, kWScr5, 256, off[13]);                              // W5[:, in_ch:]  (h4)
+      for (int mb = 0; mb < 2; ++mb) jobs.job[n - 1].cell[mb].scratch = 1;
+    } else {
+      jobs.job[n++] = square_job(4 * l, 4 * (l - 1), off[l], 256, off[8 + l]);
+    }
   }
   jobs.job[n++] = square_job(kDaSlabFeat, 28, off[16], 256, off[17]);                       // feature_linear (h7)
   {  // views_linears[0]: [feature | encoded dirs] against d hv
@@ -938,8 +979,8 @@ static int build_wjobs(const int64_t* off, int in_ch, int in_views, WJobs& jobs,
     j.n_cells = 2;
     j.bias_blocks = 2;
     j.bias_off = off[21];
-    j.cell[0] = WCell{0, 0, 256, 256, 0, 256 + in_views, off[20]};
-    j.cell[1] = WCell{0, 4, 64, in_views, 256, 256 + in_views, off[20] + 256};
+    j.cell[0] = WCell{0, 0, 256, 256, 0, 256, 1, kWScrV};
+    j.cell[1] = WCell{0, 4, 64, in_views, 256, 64, 1, kWScrVd};
     jobs.job[n++] = j;
   }
   if (n != kNumWJobs) return -1;
@@ -959,6 +1000,30 @@ static int build_wjobs(const int64_t* off, int in_ch, int in_views, WJobs& jobs,
     split.cum[i + 1] = split.cum[i] + (int64_t)blocks * w64[blocks < 10 ? blocks : 8];
   }
   return 0;
+}
+
+// the padded scratch slot of one weight-gradient launch (round-robin; a captured launch keeps its slot on replay)
+static int wgrad_scratch_slot(float** scratch) {
+  static unsigned next_slot = 0;
+  void* sym = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&sym, g_wgrad_scratch);   // address on the CURRENT device
+  if (e != cudaSuccess) {
+    set_error("internal: weight-gradient scratch symbol: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
+  *scratch = (float*)sym + (size_t)kWScratchFloats * (__atomic_fetch_add(&next_slot, 1u, __ATOMIC_RELAXED) % kWScratchSlots);
+  return 0;
+}
+static int launch_unpad(float* scratch, float* grads, const int64_t* off, int in_ch, int in_views, cudaStream_t st) {
+  WUnpad u;
+  const int start[6] = {kWScr5, kWScr0, kWScr5e, kWScrV, kWScrVd, kWScratchFloats};
+  for (int k = 0; k < 6; ++k) u.start[k] = start[k];
+  const int lg[5] = {8, 6, 6, 8, 6}, valid[5] = {256, in_ch, in_ch, 256, in_views};
+  const int ld[5] = {256 + in_ch, in_ch, 256 + in_ch, 256 + in_views, 256 + in_views};
+  const int64_t dst[5] = {off[5] + in_ch, off[0], off[5], off[20], off[20] + 256};
+  for (int k = 0; k < 5; ++k) { u.cols_log2[k] = lg[k]; u.valid[k] = valid[k]; u.ld[k] = ld[k]; u.off[k] = dst[k]; }
+  wgrad_unpad_kernel<<<(kWScratchFloats + 255) / 256, 256, 0, st>>>(scratch, grads, u);
+  return check_launch("wgrad_unpad_kernel");
 }
 
 static int launch_small_grads(const int64_t* off, const void* acts, const float* d_raw, int64_t M, int64_t tiles, float* grads,
@@ -1061,6 +1126,11 @@ int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const voi
       if (lim > 0 && lim < grid) grid = lim;
     }
     if (grid < 1) grid = 1;
+    float* scratch = nullptr;
+    {
+      int rc = wgrad_scratch_slot(&scratch);
+      if (rc) return rc;
+    }
     if (limit_wgrad_ctas() > 0 && grid > limit_wgrad_ctas()) {
       // SM-limited launch (a concurrent kernel owns the other SMs): CTAs are placed as pairs so that they fill whole
       // TPCs and leave the remaining TPCs free for the 2-CTA clusters of the forward / dgrad kernels
@@ -1077,12 +1147,14 @@ int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const voi
       cfg.attrs = at;
       cfg.numAttrs = 1;
       cudaLaunchKernelEx(&cfg, mlp_wgrad_kernel<false>, jobs, split, WStream{}, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, grads,
-                         (const int*)nullptr);
+                         (const int*)nullptr, scratch);
     } else {
       mlp_wgrad_kernel<false><<<(int)grid, 384, kWSmemBytes, st>>>(jobs, split, WStream{}, (const uint8_t*)acts, (const uint8_t*)dA,
-                                                                   (int)tiles, grads, nullptr);
+                                                                   (int)tiles, grads, nullptr, scratch);
     }
     int rc = check_launch("mlp_wgrad_kernel");
+    if (rc) return rc;
+    rc = launch_unpad(scratch, grads, off, in_ch, in_views, st);
     if (rc) return rc;
   }
   {
@@ -1170,9 +1242,14 @@ int nb_mlp_bwd_tc_streamed(const void* packed_bwd, int L_pts, int L_dirs, const 
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
+    float* scratch = nullptr;
+    int rc = wgrad_scratch_slot(&scratch);
+    if (rc) return rc;
     cudaLaunchKernelEx(&cfg, mlp_wgrad_kernel<true>, jobs, split, ws, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, grads,
-                       (const int*)ready);
-    int rc = check_launch("mlp_wgrad_kernel<stream>");
+                       (const int*)ready, scratch);
+    rc = check_launch("mlp_wgrad_kernel<stream>");
+    if (rc) return rc;
+    rc = launch_unpad(scratch, grads, grad_off_host24, in_ch, in_views, aux->s);
     if (rc) return rc;
   }
   {
