@@ -162,6 +162,24 @@ NB_API int nb_render_rays_fwd(const void* packed_coarse, const void* packed_fine
                               int64_t workspace_bytes, float* rgb, float* disp, float* acc, float* rgb0, float* disp0,
                               float* acc0, float* z_std, float* raw_out, void* stream);
 
+/* nb_render_rays_fwd for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, same kernels and bit-identical results as nb_render_rays_fwd, minus `workspace`: the
+ * workspace is a file-scope device array of NB_RENDER_RAYS_NOALLOC_MAX_BYTES inside the library (every GPU that loads the
+ * library holds it until the process exits; its device address is taken with cudaGetSymbolAddress once per device).  The
+ * call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).  Sizes with
+ * nb_render_rays_workspace_bytes(n, S, I) > NB_RENDER_RAYS_NOALLOC_MAX_BYTES (about 1,900 rays at S = 64, I = 128) return
+ * NB_E_ARG with a message.  All calls on a device share the array and it keeps the last call's contents; every section
+ * is rewritten in full before it is read, so nothing needs clearing -- but calls that OVERLAP on the GPU (two streams or
+ * threads on one device) race on it and must be serialised by the caller. */
+#define NB_RENDER_RAYS_NOALLOC_MAX_BYTES (16ll << 20)
+NB_API int nb_render_rays_fwd_noalloc(const void* packed_coarse, const void* packed_fine, int L_pts, int L_dirs,
+                                      const float* rays_o, const float* rays_d, const float* view_src, float near_, float far_,
+                                      int64_t n, int S, int I, const float* t_vals, const float* t_rand, const float* u_det,
+                                      const float* u, const float* noise_c, const float* noise_f, int lindisp, int white_bkgd,
+                                      float* rgb, float* disp, float* acc, float* rgb0, float* disp0, float* acc0, float* z_std,
+                                      float* raw_out, void* stream);
+
 /* ---- frame output ------------------------------------------------------------------------ */
 /* out[i] = (uint8)(255 * clip(x[i], 0, 1)), NumPy's truncating cast.  replaces: utils.to8b utils.py:30 (host NumPy) in
  * render_path / render_from_batch_poses (utils.py:330-357, render_utils.py:293-319). */

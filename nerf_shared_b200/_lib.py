@@ -50,6 +50,8 @@ SIGNATURES = {
     "nb_render_rays_workspace_bytes": (i64, [i64, i32, i32]),
     "nb_render_rays_fwd": (i32, [vp, vp, i32, i32, vp, vp, vp, f32, f32, i64, i32, i32, vp, vp, vp, vp, vp, vp, i32, i32, vp, i64,
                                  vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "nb_render_rays_fwd_noalloc": (i32, [vp, vp, i32, i32, vp, vp, vp, f32, f32, i64, i32, i32, vp, vp, vp, vp, vp, vp, i32, i32,
+                                         vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "nb_composite_train": (i32, [vp, vp, vp, vp, vp, i64, i32, i32, f32, vp, vp, vp, vp, vp, vp, vp]),
     "nb_loss_finalize": (i32, [vp, vp, vp, vp]),
     "nb_mse_pair_fwd": (i32, [vp, vp, vp, i64, vp, vp]),

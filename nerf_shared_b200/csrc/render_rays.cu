@@ -66,3 +66,71 @@ int nb_render_rays_fwd(const void* packed_coarse, const void* packed_fine, int L
 }
 
 }  // extern "C"
+
+// ---- nb_render_rays_fwd_noalloc: the same call for callers that cannot allocate --------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The workspace of nb_render_rays_fwd
+// lives in this file-scope device array: NB_RENDER_RAYS_NOALLOC_MAX_BYTES (16 MiB) on every GPU that loads the library,
+// held until the process exits.  In host code `g_render_scratch` is only a stand-in for the symbol, not a device address:
+// the address on a device comes from cudaGetSymbolAddress, taken once per device with that device current.
+static constexpr int64_t kRenderScratchBytes = 16ll << 20;
+static __device__ __align__(256) unsigned char g_render_scratch[kRenderScratchBytes];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_render_scratch_ptr[kMaxDevices];   // device address of g_render_scratch per device ordinal, NULL = not taken yet
+
+// the current device's address of the scratch array (looked up on the first call on that device, then cached)
+int render_scratch_for_current_device(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    nb::set_error("nb_render_rays_fwd_noalloc: cudaGetDevice failed or device ordinal %d out of range: %s", dev,
+                  cudaGetErrorString(e));
+    return e != cudaSuccess ? (int)e : NB_E_DEVICE;
+  }
+  void* p = __atomic_load_n(&g_render_scratch_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    e = cudaGetSymbolAddress((void**)&p, g_render_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      nb::set_error("nb_render_rays_fwd_noalloc: cudaGetSymbolAddress(g_render_scratch) on device %d: %s", dev,
+                    cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : NB_E_DEVICE;
+    }
+    __atomic_store_n(&g_render_scratch_ptr[dev], p, __ATOMIC_RELEASE);   // racing first calls store the same address
+  }
+  *out = p;
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+// Same arguments and results as nb_render_rays_fwd without `workspace` / `workspace_bytes`.  Calls no cudaMalloc / cudaFree
+// and no allocating library routine.  Every call on a device shares the one array, which keeps the previous call's
+// contents: every section of the workspace is written in full by the stage that produces it before the next stage reads
+// it (nothing has to start at zero, so nothing is cleared), but two calls that overlap on the GPU (different streams or
+// threads, same device) race on it -- serialise them.  Sizes whose workspace exceeds the array are rejected.
+int nb_render_rays_fwd_noalloc(const void* packed_coarse, const void* packed_fine, int L_pts, int L_dirs, const float* rays_o,
+                               const float* rays_d, const float* view_src, float near_, float far_, int64_t n, int S, int I,
+                               const float* t_vals, const float* t_rand, const float* u_det, const float* u,
+                               const float* noise_c, const float* noise_f, int lindisp, int white_bkgd, float* rgb, float* disp,
+                               float* acc, float* rgb0, float* disp0, float* acc0, float* z_std, float* raw_out, void* stream) {
+  if (n == 0) return 0;
+  NB_REQUIRE(n > 0 && S >= 1 && I >= 0, "nb_render_rays_fwd_noalloc: bad sizes (n = %lld, S = %d, I = %d)", (long long)n, S, I);
+  const int64_t need = nb_render_rays_workspace_bytes(n, S, I);
+  if (need > kRenderScratchBytes) {
+    nb::set_error("nb_render_rays_fwd_noalloc: %lld rays x (%d + %d) samples need %lld bytes of workspace, the built-in scratch "
+                  "holds %lld (NB_RENDER_RAYS_NOALLOC_MAX_BYTES): render fewer rays per call or use nb_render_rays_fwd",
+                  (long long)n, S, I, (long long)need, (long long)kRenderScratchBytes);
+    return NB_E_ARG;
+  }
+  void* ws = nullptr;
+  int rc = render_scratch_for_current_device(&ws);
+  if (rc) return rc;
+  return nb_render_rays_fwd(packed_coarse, packed_fine, L_pts, L_dirs, rays_o, rays_d, view_src, near_, far_, n, S, I, t_vals,
+                            t_rand, u_det, u, noise_c, noise_f, lindisp, white_bkgd, ws, kRenderScratchBytes, rgb, disp, acc,
+                            rgb0, disp0, acc0, z_std, raw_out, stream);
+}
+
+}  // extern "C"
