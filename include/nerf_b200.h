@@ -241,7 +241,8 @@ NB_API int64_t nb_mlp_act_bytes(int64_t M);
 /* Backward of the MLP from the activations nb_mlp_fwd_tc saved (autograd of nerf.py:110-134).
  * packed_bwd: transposed bf16 weight slabs (nb_mlp_pack_bwd, nb_mlp_bwd_packed_bytes bytes).
  * d_raw: [M,4] upstream gradient.  dA: scratch of nb_mlp_da_bytes(M) bytes (pre-activation
- * gradients of every layer, tiled like the activations).  grads: flat fp32 buffer the weight /
+ * gradients of every layer, tiled like the activations, followed by 544 KB in which the weight gradients whose rows
+ * are not 16-byte aligned are reduced before they are added to `grads`; private to the call).  grads: flat fp32 buffer the weight /
  * bias gradients are ACCUMULATED into (caller zeroes), laid out by grad_off_host24 (HOST array of
  * 24 float offsets: pts_linears weights 0..7, their biases 8..15, feature w/b 16,17, alpha w/b
  * 18,19, views w/b 20,21, rgb w/b 22,23); grads == NULL runs only the dgrad chain. */

@@ -437,13 +437,12 @@ __device__ __forceinline__ void wgrad_range(const WSplit& sp, const WStream& ws,
 // Padded scratch of a launch.  Three weight matrices have rows that are not 16-byte aligned (row strides in_ch,
 // 256 + in_ch and 256 + in_views floats); scalar atomics from the ~16 CTAs of such a job, all flushing the same elements
 // at the same moment, took 40-70 us (tools/wgrad_skew.py).  Their cells are reduced into padded blocks here with vector
-// atomics, and wgrad_unpad_kernel adds the blocks to the real rows and zeroes them again.  One slot per launch, taken
-// round-robin by the host (the coarse and the fine launch of a step may overlap: consecutive launches never share a slot).
+// atomics, and wgrad_unpad_kernel adds the blocks to the real rows.  The scratch is the tail of the caller's dA buffer
+// (nb_mlp_da_bytes counts it), zeroed by the call before the weight-gradient kernel starts: private to the call, so
+// launches that overlap on the GPU (the coarse and the fine branch of a step) cannot meet in it.
 //   [256][256] dW_5[:, in_ch:] | [256][64] dW_0 | [256][64] dW_5[:, :in_ch] | [128][256] dW_v[:, :256] | [128][64] dW_v[:, 256:]
 constexpr int kWScr5 = 0, kWScr0 = kWScr5 + 256 * 256, kWScr5e = kWScr0 + 256 * 64, kWScrV = kWScr5e + 256 * 64,
               kWScrVd = kWScrV + 128 * 256, kWScratchFloats = kWScrVd + 128 * 64;
-constexpr int kWScratchSlots = 8;
-__device__ __align__(256) float g_wgrad_scratch[kWScratchSlots][kWScratchFloats];
 struct WUnpad {
   int start[6];      // first scratch float of region k (start[5] = end)
   int cols_log2[5];  // padded row length
@@ -452,12 +451,11 @@ struct WUnpad {
   int64_t off[5];    // destination of element (0, 0)
 };
 
-// adds the padded scratch cells to the real gradient rows and leaves the scratch zeroed
-__global__ void __launch_bounds__(256) wgrad_unpad_kernel(float* __restrict__ scratch, float* __restrict__ grads, WUnpad u) {
+// adds the padded scratch cells to the real gradient rows
+__global__ void __launch_bounds__(256) wgrad_unpad_kernel(const float* __restrict__ scratch, float* __restrict__ grads, WUnpad u) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= kWScratchFloats) return;
   const float v = scratch[i];
-  scratch[i] = 0.f;
   int k = 0;
   while (i >= u.start[k + 1]) ++k;
   const int e = i - u.start[k], r = e >> u.cols_log2[k], c = e & ((1 << u.cols_log2[k]) - 1);
@@ -1002,19 +1000,13 @@ static int build_wjobs(const int64_t* off, int in_ch, int in_views, WJobs& jobs,
   return 0;
 }
 
-// the padded scratch slot of one weight-gradient launch (round-robin; a captured launch keeps its slot on replay)
-static int wgrad_scratch_slot(float** scratch) {
-  static unsigned next_slot = 0;
-  void* sym = nullptr;
-  cudaError_t e = cudaGetSymbolAddress(&sym, g_wgrad_scratch);   // address on the CURRENT device
-  if (e != cudaSuccess) {
-    set_error("internal: weight-gradient scratch symbol: %s", cudaGetErrorString(e));
-    return (int)e;
-  }
-  *scratch = (float*)sym + (size_t)kWScratchFloats * (__atomic_fetch_add(&next_slot, 1u, __ATOMIC_RELAXED) % kWScratchSlots);
-  return 0;
+// the padded scratch of a call: the tail of its dA buffer, zeroed on the stream the weight-gradient kernel runs on
+static float* wgrad_scratch(void* dA, int64_t tiles, cudaStream_t st) {
+  float* scratch = reinterpret_cast<float*>((uint8_t*)dA + (size_t)tiles * kDaSlabs * kSlabBytes);
+  cudaMemsetAsync(scratch, 0, sizeof(float) * (size_t)kWScratchFloats, st);
+  return scratch;
 }
-static int launch_unpad(float* scratch, float* grads, const int64_t* off, int in_ch, int in_views, cudaStream_t st) {
+static int launch_unpad(const float* scratch, float* grads, const int64_t* off, int in_ch, int in_views, cudaStream_t st) {
   WUnpad u;
   const int start[6] = {kWScr5, kWScr0, kWScr5e, kWScrV, kWScrVd, kWScratchFloats};
   for (int k = 0; k < 6; ++k) u.start[k] = start[k];
@@ -1067,7 +1059,10 @@ int64_t nb_mlp_bwd_packed_bytes(int L_pts, int L_dirs) {
   return (int64_t)kBwdSlabs * kSlabBytes + kBwdConstFloats * 4;
 }
 
-int64_t nb_mlp_da_bytes(int64_t M) { return ((M + kTileM - 1) / kTileM) * (int64_t)kDaSlabs * kSlabBytes; }
+// the dA tiles + the padded weight-gradient scratch of the call (see g_wgrad scratch layout above)
+int64_t nb_mlp_da_bytes(int64_t M) {
+  return ((M + kTileM - 1) / kTileM) * (int64_t)kDaSlabs * kSlabBytes + (int64_t)sizeof(float) * kWScratchFloats;
+}
 
 int nb_mlp_pack_bwd(const NbMlpWeights* w, void* packed_bwd, void* stream) {
   NB_REQUIRE(w && packed_bwd, "nb_mlp_pack_bwd: null pointer");
@@ -1126,11 +1121,7 @@ int nb_mlp_bwd_tc_parts(const void* packed_bwd, int L_pts, int L_dirs, const voi
       if (lim > 0 && lim < grid) grid = lim;
     }
     if (grid < 1) grid = 1;
-    float* scratch = nullptr;
-    {
-      int rc = wgrad_scratch_slot(&scratch);
-      if (rc) return rc;
-    }
+    float* scratch = wgrad_scratch(dA, tiles, st);
     if (limit_wgrad_ctas() > 0 && grid > limit_wgrad_ctas()) {
       // SM-limited launch (a concurrent kernel owns the other SMs): CTAs are placed as pairs so that they fill whole
       // TPCs and leave the remaining TPCs free for the 2-CTA clusters of the forward / dgrad kernels
@@ -1242,12 +1233,10 @@ int nb_mlp_bwd_tc_streamed(const void* packed_bwd, int L_pts, int L_dirs, const 
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
     cfg.numAttrs = 1;
-    float* scratch = nullptr;
-    int rc = wgrad_scratch_slot(&scratch);
-    if (rc) return rc;
+    float* scratch = wgrad_scratch(dA, tiles, aux->s);
     cudaLaunchKernelEx(&cfg, mlp_wgrad_kernel<true>, jobs, split, ws, (const uint8_t*)acts, (const uint8_t*)dA, (int)tiles, grads,
                        (const int*)ready, scratch);
-    rc = check_launch("mlp_wgrad_kernel<stream>");
+    int rc = check_launch("mlp_wgrad_kernel<stream>");
     if (rc) return rc;
     rc = launch_unpad(scratch, grads, grad_off_host24, in_ch, in_views, aux->s);
     if (rc) return rc;
