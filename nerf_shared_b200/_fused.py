@@ -195,9 +195,15 @@ class _Graphs:
         return g, out
 
     def forward(self, o, d, v):
-        self.inp[0].copy_(o)
-        self.inp[1].copy_(d)
-        self.inp[2].copy_(v)
+        # main.py hands over the two halves of one [2, n, 3] batch and takes the view directions from rays_d: one copy
+        # for both rays when they are adjacent in memory, one device-side copy for the directions
+        if (d.data_ptr() == o.data_ptr() + 4 * o.numel() and o.is_contiguous() and d.is_contiguous()
+                and o.untyped_storage().data_ptr() == d.untyped_storage().data_ptr()):
+            self.inp[:2].copy_(torch.as_strided(o, (2, self.n, 3), (3 * self.n, 3, 1)))
+        else:
+            self.inp[0].copy_(o)
+            self.inp[1].copy_(d)
+        self.inp[2].copy_(self.inp[1] if v.data_ptr() == d.data_ptr() else v)
         if self.fwd is None:
             rng = torch.cuda.get_rng_state(self.dev)     # the warm-up run consumes draws: the first replay gets the ones
             with torch.no_grad():                        # an uncaptured first call would have made
@@ -207,14 +213,26 @@ class _Graphs:
             torch.cuda.set_rng_state(rng, self.dev)
         self.fwd.replay()
         self.generation += 1
-        # the caller gets its own copies: the static outputs are overwritten by the next replay
-        return tuple(t.clone() for t in self.outs)
+        # the caller gets its own copies (the static outputs are overwritten by the next replay): one allocation and
+        # one multi-tensor copy launch for all of them
+        return self._copies(self.outs)
+
+    @staticmethod
+    def _copies(src):
+        flat = torch.empty((sum(t.numel() for t in src),), device=src[0].device, dtype=src[0].dtype)
+        dst, o = [], 0
+        for t in src:
+            dst.append(flat[o:o + t.numel()].view(t.shape))
+            o += t.numel()
+        torch._foreach_copy_(dst, list(src))
+        return tuple(dst)
 
     def backward(self, g_rgb, g_rgb0, white, dims):
         """-> (d_rays_o, d_rays_d, d_view_src) in pose mode, None in train mode (gradients accumulated in place)."""
-        self.g_in[0].copy_(g_rgb)
         if g_rgb0 is not None:
-            self.g_in[1].copy_(g_rgb0)
+            torch._foreach_copy_([self.g_in[0], self.g_in[1]], [g_rgb, g_rgb0])
+        else:
+            self.g_in[0].copy_(g_rgb)
         key = g_rgb0 is not None
         pose = self.mode == "pose"
         need = [not pose] * 24
@@ -228,7 +246,7 @@ class _Graphs:
             if not pose:
                 return None       # the capture's eager warm-up run already accumulated this step's gradients once
         self.bwd[key].replay()
-        return tuple(t.clone() for t in self.bwd_out[key]) if pose else None
+        return self._copies(self.bwd_out[key]) if pose else None
 
 
 def _graphs_for(r, coarse, fine, n, dev, ray_grads):

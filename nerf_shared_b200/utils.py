@@ -238,15 +238,19 @@ def _choice_without_replacement(n, k):
 
 
 def _pinned_stage(n):
-    """Rotating pinned staging buffers per batch size.  A stage is refilled only after the H2D copies that read it
-    last time have completed (`ev`, recorded by the caller after issuing them): the training loop never
-    synchronises per step, so without the event the host could run more than a ring ahead of the GPU and tear a
-    batch.  Allocated with device="cpu" explicitly: main.py:151 makes CUDA the default tensor type."""
+    """Rotating pinned staging buffers per batch size: pixel ids (int64) and target colours (fp32) of one batch in ONE
+    buffer, so that a batch is one H2D copy.  A stage is refilled only after the H2D copy that read it last time has
+    completed (`ev`, recorded by the caller after issuing it): the training loop never synchronises per step, so
+    without the event the host could run more than a ring ahead of the GPU and tear a batch.  Allocated with
+    device="cpu" explicitly: main.py:151 makes CUDA the default tensor type."""
     st = _stages.get(n)
     if st is None:
-        st = {"i": 0, "bufs": [{"pix": torch.empty(n, dtype=torch.int64, device="cpu", pin_memory=True),
-                                 "tgt": torch.empty((n, 3), dtype=torch.float32, device="cpu", pin_memory=True),
-                                 "ev": None} for _ in range(4)]}
+        bufs = []
+        for _ in range(4):
+            raw = torch.empty(20 * n, dtype=torch.uint8, device="cpu", pin_memory=True)
+            pix, tgt = raw[:8 * n].view(torch.int64), raw[8 * n:].view(torch.float32).view(n, 3)
+            bufs.append({"raw": raw, "pix": pix, "tgt": tgt, "pix_np": pix.numpy(), "tgt_np": tgt.numpy(), "ev": None})
+        st = {"i": 0, "bufs": bufs}
         _stages[n] = st
     st["i"] = (st["i"] + 1) % len(st["bufs"])
     b = st["bufs"][st["i"]]
@@ -306,15 +310,35 @@ def sample_random_ray_batch(args, images, poses, rays_rgb, N_rand, use_batching,
         # gather the N_rand target pixels on the host and ship 12 B per ray, not the whole image
         tnp = tgt.numpy() if torch.is_tensor(tgt) else tgt
         stage = _pinned_stage(N_rand)
-        stage["pix"].copy_(pix_h)
-        stage["tgt"].copy_(torch.from_numpy(np.ascontiguousarray(tnp[py, px], dtype=np.float32)))
-        pix = stage["pix"].to(device, non_blocking=True)
-        target_s = stage["tgt"].to(device, non_blocking=True)
+        np.add(py * W, px, out=stage["pix_np"], casting="unsafe")            # written straight into pinned memory
+        if tnp.dtype == np.float32 and tnp.shape[-1] == 3 and tnp.flags.c_contiguous:
+            np.take(tnp.reshape(-1, 3), stage["pix_np"], axis=0, out=stage["tgt_np"])
+        else:
+            stage["tgt_np"][...] = tnp[py, px]
+        both = stage["raw"].to(device, non_blocking=True)                     # one H2D copy per batch
         if stage["ev"] is None:
             stage["ev"] = torch.cuda.Event()
-        stage["ev"].record(torch.cuda.current_stream(pix.device))
+        stage["ev"].record(torch.cuda.current_stream(both.device))
+        pix = both[:8 * N_rand].view(torch.int64)
+        target_s = both[8 * N_rand:].view(torch.float32).view(N_rand, 3)
+        return get_ray_batch_at(H, W, K, pose, pix), target_s, rays_rgb, i_batch
     rays_o, rays_d = get_rays_at(H, W, K, pose, pix)
     return torch.stack([rays_o, rays_d], 0), target_s, rays_rgb, i_batch
+
+
+def get_ray_batch_at(H, W, K, c2w, pix):
+    """[2, n, 3] = stack(get_rays_at(...)) for a pose without gradient: the kernel writes both halves of the batch."""
+    c2w = _on_gpu(c2w)
+    if c2w.requires_grad:
+        return torch.stack(get_rays_at(H, W, K, c2w, pix), 0)
+    fx, fy, cx, cy = _intrinsics(K)
+    n = pix.numel()
+    c = _ops.f32c(c2w)
+    batch = torch.empty((2, n, 3), device=c.device, dtype=torch.float32)
+    with torch.cuda.device(c.device):
+        _ops.check(_ops._lib_for(c).nb_get_rays_sel_fwd(int(H), int(W), fx, fy, cx, cy, _ops.ptr(c), c.stride(0), _ops.ptr(pix), n,
+                                                        _ops.ptr(batch[0]), _ops.ptr(batch[1]), None, _ops.stream_ptr()), "nb_get_rays")
+    return batch
 
 
 # ----------------------------------------------------------------------------- logging / video (utils.py:330-358,458-494)

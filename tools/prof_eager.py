@@ -66,3 +66,44 @@ for i in range(300):
 pr.disable()
 torch.cuda.synchronize()
 pstats.Stats(pr, stream=sys.stdout).sort_stats("tottime").print_stats(35)
+pstats.Stats(pr, stream=sys.stdout).sort_stats("cumtime").print_stats(45)
+# host time per phase without the profiler (perf_counter around each call, no syncs)
+import collections
+acc = collections.defaultdict(float)
+def timed_one(i):
+    t = time.perf_counter
+    a = t()
+    batch_rays, target_s, _, _ = utils.sample_random_ray_batch(args, images_pinned, poses_d, None, 1024, False, None, i_train,
+                                                                hwf, K, 0, i + 1)
+    b = t(); acc["sample"] += b - a
+    rgb, _, _, extras = renderer.render_from_rays(bench.H, bench.W, K, chunk=args.chunk, rays=batch_rays, coarse_model=coarse,
+                                                  fine_model=fine, retraw=True)
+    c = t(); acc["render"] += c - b
+    opt.zero_grad()
+    d = t(); acc["zero_grad"] += d - c
+    img_loss = utils.img2mse(rgb, target_s)
+    trans = extras['raw'][..., -1]
+    loss = img_loss
+    psnr = utils.mse2psnr(img_loss)
+    img_loss0 = utils.img2mse(extras['rgb0'], target_s)
+    loss = loss + img_loss0
+    psnr0 = utils.mse2psnr(img_loss0)
+    e = t(); acc["losses"] += e - d
+    loss.backward()
+    f = t(); acc["backward"] += f - e
+    opt.step()
+    g = t(); acc["opt.step"] += g - f
+    for gr in opt.param_groups:
+        gr['lr'] = 5e-4 * (0.1 ** (i / 250000))
+    acc["lr"] += t() - g
+_orig_stage = utils._pinned_stage
+def _timed_stage(n):
+    a = time.perf_counter()
+    r = _orig_stage(n)
+    acc["(stage wait inside sample)"] += time.perf_counter() - a
+    return r
+utils._pinned_stage = _timed_stage
+for i in range(300):
+    timed_one(i)
+torch.cuda.synchronize()
+print("host ms/step by phase (no profiler):", {k: round(v / 0.3, 4) for k, v in acc.items()}, "sum", round(sum(acc.values()) / 0.3, 4))
