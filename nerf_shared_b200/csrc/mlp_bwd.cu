@@ -147,7 +147,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBwdStages; ++i) {
       mbar_init(bar_full + 8 * i, 1);
-      mbar_init(bar_empty + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 2);   // a weight slab is fetched once per step and released by BOTH tiles' MMAs
     }
     for (int x = 0; x < 2; ++x) {
       mbar_init(bar_act + 8 * x, 16);  // one arrival per epilogue warp of the tile (8), both CTAs
@@ -178,20 +178,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
     for (int quad = cluster; quad < num_quads; quad += num_clusters) {
       for (int step = 0; step < 9; ++step) {
         const int nks = bwd_ks_count(step), sb = bwd_slab_base(step);
-        for (int x = 0; x < 2; ++x) {
-          for (int ks = 0; ks < nks; ++ks) {
-            mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-            const int row0 = (sb + ks * 2 + (int)rank) * 128;  // this CTA's 128 output columns
-            if (elect_one()) {
-              if (rank == 0) mbar_expect_tx(bar_full + 8 * stage, 2 * kSlabBytes);
-              const uint32_t full_leader = full_leader0 + 8 * stage;
-              const uint32_t dst = base + kBSmRing + stage * kSlabBytes;
-              tma_load_2d_2sm(dst, &wmap, 0, row0, full_leader);
-              tma_load_2d_2sm(dst + 8192, &wmap, 0, row0 + 64, full_leader);
-            }
-            __syncwarp();
-            if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
+        // one fetch per step: the step's slabs (<= 4 of the 5 stages) stay in the ring for the MMAs of both tiles
+        for (int ks = 0; ks < nks; ++ks) {
+          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+          const int row0 = (sb + ks * 2 + (int)rank) * 128;  // this CTA's 128 output columns
+          if (elect_one()) {
+            if (rank == 0) mbar_expect_tx(bar_full + 8 * stage, 2 * kSlabBytes);
+            const uint32_t full_leader = full_leader0 + 8 * stage;
+            const uint32_t dst = base + kBSmRing + stage * kSlabBytes;
+            tma_load_2d_2sm(dst, &wmap, 0, row0, full_leader);
+            tma_load_2d_2sm(dst + 8192, &wmap, 0, row0 + 64, full_leader);
           }
+          __syncwarp();
+          if (++stage == kBwdStages) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -203,7 +202,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kBwdThreads, 1)
       for (int quad = cluster; quad < num_quads; quad += num_clusters) {
         for (int step = 0; step < 9; ++step) {
           const int nks = bwd_ks_count(step);
+          const uint32_t stage0 = stage, phase0 = phase;   // both tiles walk the same stages of the ring
           for (int x = 0; x < 2; ++x) {
+            stage = stage0;
+            phase = phase0;
             const uint32_t sAct = base + (x ? kBSmAct1 : kBSmAct0);
             if (x == 0) { mbar_wait_cluster(bar_act, par_act0); par_act0 ^= 1; }
             else { mbar_wait_cluster(bar_act + 8, par_act1); par_act1 ^= 1; }
