@@ -79,8 +79,9 @@ def test_noalloc_entry_equals_the_workspace_entry_on_two_calls_in_a_row():
             assert not torch.isnan(b).all()
             assert torch.equal(a.nan_to_num(), b.nan_to_num()), (k, n)       # same kernels, same order: the same bits
         assert float(ref[2].max()) > 0.5                                    # not a blank render
-    # the third call (every kernel's module loaded, inputs and outputs allocated before) took no device memory
-    assert free_after >= free_before, (free_before, free_after)
+    # the third call (every kernel's module loaded, inputs and outputs allocated before) took no device memory: a workspace
+    # allocated by the call would be 12.8 MB here (4 MiB of slack for other contexts on the device)
+    assert free_after >= free_before - (4 << 20), (free_before, free_after)
 
 
 def test_noalloc_entry_rejects_sizes_beyond_its_scratch():
