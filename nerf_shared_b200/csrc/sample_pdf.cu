@@ -313,22 +313,25 @@ __device__ __forceinline__ void search_step(uint32_t& addr, float u) {
 // a 65-entry histogram of the a_e.  The cdf's 62 dependent additions (torch.cumsum order) run on one lane from
 // shared memory as float4 reads / writes; every binary search is six fixed, branch-free steps.
 // Same bits as sample_pdf_merge_fast_kernel for z_out (the multiset of samples is identical).
-template <int SPT>
+// SC: the number of coarse samples as a compile-time constant (64: every shipped config; the bounds predicates fold
+// away) or 0 = the run-time value.  The host launches it with fewer than 2^31 rays: row indices are 32-bit.
+template <int SPT, int SC>
 __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const float* __restrict__ z,
                                                                       const float* __restrict__ weights,
                                                                       const float* __restrict__ u,
-                                                                      const float* __restrict__ u_det, int64_t n, int S,
+                                                                      const float* __restrict__ u_det, int64_t n, int S_rt,
                                                                       float* __restrict__ z_out, float* __restrict__ z_std) {
   constexpr int I = 32 * SPT;
+  const int S = SC ? SC : S_rt;
   // + 4: the row stride is 20 (mod 32) banks, so the eight lanes of the block-wide cumsum below read / write their
   // rows' float4 without bank conflicts
   constexpr int kQ = 0, kCdf = 64, kBins = 128, kZc = 192, kHist = 264, kOut = 336, kPerWarp = kOut + 64 + I + 4;
   __shared__ __align__(16) float smem[8][kPerWarp];
   const int lane = threadIdx.x & 31;
   const int wib = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
-  const int64_t r_raw = (int64_t)blockIdx.x * 8 + wib;
-  const bool live = r_raw < n;                 // no early exit: the block meets at two barriers
-  const int64_t r = live ? r_raw : n - 1;
+  const uint32_t r_raw = blockIdx.x * 8u + (uint32_t)wib, n32 = (uint32_t)n;
+  const bool live = r_raw < n32;               // no early exit: the block meets at two barriers
+  const uint32_t r = live ? r_raw : n32 - 1u;
   float* qv = smem[wib] + kQ;
   float* cdf = smem[wib] + kCdf;
   float* bins = smem[wib] + kBins;
@@ -336,11 +339,11 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const floa
   int* hist = reinterpret_cast<int*>(smem[wib] + kHist);
   float* outb = smem[wib] + kOut;
   const int B = S - 1;
-  const float* zr = z + r * S;
-  const float* wr = weights + r * S + 1;   // weights[..., 1:-1]: B - 1 = S - 2 entries
+  const float* zr = z + (size_t)r * (uint32_t)S;
+  const float* wr = weights + (size_t)r * (uint32_t)S + 1;   // weights[..., 1:-1]: B - 1 = S - 2 entries
   float uu[SPT];
   {
-    const float* up = (u ? u + r * I : u_det) + lane * SPT;
+    const float* up = (u ? u + (size_t)r * I : u_det) + lane * SPT;
     if constexpr (SPT == 4) {
       const float4 v = u ? __ldcs(reinterpret_cast<const float4*>(up)) : *reinterpret_cast<const float4*>(up);
       uu[0] = v.x; uu[1] = v.y; uu[2] = v.z; uu[3] = v.w;
@@ -451,6 +454,8 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const floa
     }
   }
   float smp[SPT], sum = 0.f;
+  int cnt[SPT];
+  bool any2 = false;
 #pragma unroll
   for (int k = 0; k < SPT; ++k) {
     const int below = max(pos[k] - 1, 0), above = min(B - 1, pos[k]);
@@ -462,12 +467,20 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const floa
     sum += smp[k];
     // a_e = #{coarse <= sample}: coarse[below] <= bins[below] <= sample <= bins[above] <= coarse[below + 2]
     const bool c1 = zc[below + 1] <= smp[k], c2 = zc[below + 2] <= smp[k];
-    int cnt = below + 1 + (c1 ? 1 : 0) + (c2 ? 1 : 0);
-    if (c2) {  // equal coarse depths (degenerate rays): count on
-      while (cnt < S && zc[cnt] <= smp[k]) ++cnt;
-    }
-    atomicAdd(hist + cnt, 1);
-    outb[lane * SPT + k + cnt] = smp[k];
+    cnt[k] = below + 1 + (c1 ? 1 : 0) + (c2 ? 1 : 0);
+    any2 |= c2;
+  }
+  // c2 needs sample == bins[above] == coarse[below + 2], i.e. equal coarse depths (degenerate rays): count on, for the
+  // whole warp at once and almost never
+  if (__any_sync(0xffffffffu, any2)) {
+#pragma unroll
+    for (int k = 0; k < SPT; ++k)
+      while (cnt[k] < S && zc[cnt[k]] <= smp[k]) ++cnt[k];
+  }
+#pragma unroll
+  for (int k = 0; k < SPT; ++k) {
+    atomicAdd(hist + cnt[k], 1);
+    outb[lane * SPT + k + cnt[k]] = smp[k];
   }
   if (z_std) {
     const float mean = warp_sum(sum) / (float)I;
@@ -497,7 +510,7 @@ __global__ void __launch_bounds__(256) sample_pdf_merge_sorted_kernel(const floa
   }
   __syncwarp();
   if (!live) return;
-  float* zo = z_out + r * (int64_t)(S + I);
+  float* zo = z_out + (size_t)r * (uint32_t)(S + I);
   if (S == 64 && ((uintptr_t)z_out & 15) == 0) {  // 16-byte stores ((64 + I) * 4 bytes per ray keeps the rows aligned)
     const float4* ob = reinterpret_cast<const float4*>(outb);
 #pragma unroll
@@ -541,12 +554,17 @@ int nb_sample_pdf_merge(const float* z, const float* weights, const float* u, co
   if (n == 0) return 0;
   NB_REQUIRE(z && weights && z_out && S >= 3 && I >= 1, "nb_sample_pdf_merge: bad arguments");
   NB_REQUIRE(u || u_det, "nb_sample_pdf_merge: need u or u_det");
-  if (S <= 64 && (I == 64 || I == 128) && !z_samples && (n + 7) / 8 < (1ll << 31)) {
+  if (S <= 64 && (I == 64 || I == 128) && !z_samples && n < (1ll << 31) - 8) {
     const unsigned grid = (unsigned)((n + 7) / 8);   // one warp per ray
-    if (I == 128)
-      sample_pdf_merge_sorted_kernel<4><<<grid, 256, 0, as_stream(stream)>>>(z, weights, u, u_det, n, S, z_out, z_std);
+    cudaStream_t st = as_stream(stream);
+    if (I == 128 && S == 64)
+      sample_pdf_merge_sorted_kernel<4, 64><<<grid, 256, 0, st>>>(z, weights, u, u_det, n, S, z_out, z_std);
+    else if (I == 128)
+      sample_pdf_merge_sorted_kernel<4, 0><<<grid, 256, 0, st>>>(z, weights, u, u_det, n, S, z_out, z_std);
+    else if (S == 64)
+      sample_pdf_merge_sorted_kernel<2, 64><<<grid, 256, 0, st>>>(z, weights, u, u_det, n, S, z_out, z_std);
     else
-      sample_pdf_merge_sorted_kernel<2><<<grid, 256, 0, as_stream(stream)>>>(z, weights, u, u_det, n, S, z_out, z_std);
+      sample_pdf_merge_sorted_kernel<2, 0><<<grid, 256, 0, st>>>(z, weights, u, u_det, n, S, z_out, z_std);
     return check_launch("nb_sample_pdf_merge");
   }
   if (S <= 64 && (I == 64 || I == 128)) {   // per-sample output wanted (u order): sort after the inversion
