@@ -476,6 +476,23 @@ def kernel_breakdown(a, coarse, fine, batch, dev):
     # through HBM, and that traffic (not the algorithm's) is what the weight-gradient kernel is limited by
     roof["hbm_design_traffic"] = {"bytes_per_launch": int(by), "GBps": by / t / 1e6, "frac_of_copy_peak": by / t / 1e6 / hbm,
                                   "peak": hbm, "note": "design traffic (saved bf16 activations + activation gradients), not algorithmic bytes"}
+    # the weight-gradient kernel by itself (the lumped entry above also holds the heads kernel, the unpad pass, a memset and
+    # the gaps between them): first CTA start to last CTA end of its last launch, from the kernel's own globaltimer trace
+    try:
+        buf = (C.c_uint64 * 296)()
+        bwd(True)
+        torch.cuda.synchronize()
+        if lib.nb_debug_wgrad_trace(buf, 296) == 0:
+            tt = np.array(buf[:], dtype=np.int64).reshape(148, 2)
+            t_k = float(tt[:, 1].max() - tt[:, 0].min()) / 1e6
+            w_flop = (FLOP_FWD - 2 * (256 + 384)) * M            # dW GEMMs: the forward's MACs without the two CUDA-core heads
+            w_by = 80 * 128 * M                                  # 80 operand slabs per tile: 76 distinct ones, dA_5 twice
+            per["mlp_wgrad_kernel alone (device globaltimer)"] = {
+                "ms": round(t_k, 4), "algorithmic_flop": int(w_flop), "tflops": round(w_flop / t_k / 1e9, 1),
+                "frac_tensor_burst": round(w_flop / t_k / 1e9 / burst, 3), "design_traffic_bytes": int(w_by),
+                "design_traffic_GBps": round(w_by / t_k / 1e6, 1), "design_traffic_frac_hbm": round(w_by / t_k / 1e6 / hbm, 3)}
+    except Exception as e:      # a debugging aid: never fail the bench on it
+        per["mlp_wgrad_kernel alone (device globaltimer)"] = {"error": str(e)}
     roof["per_kernel"] = per
     roof["mlp_tensor_pipe"] = {"kernel": "mlp_fwd_tc(inference 32768x192)", "tflops": per["mlp_fwd_tc(inference 32768x192)"]["tflops"],
                                "frac_of_burst_peak": round(FLOP_FWD * Mi / t_inf / 1e9 / burst, 3),
